@@ -1,0 +1,233 @@
+"""Generate tests/golden/*.npz from the REAL reference (dev container only; TEST INFRASTRUCTURE).
+
+    python -m oracle.make_golden
+
+Imports the unmodified reference from /root/reference through ``oracle.ref_shim`` and records
+small fixtures that pin the restatement in ``oracle/`` (and, on the GPU box where the reference
+tree does not exist, the CUDA path):
+
+* ``traj_tokenizer.npz`` -- utils/utils.py:13-104 (discretize_action / token_to_action /
+  str_to_float(rt2=True) / rt2_scaler / simple_scaler) and dataset.py:126-148 (denorm).
+* ``traj_vlm_tiny.npz``  -- PointLLMLlamaForCausalLM (pointllm.py:181-253) on BASELINE config A
+  (tiny, B=2, L=696): logits (sub-sampled), loss (train.py:174-181), gradients of the default
+  trainable set (model_arch.py:33-51), manual KV-cache greedy ids and poses.
+
+Weights come from ``egoscaler_b200.synth.det_state_dict`` (pure function of the state_dict keys),
+so the fixture stays small.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_shim, traj_tokenizer as tt          # noqa: E402
+from oracle.traj_vlm import LlmCfg                          # noqa: E402
+from egoscaler_b200 import synth                            # noqa: E402
+from egoscaler_b200.config import TrajVLMConfig             # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+FPS_SEED = 1234          # torch.manual_seed right before each forward (misc.py:52 draws the FPS start)
+
+
+def golden_tokenizer():
+    _, _, ru = ref_shim.load()
+    rng = np.random.default_rng(7)
+    edges = np.linspace(-1, 1, 256)
+    x32 = np.concatenate([
+        rng.uniform(-1.05, 1.05, 4096).astype(np.float32),
+        edges.astype(np.float32),                                # float32-rounded edges
+        np.nextafter(edges.astype(np.float32), np.float32(2)),
+        np.nextafter(edges.astype(np.float32), np.float32(-2)),
+        np.array([np.nan, np.inf, -np.inf, -1.0, 1.0, 0.0, -0.0, 1e-45, -1e-45, 3.4e38, -3.4e38], np.float32),
+    ])
+    x64 = np.concatenate([rng.uniform(-1.05, 1.05, 1024), edges, np.nextafter(edges, 2), np.nextafter(edges, -2)])
+    out = dict(x32=x32, q32=np.array(ru.discretize_action(x32, 256), np.int64),
+               x64=x64, q64=np.array(ru.discretize_action(x64, 256), np.int64),
+               q32_64bins=np.array(ru.discretize_action(x32, 64), np.int64))
+    ids = np.arange(256)
+    out["deq256"] = np.array(ru.token_to_action(ids.tolist(), 256), np.float64)
+    out["deq64"] = np.array(ru.token_to_action(np.arange(64).tolist(), 64), np.float64)
+    # str_to_float(rt2=True): well-formed, with a missing segment, with garbage, empty
+    strs = []
+    b = rng.integers(0, 256, (20, 6))
+    strs.append("<ts>" + "".join(" ".join(f"<p{v}>" for v in row) + "<tsep>" for row in b) + "<te>")
+    s1 = [" ".join(f"<p{v}>" for v in row) for row in b[:6]]
+    s1[2] = "<p3> <p4>"                       # malformed -> repeats previous pose
+    s1[4] = ""
+    strs.append("<tsep>".join(s1))
+    strs.append("hello <p1> <p2> <p3> <p4> <p5> <p6> world<tsep>junk<tsep><p255> <p0> <p128> <p127> <p1> <p254>")
+    strs.append("nothing here")
+    maxmin = [2.5, 0.1]
+    for i, s in enumerate(strs):
+        r = ru.str_to_float(s, maxmin, "val", rt2=True, num_bins=256)
+        out[f"s2f_{i}"] = np.zeros((0, 6), np.float32) if r is None else r
+    out["s2f_strings"] = np.array(strs)
+    out["s2f_maxmin"] = np.array(maxmin)
+    t = rng.uniform(-1, 1, (33, 6)).astype(np.float32)
+    out["scaler_in"] = t
+    out["rt2_out"] = ru.rt2_scaler(t.copy(), maxmin, "val")
+    t2 = rng.uniform(0, 100, (33, 6)).astype(np.float32)
+    out["simple_in"] = t2
+    out["simple_out"] = ru.simple_scaler(t2.copy(), maxmin)
+    # denorm (dataset.py:126-148): the method only reads self.do_norm/do_standard/mean/std
+    import importlib.util
+    cwd = os.getcwd()
+    os.chdir(os.path.join(ref_shim.REF_ROOT, "egoscaler", "models", "pointllm"))
+    sys.path.insert(0, os.getcwd())
+    try:
+        sys.modules.setdefault("utils.utils", ru)
+        src = open("dataset.py").read()
+    finally:
+        os.chdir(cwd)
+    # exec only the denorm method body against the reference's DatasetConfig
+    from egoscaler.configs.dataset import DatasetConfig as dataset_cfg
+    start = src.index("    def denorm(")
+    end = src.index("    def collate_fn(")
+    ns = {"np": np, "torch": torch, "dataset_cfg": dataset_cfg}
+    exec("class _D:\n" + src[start:end], ns)
+    D = ns["_D"]
+    tr = torch.from_numpy(rng.uniform(-1, 1, (3, 20, 6)).astype(np.float32))
+    d = D(); d.do_norm, d.do_standard = True, False
+    out["denorm_in"] = tr.numpy().copy()
+    out["denorm_norm_out"] = d.denorm(tr.clone(), None)
+    d = D(); d.do_norm, d.do_standard = False, True
+    d.mean = rng.normal(size=6); d.std = rng.uniform(0.5, 2, 6)
+    ma = rng.uniform(0.5, 3, (3, 6))
+    out["denorm_mean"], out["denorm_std"], out["denorm_max_abs"] = d.mean, d.std, ma
+    out["denorm_std_out"] = d.denorm(tr.clone(), ma)
+    # real trajectory from the reference's demo asset, normalised like denorm's inverse
+    import pickle
+    with open(os.path.join(ref_shim.REF_ROOT, "assets", "demo", "trajectory.pkl"), "rb") as f:
+        demo = pickle.load(f)
+    rv = np.asarray(demo["traj_rotvec"], np.float64)
+    out["demo_rotvec"] = rv
+    n = rv.copy()
+    n[:, 0] = (n[:, 0] - dataset_cfg.min_x) / (dataset_cfg.max_x - dataset_cfg.min_x) * 2 - 1
+    n[:, 1] = (n[:, 1] - dataset_cfg.min_y) / (dataset_cfg.max_y - dataset_cfg.min_y) * 2 - 1
+    n[:, 2] = (n[:, 2] - dataset_cfg.min_z) / (dataset_cfg.max_z - dataset_cfg.min_z) * 2 - 1
+    n[:, 3:] /= np.pi
+    out["demo_norm"] = n
+    out["demo_q"] = np.array(ru.discretize_action(n, 256), np.int64)
+    np.savez_compressed(os.path.join(GOLD, "traj_tokenizer.npz"), **out)
+    print("traj_tokenizer.npz:", {k: v.shape for k, v in out.items()})
+
+
+def _fps_start(n_points: int, batch: int) -> torch.Tensor:
+    """The draw misc.py:52 makes right after ``torch.manual_seed(FPS_SEED)``."""
+    torch.manual_seed(FPS_SEED)
+    return torch.randint(0, n_points, (batch,), dtype=torch.long)
+
+
+def _ref_forward(m, ids, mask, pc, **kw):
+    torch.manual_seed(FPS_SEED)
+    return m(input_ids=ids, attention_mask=mask, point_clouds=pc, return_dict=True, **kw)
+
+
+def golden_model(name="traj_vlm_tiny", batch=2, new_tokens=152):
+    llm = LlmCfg.tiny()
+    m = ref_shim.build_reference_model(llm)
+    sd = synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True)
+    m.load_state_dict(sd, strict=True)
+    # model_arch.py:33-51 + :110-124 : default freezing, frozen parts in eval
+    for p in m.model.point_backbone.parameters():
+        p.requires_grad = False
+    for p in m.model.layers.parameters():
+        p.requires_grad = False
+    m.train()
+    m.model.layers.eval()
+    m.model.point_backbone.eval()
+
+    cfg = TrajVLMConfig.tiny()
+    bt = synth.make_batch(cfg, batch, seed=1)
+    ids, mask, pc = bt["tokens"], bt["attention_masks"], bt["pcrgbs"]
+    P = bt["prompts"].shape[1]
+    out = dict(fps_seed=np.int64(FPS_SEED), fps_start=_fps_start(pc.shape[1], batch).numpy(),
+               tokens=ids.numpy(), prompt_len=np.int64(P),
+               torch_version=np.array(torch.__version__), transformers_version=np.array(__import__("transformers").__version__))
+
+    # ---- forward + loss + grads (train.py:166-183)
+    res = _ref_forward(m, ids, mask, pc)
+    logits = res.logits
+    lg = logits[:, P - 1:-1, :]
+    tg = ids[:, P:]
+    loss = torch.nn.functional.cross_entropy(lg.reshape(-1, lg.shape[-1]), tg.flatten(), ignore_index=llm.pad_token_id)
+    loss.backward()
+    L = logits.detach()
+    rng = np.random.default_rng(3)
+    cols = np.sort(np.concatenate([rng.choice(32000, 256, replace=False), np.arange(32000, 32262)]))
+    rows = np.sort(np.concatenate([np.arange(0, 8), np.arange(510, 530), np.arange(P - 4, L.shape[1])]))
+    out.update(logit_rows=rows, logit_cols=cols,
+               logits_sub=L[:, rows][:, :, cols].numpy(),
+               logits_argmax=L.argmax(-1).numpy(), logits_max=L.max(-1).values.numpy(),
+               logits_lse=torch.logsumexp(L, -1).numpy(),
+               loss=np.float64(loss.item()))
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        g = p.grad.detach()
+        out[f"gradnorm/{k}"] = np.float64(g.norm().item())
+        flat = g.flatten()
+        sel = torch.from_numpy(rng.choice(flat.numel(), min(4096, flat.numel()), replace=False)).long()
+        out[f"gradidx/{k}"] = sel.numpy()
+        out[f"gradval/{k}"] = flat[sel].numpy()
+    # embedding-grad rows that are touched (token rows) -- useful to check the scatter
+    eg = m.model.embed_tokens.weight.grad
+    out["embed_grad_rownorm_nonzero"] = torch.nonzero(eg.norm(dim=1) > 0).flatten().numpy()
+
+    # ---- intermediate: point tokens after projector (for encoder parity)
+    with torch.no_grad():
+        torch.manual_seed(FPS_SEED)
+        pf = m.model.point_backbone(pc)
+        out["point_feats_sub"] = pf[:, ::16, ::8].numpy()
+        out["point_proj_sub"] = m.model.point_proj(pf)[:, ::16, ::8].numpy()
+
+    # ---- manual KV-cache greedy decode (generate() is unusable under transformers 5.5)
+    m.eval()
+    with torch.no_grad():
+        seq, msk = bt["prompts"].clone(), bt["prompt_masks"].clone()
+        r = _ref_forward(m, seq, msk, pc, use_cache=True)
+        past = r.past_key_values
+        step_logits = [r.logits[:, -1].float()]
+        unfinished = torch.ones(batch, dtype=torch.long)
+        gen = []
+        for t in range(new_tokens):
+            lgt = step_logits[-1]
+            nxt = lgt.argmax(-1)
+            nxt = nxt * unfinished + llm.pad_token_id * (1 - unfinished)
+            gen.append(nxt)
+            unfinished = unfinished & (nxt != llm.eos_token_id).long()
+            msk = torch.cat((msk, torch.ones(batch, 1, dtype=torch.bool)), 1)
+            if t == new_tokens - 1 or unfinished.max() == 0:
+                break
+            r = m(input_ids=nxt[:, None], attention_mask=msk, past_key_values=past, use_cache=True, return_dict=True)
+            past = r.past_key_values
+            step_logits.append(r.logits[:, -1].float())
+        gen = torch.stack(gen, 1)
+        out["greedy_ids"] = gen.numpy()
+        sl = torch.stack(step_logits, 1)
+        out["greedy_step_logits_sub"] = sl[:, :, cols].numpy()
+        out["greedy_step_top2gap"] = (sl.topk(2, -1).values[..., 0] - sl.topk(2, -1).values[..., 1]).numpy()
+
+        # teacher-forced decode of the ground-truth trajectory tokens: ids -> poses path
+        tf_ids = ids[:, P:]
+        poses = []
+        for b in range(batch):
+            p_ = tt.ids_to_poses(tf_ids[b].tolist())
+            poses.append(p_)
+        out["tf_poses"] = np.stack(poses)
+    np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
+    print(f"{name}.npz: loss={out['loss']:.6f} greedy[0,:12]={out['greedy_ids'][0, :12]}",
+          f"size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLD, exist_ok=True)
+    torch.set_num_threads(os.cpu_count())
+    golden_tokenizer()
+    golden_model()

@@ -1,0 +1,150 @@
+"""CPU: pin the restatement in oracle/ against fixtures generated from the REAL reference
+(oracle/make_golden.py; the reference ships no tests for this path)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import traj_tokenizer as tt
+from oracle.traj_vlm import LlmCfg, PointCfg, TrajVLMOracle, train_loss, greedy_decode
+from egoscaler_b200 import synth
+from egoscaler_b200.config import TrajVLMConfig
+from conftest import GOLDEN
+
+
+@pytest.fixture(scope="module")
+def gtok():
+    return np.load(os.path.join(GOLDEN, "traj_tokenizer.npz"))
+
+
+def test_discretize_matches_reference(gtok):
+    assert np.array_equal(tt.discretize_action(gtok["x32"], 256), gtok["q32"])
+    assert np.array_equal(tt.discretize_action(gtok["x64"], 256), gtok["q64"])
+    assert np.array_equal(tt.discretize_action(gtok["x32"], 64), gtok["q32_64bins"])
+    assert np.array_equal(tt.discretize_action(gtok["demo_norm"], 256), gtok["demo_q"])
+
+
+def test_token_to_action_matches_reference(gtok):
+    assert np.array_equal(tt.token_to_action(np.arange(256), 256), gtok["deq256"])
+    assert np.array_equal(tt.token_to_action(np.arange(64), 64), gtok["deq64"])
+
+
+def test_str_to_float_matches_reference(gtok):
+    maxmin = gtok["s2f_maxmin"].tolist()
+    for i, s in enumerate(gtok["s2f_strings"].tolist()):
+        r = tt.str_to_float_rt2(s, maxmin)
+        ref = gtok[f"s2f_{i}"]
+        if ref.shape[0] == 0:
+            assert r is None
+        else:
+            assert r.dtype == np.float32 and np.array_equal(r, ref)
+
+
+def test_scalers_and_denorm_match_reference(gtok):
+    maxmin = gtok["s2f_maxmin"].tolist()
+    assert np.array_equal(tt.rt2_scaler(gtok["scaler_in"].copy(), maxmin), gtok["rt2_out"])
+    assert np.array_equal(tt.simple_scaler(gtok["simple_in"].copy(), maxmin), gtok["simple_out"])
+    assert np.array_equal(tt.denorm(gtok["denorm_in"], True), gtok["denorm_norm_out"])
+    out = tt.denorm(gtok["denorm_in"], False, gtok["denorm_max_abs"], gtok["denorm_mean"], gtok["denorm_std"])
+    assert np.array_equal(out, gtok["denorm_std_out"])
+
+
+def test_ids_to_poses_equals_string_path(gtok):
+    rng = np.random.default_rng(0)
+    b = rng.integers(0, 256, (20, 6))
+    ids = [tt.TS_TOKEN]
+    for row in b:
+        ids += (row + tt.TRAJ_TOKEN_BASE).tolist() + [tt.TSEP_TOKEN]
+    ids += [tt.TE_TOKEN, 2, 0, 0]
+    s = "<ts>" + "".join(" ".join(f"<p{v}>" for v in row) + "<tsep>" for row in b) + "<te>"
+    a = tt.ids_to_poses(ids)
+    r = tt.str_to_float_rt2(s, None, scale=False)
+    assert np.array_equal(a, r)
+
+
+# ------------------------------------------------------------------ model
+@pytest.fixture(scope="module")
+def gm():
+    return np.load(os.path.join(GOLDEN, "traj_vlm_tiny.npz"))
+
+
+@pytest.fixture(scope="module")
+def oracle_model():
+    torch.manual_seed(0)
+    m = TrajVLMOracle(LlmCfg.tiny(), PointCfg())
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    m.configure_trainable()
+    m.eval()
+    return m
+
+
+def test_oracle_state_dict_keys_match_reference(oracle_model, gm):
+    keys = set(oracle_model.state_dict().keys())
+    gk = {k.split("/", 1)[1] for k in gm.files if k.startswith("gradnorm/")}
+    assert gk <= keys
+    assert "model.layers.0.self_attn.q_proj.weight" in keys and "lm_head.weight" in keys
+    assert "model.point_backbone.encoder.first_conv.1.running_mean" in keys
+
+
+def test_oracle_forward_loss_grads_match_reference(oracle_model, gm):
+    m = oracle_model
+    bt = synth.make_batch(TrajVLMConfig.tiny(), 2, seed=1)
+    assert np.array_equal(bt["tokens"].numpy(), gm["tokens"])
+    P = int(gm["prompt_len"])
+    start = torch.from_numpy(gm["fps_start"])
+    logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=start, training=True)
+    loss = train_loss(logits, bt["tokens"], P, 0)
+    loss.backward()
+    L = logits.detach()
+    sub = L[:, gm["logit_rows"]][:, :, gm["logit_cols"]].numpy()
+    np.testing.assert_allclose(sub, gm["logits_sub"], atol=2e-4, rtol=1e-4)
+    np.testing.assert_allclose(torch.logsumexp(L, -1).numpy(), gm["logits_lse"], atol=2e-4, rtol=1e-5)
+    assert (L.argmax(-1).numpy() == gm["logits_argmax"]).mean() > 0.999
+    assert abs(loss.item() - float(gm["loss"])) < 1e-4
+    n = 0
+    for k, p in m.named_parameters():
+        if f"gradnorm/{k}" not in gm.files:
+            assert p.grad is None or not p.requires_grad or p.grad.abs().max() == 0, k
+            continue
+        g = p.grad.flatten()
+        ref = gm[f"gradval/{k}"]
+        got = g[torch.from_numpy(gm[f"gradidx/{k}"])].numpy()
+        np.testing.assert_allclose(got, ref, atol=1e-6 + 1e-3 * np.abs(ref).max(), rtol=1e-3, err_msg=k)
+        assert abs(g.norm().item() - float(gm[f"gradnorm/{k}"])) <= 1e-3 * float(gm[f"gradnorm/{k}"]) + 1e-9, k
+        n += 1
+    assert n >= 9      # embed, lm_head, norm, 6 projector tensors
+
+
+def test_oracle_point_encoder_matches_reference(oracle_model, gm):
+    bt = synth.make_batch(TrajVLMConfig.tiny(), 2, seed=1)
+    with torch.no_grad():
+        pf = oracle_model.model.point_backbone(bt["pcrgbs"], torch.from_numpy(gm["fps_start"]))
+        pp = oracle_model.model.point_proj(pf)
+    np.testing.assert_allclose(pf[:, ::16, ::8].numpy(), gm["point_feats_sub"], atol=1e-4, rtol=1e-4)
+    np.testing.assert_allclose(pp[:, ::16, ::8].numpy(), gm["point_proj_sub"], atol=1e-4, rtol=1e-4)
+
+
+def test_oracle_greedy_decode_matches_reference(oracle_model, gm):
+    bt = synth.make_batch(TrajVLMConfig.tiny(), 2, seed=1)
+    T = gm["greedy_ids"].shape[1]
+    ids, scores = greedy_decode(oracle_model, bt["prompts"], bt["prompt_masks"], bt["pcrgbs"], T,
+                                fps_start=torch.from_numpy(gm["fps_start"]), return_scores=True)
+    P = bt["prompts"].shape[1]
+    gen = ids[:, P:].numpy()
+    gap = gm["greedy_step_top2gap"]
+    agree = gen[:, :gap.shape[1]] == gm["greedy_ids"][:, :gap.shape[1]]
+    # ids must agree wherever the reference's own top-2 margin is above fp32 noise
+    assert agree[gap > 1e-3].all()
+    sl = torch.stack(scores, 1)[:, :, gm["logit_cols"]].numpy()
+    n = min(sl.shape[1], gm["greedy_step_logits_sub"].shape[1])
+    np.testing.assert_allclose(sl[:, :n], gm["greedy_step_logits_sub"][:, :n], atol=5e-4, rtol=1e-4)
+
+
+def test_teacher_forced_poses(gm):
+    P = int(gm["prompt_len"])
+    for b in range(2):
+        p = tt.ids_to_poses(gm["tokens"][b, P:].tolist())
+        # the prompt holds <ts> + first pose + <tsep>; 19 poses follow, and the trailing "<te>" segment
+        # has no match so it repeats the last pose (utils.py:91-93) -> 20 rows
+        assert p.shape == (20, 6) and np.array_equal(p[-1], p[-2]) and np.array_equal(p, gm["tf_poses"][b])
