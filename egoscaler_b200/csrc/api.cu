@@ -1,0 +1,79 @@
+// extern "C" surface of libegoscaler_b200.so (declared in include/egoscaler_b200.h) + error plumbing.
+#include "esb_internal.h"
+#include "esb_ops.h"
+#include "../../include/egoscaler_b200.h"
+
+#include <cstdarg>
+#include <cstdio>
+
+namespace esb {
+
+static thread_local char g_err[512] = "";
+
+void set_last_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_last_error("%s: %s", what, cudaGetErrorString(e));
+        return -3;
+    }
+    return 0;
+}
+
+int device_sm_count() {
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (sms[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        sms[dev] = v;
+    }
+    return sms[dev];
+}
+
+}  // namespace esb
+
+using namespace esb;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int esb_version(void) { return 100; }
+const char* esb_last_error(void) { return last_error(); }
+int esb_device_sm_count(void) { return device_sm_count(); }
+
+int esb_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
+                  const float* bias, const void* residual, int64_t ldr, int act, int out_fp32, int accumulate,
+                  float alpha, int force_bn, void* stream) {
+    return gemm_bf16(A, lda, B, ldb, C, ldc, M, N, K, bias, residual, ldr, act, out_fp32, accumulate, alpha, force_bn,
+                     ST(stream));
+}
+
+int esb_traj_quantize(const void* x, int is_f64, int64_t n, int num_bins, int64_t id_offset, int64_t* out, void* stream) {
+    return traj_quantize(x, is_f64, n, num_bins, id_offset, reinterpret_cast<long long*>(out), ST(stream));
+}
+int esb_traj_dequantize(const int64_t* ids, int64_t n_poses, int num_bins, int64_t id_offset, int scale_mode,
+                        double d_max, double d_min, float* out, void* stream) {
+    return traj_dequantize(reinterpret_cast<const long long*>(ids), n_poses, num_bins, id_offset, scale_mode, d_max,
+                           d_min, out, ST(stream));
+}
+int esb_traj_scale(float* poses, int64_t n_poses, int scale_mode, double d_max, double d_min, void* stream) {
+    return traj_scale(poses, n_poses, scale_mode, d_max, d_min, ST(stream));
+}
+int esb_traj_ids_to_poses(const int64_t* ids, int B, int T, int num_bins, int64_t base_id, int64_t tsep_id,
+                          int64_t eos_id, int scale_mode, double d_max, double d_min, int max_steps, int pad_repeat,
+                          float* out, int32_t* count, void* stream) {
+    return traj_ids_to_poses(reinterpret_cast<const long long*>(ids), B, T, num_bins, base_id, tsep_id, eos_id,
+                             scale_mode, d_max, d_min, max_steps, pad_repeat, out, count, ST(stream));
+}
+
+}  // extern "C"

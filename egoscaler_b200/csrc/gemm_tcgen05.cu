@@ -1,0 +1,366 @@
+// bf16 GEMM on the 5th-generation tensor cores:  C[M,N] = epilogue(A[M,K] * B[N,K]^T)
+//
+// This is the contraction every Linear on the trajectory-VLM hot path reduces to (reference call sites:
+// HF LlamaAttention/LlamaMLP reached from pointllm/model/pointllm.py:173-178, lm_head pointllm.py:228,
+// point_proj pointllm.py:67-81,129, PointBERT Linear/Conv1d(k=1) layers point_encoder.py:11-55, dvae.py:194-205).
+// Weights are stored [out_features, in_features] exactly like the reference state_dict, i.e. B is K-major.
+//
+// Structure (persistent, warp-specialised, one CTA per SM):
+//   warp 0 lane 0 : TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
+//   warp 1 lane 0 : MMA issuer     (tcgen05.mma cta_group::1 kind::f16, 128 x BN x 16, fp32 accum in TMEM)
+//   warp 2        : TMEM allocator (2 accumulator stages = 2*BN columns)
+//   warps 4..7    : epilogue       (tcgen05.ld 32x32b -> bias / activation / residual -> bf16|fp32 global)
+// Pipelines: smem ring full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue), static tile scheduler.
+// Ragged M/N/K edges rely on TMA zero fill for loads and on masked stores in the epilogue.
+#include "common.cuh"
+#include "esb_internal.h"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+
+namespace esb {
+
+constexpr int BM = 128;
+constexpr int BK = 64;   // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 256;
+
+struct GemmParams {
+    int M, N, K;
+    void* C;
+    long long ldc;
+    const float* bias;        // [N] or null
+    const __nv_bfloat16* res; // [M, ldr] or null
+    long long ldr;
+    int act;                  // 0 none, 1 gelu(erf), 2 relu
+    int out_fp32;             // 0 -> bf16 out, 1 -> fp32 out
+    int accumulate;           // fp32 out only: C += result
+    float alpha;              // scales the product before bias
+    int tiles_m, tiles_n;
+};
+
+template <int BN>
+struct GemmSmem {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int BAR_BYTES = 1024;
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024;   // +1024 alignment slack
+};
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const GemmParams p) {
+    using S = GemmSmem<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* tiles = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::STAGES * S::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + S::STAGES;
+    uint64_t* tmem_full = bars + 2 * S::STAGES;
+    uint64_t* tmem_empty = bars + 2 * S::STAGES + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int num_kb = (p.K + BK - 1) / BK;
+    const int num_tiles = p.tiles_m * p.tiles_n;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < S::STAGES; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 128);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(tmem_slot, 2 * BN);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===================== TMA producer
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t % p.tiles_m) * BM;
+                const int n0 = (t / p.tiles_m) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    uint8_t* sa = tiles + stage * S::STAGE_BYTES;
+                    uint8_t* sb = sa + S::A_BYTES;
+                    mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+                    tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m0);
+                    tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n0);
+                    if (++stage == S::STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===================== MMA issuer
+            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(tiles + stage * S::STAGE_BYTES);
+                    const uint32_t sb = sa + S::A_BYTES;
+                    const uint64_t da = umma_desc_kmajor_sw128(sa);
+                    const uint64_t db = umma_desc_kmajor_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
+                        umma_bf16_ss(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k), idesc,
+                                     (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);       // smem slot reusable once these MMAs retire
+                    if (++stage == S::STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(&tmem_full[acc]);             // accumulator complete -> epilogue
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue: TMEM -> registers -> global
+        const int q = warp & 3;                            // TMEM lane quarter this warp may access
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        const bool vec_ok_bf16 = (!p.out_fp32) && ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+        const bool vec_ok_f32 = (p.out_fp32) && ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+        const bool res_vec_ok = p.res && ((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.res) & 15) == 0);
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const int m0 = (t % p.tiles_m) * BM;
+            const int n0 = (t / p.tiles_m) * BN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const bool row_ok = row < p.M;
+            const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int col0 = n0 + c * 32;
+                if (col0 >= p.N) break;                    // warp-uniform
+                uint32_t r[32];
+                tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
+                tmem_ld_wait();
+                const int ncols = min(32, p.N - col0);
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                if (p.bias) {
+                    if (ncols == 32) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
+                    }
+                }
+                if (p.act == 1) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                } else if (p.act == 2) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+                }
+                if (row_ok) {
+                    if (p.res) {
+                        const __nv_bfloat16* rp = p.res + static_cast<long long>(row) * p.ldr + col0;
+                        if (res_vec_ok && ncols == 32) {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + g);
+                                const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
+                                             d = unpack_bf16x2(u.w);
+                                v[g * 8 + 0] += a.x; v[g * 8 + 1] += a.y; v[g * 8 + 2] += b.x; v[g * 8 + 3] += b.y;
+                                v[g * 8 + 4] += cc.x; v[g * 8 + 5] += cc.y; v[g * 8 + 6] += d.x; v[g * 8 + 7] += d.y;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < ncols) v[j] += __bfloat162float(rp[j]);
+                        }
+                    }
+                    if (!p.out_fp32) {
+                        __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+                        if (vec_ok_bf16 && ncols == 32) {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                uint4 u;
+                                u.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+                                u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+                                u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+                                u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+                                reinterpret_cast<uint4*>(cp)[g] = u;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < ncols) cp[j] = __float2bfloat16_rn(v[j]);
+                        }
+                    } else {
+                        float* cp = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+                        if (vec_ok_f32 && ncols == 32) {
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) {
+                                float4 u = make_float4(v[g * 4 + 0], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+                                if (p.accumulate) {
+                                    const float4 o = reinterpret_cast<float4*>(cp)[g];
+                                    u.x += o.x; u.y += o.y; u.z += o.z; u.w += o.w;
+                                }
+                                reinterpret_cast<float4*>(cp)[g] = u;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < ncols) cp[j] = p.accumulate ? cp[j] + v[j] : v[j];
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1u;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 2 * BN);
+    }
+}
+
+// ----------------------------------------------------------------------------- host side
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static void load_encode() {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+        g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+}
+
+// 2-D bf16 row-major [rows, cols] tensor with leading dimension ld (elements); box = {64 cols, box_rows}.
+int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
+    std::call_once(g_encode_once, load_encode);
+    if (!g_encode) {
+        set_last_error("cuTensorMapEncodeTiled entry point unavailable");
+        return ESB_ERR_DRIVER;
+    }
+    cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_last_error("cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld ptr=%p", (int)r, rows, cols, ld, ptr);
+        return ESB_ERR_DRIVER;
+    }
+    return ESB_OK;
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
+    using S = GemmSmem<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        if (e != cudaSuccess) {
+            set_last_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e));
+            return ESB_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    p.tiles_m = (p.M + BM - 1) / BM;
+    p.tiles_n = (p.N + BN - 1) / BN;
+    const int tiles = p.tiles_m * p.tiles_n;
+    const int grid = tiles < sms ? tiles : sms;
+    gemm_bf16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
+    return check_launch("gemm_bf16_tcgen05");
+}
+
+int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* C, long long ldc, int M, int N, int K,
+              const float* bias, const void* residual, long long ldr, int act, int out_fp32, int accumulate, float alpha,
+              int force_bn, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return ESB_OK;
+    if (K <= 0 || !A || !B || !C) {
+        set_last_error("gemm_bf16: bad arguments (M=%d N=%d K=%d)", M, N, K);
+        return ESB_ERR_INVALID_ARG;
+    }
+    if ((lda & 7) || (ldb & 7) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) {
+        set_last_error("gemm_bf16: A/B must be 16-byte aligned with leading dimensions that are multiples of 8 (lda=%lld ldb=%lld)",
+                       lda, ldb);
+        return ESB_ERR_INVALID_ARG;
+    }
+    if (accumulate && !out_fp32) {
+        set_last_error("gemm_bf16: accumulate requires fp32 output");
+        return ESB_ERR_INVALID_ARG;
+    }
+    const int sms = device_sm_count();
+    int bn = force_bn;
+    if (bn == 0) {
+        if (N <= 64) bn = 64;
+        else if (N <= 128) bn = 128;
+        else {
+            const long long t256 = static_cast<long long>((M + BM - 1) / BM) * ((N + 255) / 256);
+            bn = (t256 >= sms) ? 256 : 128;
+            if (bn == 128) {
+                const long long t128 = static_cast<long long>((M + BM - 1) / BM) * ((N + 127) / 128);
+                if (t128 < sms / 2) bn = 64;
+            }
+        }
+    }
+    CUtensorMap ta, tb;
+    int rc = make_tma_2d_bf16(&ta, A, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tma_2d_bf16(&tb, B, N, K, ldb, bn);
+    if (rc) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.bias = bias;
+    p.res = reinterpret_cast<const __nv_bfloat16*>(residual); p.ldr = ldr;
+    p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
+    p.tiles_m = p.tiles_n = 0;
+    switch (bn) {
+        case 256: return launch_gemm<256>(ta, tb, p, stream, sms);
+        case 128: return launch_gemm<128>(ta, tb, p, stream, sms);
+        case 64: return launch_gemm<64>(ta, tb, p, stream, sms);
+        default:
+            set_last_error("gemm_bf16: unsupported BN %d", bn);
+            return ESB_ERR_INVALID_ARG;
+    }
+}
+
+}  // namespace esb

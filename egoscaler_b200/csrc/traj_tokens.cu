@@ -1,0 +1,236 @@
+// Trajectory token <-> continuous 6DoF pose kernels (bit-exact with the reference NumPy code).
+//
+// Reference: egoscaler/models/pointllm/utils/utils.py
+//   discretize_action :13-16   np.digitize(x, np.linspace(-1, 1, num_bins)) - 1
+//   token_to_action   :18-21   np.linspace(-1, 1, num_bins)[id]           (left bin edge, float64)
+//   rt2_scaler        :23-34   rot * pi ; z -> [d_min, d_max] ; x,y pixel -> metric (f=605.343, c=703.5)
+//   simple_scaler     :36-45
+//   str_to_float      :47-104  split on <tsep>, first run of 6 <p*> tokens per segment, repeat previous on a miss,
+//                              float32 cast (:96) before the scaler
+// and dataset.py:126-148 (denorm, do_norm branch), train.py:251-255 (pad by repeating the last frame).
+//
+// Exactness notes.  np.linspace builds edge i as  i*step + start  in float64 (two roundings, last edge forced to
+// `stop`); the kernels rebuild that table with __dmul_rn/__dadd_rn (no FMA contraction) and bracket every input
+// against it, so values sitting exactly on an edge, NaN (-> last bin), +-inf and out-of-range inputs land where
+// np.digitize puts them.  The float32 scalers use explicit _rn intrinsics so nvcc cannot fuse mul+add.
+#include "common.cuh"
+#include "esb_internal.h"
+
+namespace esb {
+
+constexpr int kMaxBins = 1024;
+
+ESB_DEVICE void build_edges(double* edges, int num_bins) {
+    const double step = __ddiv_rn(2.0, static_cast<double>(num_bins - 1));
+    for (int i = threadIdx.x; i < num_bins; i += blockDim.x)
+        edges[i] = (i == num_bins - 1) ? 1.0 : __dadd_rn(__dmul_rn(static_cast<double>(i), step), -1.0);
+    __syncthreads();
+}
+
+// number of edges <= x, minus one  (np.digitize(x, edges, right=False) - 1); NaN sorts last.
+ESB_DEVICE int digitize_m1(double x, const double* edges, int num_bins) {
+    if (x != x) return num_bins - 1;
+    double g = floor((x + 1.0) * (0.5 * static_cast<double>(num_bins - 1)));
+    int b = g < -1.0 ? -1 : (g > static_cast<double>(num_bins - 1) ? num_bins - 1 : static_cast<int>(g));
+    while (b + 1 < num_bins && edges[b + 1] <= x) ++b;
+    while (b >= 0 && edges[b] > x) --b;
+    return b;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) traj_quantize_kernel(const T* __restrict__ x, long long n, int num_bins,
+                                                            long long id_offset, long long* __restrict__ out) {
+    __shared__ double edges[kMaxBins];
+    build_edges(edges, num_bins);
+    const long long nvec = n >> 2;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        T v[4];
+        if constexpr (sizeof(T) == 4) {
+            const float4 f = __ldg(reinterpret_cast<const float4*>(x) + i);
+            v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+        } else {
+            const double2 a = __ldg(reinterpret_cast<const double2*>(x) + 2 * i);
+            const double2 b = __ldg(reinterpret_cast<const double2*>(x) + 2 * i + 1);
+            v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+        }
+        longlong2 o0, o1;
+        o0.x = digitize_m1(static_cast<double>(v[0]), edges, num_bins) + id_offset;
+        o0.y = digitize_m1(static_cast<double>(v[1]), edges, num_bins) + id_offset;
+        o1.x = digitize_m1(static_cast<double>(v[2]), edges, num_bins) + id_offset;
+        o1.y = digitize_m1(static_cast<double>(v[3]), edges, num_bins) + id_offset;
+        reinterpret_cast<longlong2*>(out)[2 * i] = o0;
+        reinterpret_cast<longlong2*>(out)[2 * i + 1] = o1;
+    }
+    // tail
+    for (long long i = (nvec << 2) + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+        out[i] = digitize_m1(static_cast<double>(x[i]), edges, num_bins) + id_offset;
+}
+
+// mode: 0 none (left bin edge as float32), 1 rt2_scaler, 2 simple_scaler, 3 denorm(do_norm)
+ESB_DEVICE void scale_pose(float* p, int mode, float d_max_minus_min, float d_min) {
+    const float kPi = 3.14159274101257324f;          // float32(np.pi)
+    if (mode == 1) {
+        p[3] = __fmul_rn(kPi, p[3]); p[4] = __fmul_rn(kPi, p[4]); p[5] = __fmul_rn(kPi, p[5]);
+        float z = __fadd_rn(__fmul_rn(0.5f, p[2]), 0.5f);
+        z = __fadd_rn(__fmul_rn(d_max_minus_min, z), d_min);
+        p[2] = z;
+        float x = __fadd_rn(__fmul_rn(704.0f, p[0]), 704.0f);
+        p[0] = __fdiv_rn(__fmul_rn(__fsub_rn(x, 703.5f), z), 605.343f);
+        float y = __fadd_rn(__fmul_rn(704.0f, p[1]), 704.0f);
+        p[1] = __fdiv_rn(__fmul_rn(__fsub_rn(y, 703.5f), z), 605.343f);
+    } else if (mode == 2) {
+#pragma unroll
+        for (int j = 3; j < 6; ++j)
+            p[j] = __fmul_rn(kPi, __fsub_rn(__fmul_rn(2.0f, __fdiv_rn(p[j], 100.0f)), 1.0f));
+        float z = __fdiv_rn(p[2], 100.0f);
+        z = __fadd_rn(__fmul_rn(z, d_max_minus_min), d_min);
+        p[2] = z;
+        p[0] = __fdiv_rn(__fmul_rn(__fsub_rn(p[0], 703.5f), z), 605.343f);
+        p[1] = __fdiv_rn(__fmul_rn(__fsub_rn(p[1], 703.5f), z), 605.343f);
+    } else if (mode == 3) {
+        // egoscaler/configs/dataset.py:1-6 : x,y in [-2,2], z in [0,2.5]
+#pragma unroll
+        for (int j = 0; j < 3; ++j) p[j] = __fdiv_rn(__fadd_rn(p[j], 1.0f), 2.0f);
+        p[0] = __fadd_rn(__fmul_rn(p[0], 4.0f), -2.0f);
+        p[1] = __fadd_rn(__fmul_rn(p[1], 4.0f), -2.0f);
+        p[2] = __fadd_rn(__fmul_rn(p[2], 2.5f), 0.0f);
+        p[3] = __fmul_rn(p[3], kPi); p[4] = __fmul_rn(p[4], kPi); p[5] = __fmul_rn(p[5], kPi);
+    }
+}
+
+// One thread per pose: 6 ids (int64) -> 6 float32, optional scaler.  Invalid ids give NaN.
+__global__ void __launch_bounds__(256) traj_dequantize_kernel(const long long* __restrict__ ids, long long n_poses,
+                                                              int num_bins, long long id_offset, int mode,
+                                                              float d_max_minus_min, float d_min, float* __restrict__ out) {
+    __shared__ double edges[kMaxBins];
+    build_edges(edges, num_bins);
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_poses; i += stride) {
+        const longlong2* ip = reinterpret_cast<const longlong2*>(ids + 6 * i);
+        const longlong2 a = __ldg(ip), b = __ldg(ip + 1), c = __ldg(ip + 2);
+        const long long id[6] = {a.x, a.y, b.x, b.y, c.x, c.y};
+        float p[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            const long long k = id[j] - id_offset;
+            p[j] = (k >= 0 && k < num_bins) ? static_cast<float>(edges[k]) : __int_as_float(0x7fc00000);
+        }
+        scale_pose(p, mode, d_max_minus_min, d_min);
+        float2* op = reinterpret_cast<float2*>(out + 6 * i);
+        op[0] = make_float2(p[0], p[1]); op[1] = make_float2(p[2], p[3]); op[2] = make_float2(p[4], p[5]);
+    }
+}
+
+__global__ void __launch_bounds__(256) traj_scale_kernel(float* __restrict__ poses, long long n_poses, int mode,
+                                                         float d_max_minus_min, float d_min) {
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_poses; i += stride) {
+        float p[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) p[j] = poses[6 * i + j];
+        scale_pose(p, mode, d_max_minus_min, d_min);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) poses[6 * i + j] = p[j];
+    }
+}
+
+// Generated token ids -> poses, one thread per sequence (the sequential <tsep>/regex logic of str_to_float).
+// ids [B, T]; out [B, max_steps, 6]; count[B] = number of parsed timesteps (before padding).
+__global__ void traj_ids_to_poses_kernel(const long long* __restrict__ ids, int B, int T, int num_bins, long long base,
+                                         long long tsep, long long eos, int mode, float d_max_minus_min, float d_min,
+                                         int max_steps, int pad_repeat, float* __restrict__ out, int* __restrict__ count) {
+    __shared__ double edges[kMaxBins];
+    build_edges(edges, num_bins);
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const long long* row = ids + static_cast<long long>(b) * T;
+    float* o = out + static_cast<long long>(b) * max_steps * 6;
+    int n = 0;
+    bool have_last = false, found = false, stop = false;
+    float last[6], cur[6];
+    int run = 0;
+    for (int t = 0; t <= T && !stop; ++t) {
+        const long long tok = (t < T) ? row[t] : eos;
+        const bool end = (t == T) || (tok == eos);
+        if (end || tok == tsep) {
+            // close the segment
+            if (found) {
+#pragma unroll
+                for (int j = 0; j < 6; ++j) last[j] = cur[j];
+                have_last = true;
+            }
+            if ((found || have_last) && n < max_steps) {
+#pragma unroll
+                for (int j = 0; j < 6; ++j) o[n * 6 + j] = last[j];
+                ++n;
+            }
+            found = false;
+            run = 0;
+            if (end) stop = true;
+        } else if (!found) {
+            if (tok >= base && tok < base + num_bins) {
+                cur[run++] = static_cast<float>(edges[tok - base]);
+                if (run == 6) found = true;
+            } else {
+                run = 0;
+            }
+        }
+    }
+    for (int s = 0; s < n; ++s) scale_pose(o + s * 6, mode, d_max_minus_min, d_min);
+    count[b] = n;
+    if (pad_repeat && n > 0)
+        for (int s = n; s < max_steps; ++s)
+#pragma unroll
+            for (int j = 0; j < 6; ++j) o[s * 6 + j] = o[(n - 1) * 6 + j];
+}
+
+static int grid_for(long long work_items, int block, int per_sm) {
+    const long long want = (work_items + block - 1) / block;
+    const long long cap = static_cast<long long>(device_sm_count()) * per_sm;
+    long long g = want < cap ? want : cap;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+
+int traj_quantize(const void* x, int is_f64, long long n, int num_bins, long long id_offset, long long* out,
+                  cudaStream_t s) {
+    if (num_bins < 2 || num_bins > kMaxBins) { set_last_error("traj_quantize: num_bins %d out of [2,%d]", num_bins, kMaxBins); return ESB_ERR_INVALID_ARG; }
+    if (n <= 0) return ESB_OK;
+    if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) { set_last_error("traj_quantize: pointers must be 16-byte aligned"); return ESB_ERR_INVALID_ARG; }
+    const int grid = grid_for((n + 3) / 4, 256, 8);
+    if (is_f64) traj_quantize_kernel<double><<<grid, 256, 0, s>>>(static_cast<const double*>(x), n, num_bins, id_offset, out);
+    else traj_quantize_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(x), n, num_bins, id_offset, out);
+    return check_launch("traj_quantize");
+}
+
+int traj_dequantize(const long long* ids, long long n_poses, int num_bins, long long id_offset, int mode, double d_max,
+                    double d_min, float* out, cudaStream_t s) {
+    if (num_bins < 2 || num_bins > kMaxBins || mode < 0 || mode > 3) { set_last_error("traj_dequantize: bad num_bins/mode"); return ESB_ERR_INVALID_ARG; }
+    if (n_poses <= 0) return ESB_OK;
+    if ((reinterpret_cast<uintptr_t>(ids) & 15) || (reinterpret_cast<uintptr_t>(out) & 7)) { set_last_error("traj_dequantize: misaligned pointers"); return ESB_ERR_INVALID_ARG; }
+    // (d_max - d_min) is formed in float64 by the reference and rounded to float32 when it meets the array
+    const float dmm = static_cast<float>(d_max - d_min);
+    traj_dequantize_kernel<<<grid_for(n_poses, 256, 8), 256, 0, s>>>(ids, n_poses, num_bins, id_offset, mode, dmm,
+                                                                     static_cast<float>(d_min), out);
+    return check_launch("traj_dequantize");
+}
+
+int traj_scale(float* poses, long long n_poses, int mode, double d_max, double d_min, cudaStream_t s) {
+    if (mode < 1 || mode > 3) { set_last_error("traj_scale: bad mode %d", mode); return ESB_ERR_INVALID_ARG; }
+    if (n_poses <= 0) return ESB_OK;
+    traj_scale_kernel<<<grid_for(n_poses, 256, 8), 256, 0, s>>>(poses, n_poses, mode, static_cast<float>(d_max - d_min), static_cast<float>(d_min));
+    return check_launch("traj_scale");
+}
+
+int traj_ids_to_poses(const long long* ids, int B, int T, int num_bins, long long base, long long tsep, long long eos,
+                      int mode, double d_max, double d_min, int max_steps, int pad_repeat, float* out, int* count,
+                      cudaStream_t s) {
+    if (num_bins < 2 || num_bins > kMaxBins || mode < 0 || mode > 3 || max_steps < 1) { set_last_error("traj_ids_to_poses: bad arguments"); return ESB_ERR_INVALID_ARG; }
+    if (B <= 0) return ESB_OK;
+    traj_ids_to_poses_kernel<<<(B + 63) / 64, 64, 0, s>>>(ids, B, T, num_bins, base, tsep, eos, mode,
+                                                          static_cast<float>(d_max - d_min), static_cast<float>(d_min),
+                                                          max_steps, pad_repeat, out, count);
+    return check_launch("traj_ids_to_poses");
+}
+
+}  // namespace esb
