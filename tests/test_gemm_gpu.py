@@ -1,0 +1,58 @@
+"""GPU: tcgen05 GEMM vs a plain fp32 torch reference of the same contraction (floating-point kernel)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from egoscaler_b200 import ops
+
+
+def _ref(a, w, bias=None, res=None, act=0, alpha=1.0):
+    y = alpha * (a.float() @ w.float().t())
+    if bias is not None:
+        y = y + bias
+    if act == 1:
+        y = torch.nn.functional.gelu(y)
+    elif act == 2:
+        y = torch.relu(y)
+    if res is not None:
+        y = y + res.float()
+    return y
+
+
+SHAPES = [(128, 256, 64), (128, 256, 256), (256, 512, 4096), (1392, 768, 256), (1026, 1152, 384), (300, 688, 256),
+          (77, 40, 688), (5568, 4096, 4096), (1216, 32262, 256), (32, 12288, 4096), (513, 384, 1536)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("bn", [0, 64, 128, 256])
+def test_gemm_matches_fp32_reference(M, N, K, bn):
+    if bn != 0 and M * N > 4e7:
+        pytest.skip("large shape only with auto tile")
+    g = torch.Generator(device="cuda").manual_seed(M * 31 + N * 7 + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    out = ops.gemm(a, w, force_bn=bn)
+    ref = _ref(a, w)
+    # bf16 output rounding: 2^-8 relative, fp32 accumulation error is far below that
+    torch.testing.assert_close(out.float(), ref, atol=2e-2, rtol=1.6e-2)
+    assert (out.float() - ref).abs().max() / ref.abs().max() < 8e-3
+
+
+def test_gemm_epilogues_and_fp32_out():
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K = 513, 1000, 384
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    for act in (0, 1, 2):
+        out = ops.gemm(a, w, bias=bias, residual=res, act=act, out_dtype=torch.float32, alpha=0.5)
+        torch.testing.assert_close(out, _ref(a, w, bias, res, act, 0.5), atol=2e-3, rtol=1e-3)
+    out2 = ops.gemm(a, w, out=out.clone(), accumulate=True)
+    torch.testing.assert_close(out2, out + _ref(a, w), atol=2e-3, rtol=1e-3)
+    # unaligned ldc (vocab-like N) and strided A
+    a2 = torch.randn(M, 2 * K, device="cuda", generator=g).bfloat16()[:, :K]
+    w2 = w[:999]
+    out3 = ops.gemm(a2, w2, bias=bias[:999].contiguous())
+    torch.testing.assert_close(out3.float(), _ref(a2, w2, bias[:999]), atol=3e-2, rtol=1.6e-2)
