@@ -1,0 +1,80 @@
+"""Autoregressive trajectory-token generation with a static KV cache.
+
+Reference: ``TrajPointLLMForCausalLM.generate`` (model_arch.py:77-108) -> HF ``GenerationMixin`` with
+``prepare_inputs_for_generation`` (pointllm.py:255-275): the first step runs the full prompt including the point
+encoder, later steps feed one token against the cache; finished rows emit ``pad``; the attention mask grows by ones
+(HF generation/utils.py:2762-2806).  Callers: train.py:221-231, evaluate.py:114-124.
+
+Greedy decoding is the mode with a bit-exact contract (ids from identical logits); the reference's default sampling
+chain (top-k 50 -> top-p 0.95 -> multinomial) is SURVEY 8f row N1 and not built yet.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import ops
+from .llm import KVCache
+from .model import GenerateOutput, TrajPointLLMForCausalLM
+
+
+@torch.no_grad()
+def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+             point_clouds: Optional[torch.Tensor] = None, max_length: int = 20, temperature: float = 1.0, top_k: int = 50,
+             top_p: float = 0.95, repetition_penalty: float = 1.0, do_sample: bool = True, num_return_sequences: int = 1,
+             fps_start: Optional[torch.Tensor] = None, suppress_eos: bool = False, output_scores: bool = True,
+             eos_check_every: int = 16, **kwargs) -> GenerateOutput:
+    if do_sample:
+        raise NotImplementedError("sampling decode (top-k/top-p/multinomial, SURVEY 8f N1) is not built; pass do_sample=False")
+    if num_return_sequences != 1 or repetition_penalty != 1.0:
+        raise NotImplementedError("num_return_sequences != 1 / repetition_penalty != 1 are not built")
+    cfg, dev = model.cfg, model.dev
+    was_training = model.training
+    model.eval()
+    input_ids = input_ids.to(dev)
+    B, P = input_ids.shape
+    T = int(max_length)                                   # model_arch.py:96: max_new_tokens = max_length
+    V, d = cfg.vocab_size, cfg.hidden_size
+    cache = KVCache.allocate(cfg, B, P + T, dev)
+    mask = torch.zeros(B, P + T, device=dev, dtype=torch.uint8)
+    mask[:, :P] = 1 if attention_mask is None else attention_mask.to(dev).to(torch.uint8)
+    seq = torch.full((B, P + T), cfg.pad_token_id, device=dev, dtype=torch.int64)
+    seq[:, :P] = input_ids
+    unfinished = torch.ones(B, device=dev, dtype=torch.int32)
+    nxt = torch.empty(B, device=dev, dtype=torch.int64)
+    tok = torch.empty(B, 1, device=dev, dtype=torch.int64)
+    scores = torch.empty(T, B, V, device=dev, dtype=torch.float32) if output_scores else None
+    last = torch.empty(B, 1, d, device=dev, dtype=torch.bfloat16)
+    sup = cfg.eos_token_id if suppress_eos else -1
+
+    steps_done = 0
+    for s in range(T):
+        if s == 0:
+            h, _ = model.hidden_states(input_ids, mask[:, :P], point_clouds, fps_start, cache)
+            ops.copy_rows(h.view(B, P, d)[:, P - 1:P, :], last)
+            hl = last.view(B, d)
+        else:
+            hl, _ = model.hidden_states(tok, mask, None, None, cache)
+        logits = model.logits_from_hidden(hl)
+        ops.argmax_rows(logits, V, scores=None if scores is None else scores[s], suppress_col=sup, out=nxt)
+        ops.greedy_update(nxt, tok.view(B), unfinished, seq, P + s, mask, cfg.eos_token_id, cfg.pad_token_id)
+        steps_done = s + 1
+        if not suppress_eos and eos_check_every > 0 and (s + 1) % eos_check_every == 0:
+            if int(unfinished.max().item()) == 0:        # the reference checks every step (one sync per token)
+                break
+    if not suppress_eos and steps_done == T:
+        pass
+    # HF stops as soon as every row has finished; trim the columns generated after that point
+    if not suppress_eos:
+        gen = seq[:, P:P + steps_done]
+        fin = (gen == cfg.eos_token_id)
+        if bool(fin.any(dim=1).all().item()):
+            first = torch.where(fin.any(dim=1), fin.float().argmax(dim=1), torch.full((B,), steps_done - 1, device=dev))
+            steps_done = int(first.max().item()) + 1
+    model.train(was_training)
+    out_scores = tuple(scores[i] for i in range(steps_done)) if scores is not None else None
+    return GenerateOutput(sequences=seq[:, :P + steps_done], scores=out_scores)
+
+
+TrajPointLLMForCausalLM.generate = lambda self, *a, **k: generate(self, *a, **k)

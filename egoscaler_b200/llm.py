@@ -1,0 +1,172 @@
+"""LLaMA trunk on the CUDA ops: forward (training / prefill / cached decode) and the hand-written backward.
+
+Reference arithmetic: HF ``LlamaDecoderLayer`` x N (transformers 5.5.0 modeling_llama.py:292-340: RMSNorm :53-67,
+attention :253-290 with RoPE :138-168, MLP :171-184) called from pointllm/model/pointllm.py:173-178, final
+``LlamaModel.norm`` and ``lm_head`` (pointllm.py:228).
+
+Per layer (T = B*L tokens, d hidden, f MLP width):
+    xn  = rmsnorm(x)                                  [T,d]
+    qkv = xn . Wqkv^T                                 [T,3d]   one tcgen05 GEMM for q|k|v
+    rope(q,k) in place (+ KV-cache write)
+    o   = attention(q,k,v, causal & key-padding)      [T,d]
+    h   = o . Wo^T + x                                (residual fused in the GEMM epilogue)
+    hn  = rmsnorm(h)
+    gu  = hn . Wgu^T                                  [T,2f]   one GEMM for gate|up
+    a   = silu(gate) * up                             [T,f]
+    out = a . Wdown^T + h
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from .config import TrajVLMConfig
+
+
+def rope_tables(head_dim: int, theta: float, max_pos: int, device) -> "tuple[torch.Tensor, torch.Tensor]":
+    """cos/sin [max_pos, head_dim/2] bf16, computed exactly like LlamaRotaryEmbedding (modeling_llama.py:117-135):
+    fp32 inv_freq and outer product on the CPU, cast to the activation dtype.  Setup-time table, not hot path."""
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+    fr = torch.arange(max_pos, dtype=torch.float32)[:, None] * inv[None, :]
+    return fr.cos().to(torch.bfloat16).to(device).contiguous(), fr.sin().to(torch.bfloat16).to(device).contiguous()
+
+
+@dataclass
+class LayerWeights:
+    wqkv: torch.Tensor
+    wo: torch.Tensor
+    wgu: torch.Tensor
+    wdown: torch.Tensor
+    ln1: torch.Tensor
+    ln2: torch.Tensor
+    # contraction-major copies for the data-gradient GEMMs (built on first backward)
+    wqkvT: Optional[torch.Tensor] = None
+    woT: Optional[torch.Tensor] = None
+    wguT: Optional[torch.Tensor] = None
+    wdownT: Optional[torch.Tensor] = None
+
+    def ensure_transposed(self):
+        if self.wqkvT is None:
+            self.wqkvT = ops.transpose(self.wqkv)
+            self.woT = ops.transpose(self.wo)
+            self.wguT = ops.transpose(self.wgu)
+            self.wdownT = ops.transpose(self.wdown)
+
+
+@dataclass
+class KVCache:
+    """Static cache [layer] -> K, V [B, max_len, d] bf16 (keys post-RoPE like DynamicCache)."""
+    k: List[torch.Tensor]
+    v: List[torch.Tensor]
+    max_len: int
+    length: int = 0
+
+    @staticmethod
+    def allocate(cfg: TrajVLMConfig, batch: int, max_len: int, device) -> "KVCache":
+        d = cfg.hidden_size
+        k = [torch.empty(batch, max_len, d, device=device, dtype=torch.bfloat16) for _ in range(cfg.num_hidden_layers)]
+        v = [torch.empty(batch, max_len, d, device=device, dtype=torch.bfloat16) for _ in range(cfg.num_hidden_layers)]
+        return KVCache(k, v, max_len, 0)
+
+
+@dataclass
+class LayerSaved:
+    x: torch.Tensor
+    rstd1: torch.Tensor
+    qkv: torch.Tensor
+    o: torch.Tensor
+    lse: torch.Tensor
+    h: torch.Tensor
+    rstd2: torch.Tensor
+    gu: torch.Tensor
+
+
+class LlamaTrunk:
+    def __init__(self, cfg: TrajVLMConfig, layers: List[LayerWeights], device):
+        self.cfg = cfg
+        self.layers = layers
+        self.cos, self.sin = rope_tables(cfg.head_dim, cfg.rope_theta, cfg.max_position_embeddings, device)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], pos0: int = 0,
+                cache: Optional[KVCache] = None, saved: Optional[List[LayerSaved]] = None) -> torch.Tensor:
+        """x [B*L, d] bf16 -> hidden [B*L, d] (before the final norm).  kmask uint8 [B, >= pos0+L] or None.
+        With ``cache``: K/V of these L tokens are written at pos0.. and attention runs over cache[:pos0+L]."""
+        c = self.cfg
+        d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
+        decode = cache is not None and L == 1 and pos0 > 0
+        for li, w in enumerate(self.layers):
+            if saved is not None:
+                xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
+            else:
+                xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps), None
+            qkv = ops.gemm(xn, w.wqkv)                                            # [T, 3d]
+            if cache is not None:
+                ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
+                          kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len)
+            else:
+                ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0)
+            lse = None
+            if decode:
+                o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_static=pos0 + 1)
+            else:
+                q4 = qkv.view(B, L, 3, H, hd)
+                if cache is not None:
+                    k4 = cache.k[li][:, :pos0 + L].view(B, pos0 + L, H, hd)
+                    v4 = cache.v[li][:, :pos0 + L].view(B, pos0 + L, H, hd)
+                else:
+                    k4, v4 = q4[:, :, 1], q4[:, :, 2]
+                r = ops.attention(q4[:, :, 0], k4, v4, causal=True, kmask=kmask, q_pos0=pos0, want_lse=saved is not None)
+                o, lse = r if saved is not None else (r, None)
+                o = o.view(B * L, d)
+            h = ops.gemm(o, w.wo, residual=x)
+            if saved is not None:
+                hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps, want_rstd=True)
+            else:
+                hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps), None
+            gu = ops.gemm(hn, w.wgu)
+            a = ops.silu_mul(gu)
+            out = ops.gemm(a, w.wdown, residual=h)
+            if saved is not None:
+                saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu))
+            x = out
+        return x
+
+    # ------------------------------------------------------------------ backward (data gradients; frozen weights)
+    def backward(self, dout: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], saved: List[LayerSaved],
+                 wgrad: Optional[Dict[str, List[torch.Tensor]]] = None) -> torch.Tensor:
+        """dout [B*L, d] bf16 -> dx [B*L, d].  Default recipe freezes the trunk (model_arch.py:33-51): only data
+        gradients flow.  ``wgrad`` (fp32 accumulators per layer) enables the --unfreeze_language_model path."""
+        c = self.cfg
+        d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
+        for li in reversed(range(len(self.layers))):
+            w, s = self.layers[li], saved[li]
+            w.ensure_transposed()
+            da = ops.gemm(dout, w.wdownT)                                         # [T, f]
+            dgu = ops.silu_mul_bwd(s.gu, da)                                      # [T, 2f]
+            dhn = ops.gemm(dgu, w.wguT)                                           # [T, d]
+            if wgrad is not None:
+                hn = ops.rmsnorm(s.h, w.ln2, c.rms_norm_eps)
+                a = ops.silu_mul(s.gu)
+                ops.gemm(ops.transpose(dout), ops.transpose(a), out=wgrad["wdown"][li], accumulate=True)
+                ops.gemm(ops.transpose(dgu), ops.transpose(hn), out=wgrad["wgu"][li], accumulate=True)
+                dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout, dw=wgrad["ln2"][li])
+            else:
+                dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout)
+            do = ops.gemm(dh, w.woT)                                              # [T, d]
+            dqkv = ops.attention_bwd(s.qkv.view(B, L, 3, H, hd), s.o.view(B, L, d), s.lse, do.view(B, L, d), causal=True,
+                                     kmask=kmask)                                 # [T, 3d]
+            ops.rope_(dqkv.view(B * L, 3 * d), L, 2 * H, hd, self.cos, self.sin, 0, inverse=True)
+            dxn = ops.gemm(dqkv.view(B * L, 3 * d), w.wqkvT)
+            if wgrad is not None:
+                xn = ops.rmsnorm(s.x, w.ln1, c.rms_norm_eps)
+                ops.gemm(ops.transpose(dh), ops.transpose(s.o), out=wgrad["wo"][li], accumulate=True)
+                ops.gemm(ops.transpose(dqkv.view(B * L, 3 * d)), ops.transpose(xn), out=wgrad["wqkv"][li], accumulate=True)
+                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh, dw=wgrad["ln1"][li])
+            else:
+                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh)
+            saved[li] = None                                                      # free activations as we go
+        return dout

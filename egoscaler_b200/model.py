@@ -1,0 +1,233 @@
+"""Drop-in module for the reference's ``TrajPointLLMForCausalLM`` (egoscaler/models/pointllm/model_arch.py:8-124),
+i.e. ``PointLLMLlamaForCausalLM`` (pointllm/model/pointllm.py:181-275) with EgoScaler's freezing semantics, running on
+the hand-written CUDA path (no ATen math, no CPU fallback).
+
+Same surface: ``forward(input_ids, attention_mask, ..., point_clouds, return_dict)`` -> object with ``.logits``;
+``generate(...)`` -> object with ``.sequences`` / ``.scores``; ``train(mode)`` keeps frozen parts in eval;
+``state_dict()`` / ``load_state_dict()`` use the reference's parameter names (params.ParamTree);
+``get_model().point_backbone_config`` carries the same keys (pointllm.py:49-59,281-300).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .config import (TrajVLMConfig, POINT_PATCH_TOKEN_ID, POINT_START_TOKEN_ID, POINT_END_TOKEN_ID)
+from .encoder import (PackedPointEncoder, PackedProjector, point_encoder_forward, projector_forward)
+from .llm import KVCache, LayerWeights, LlamaTrunk
+from .params import ParamTree
+
+
+@dataclass
+class CausalLMOutput:
+    """Stand-in for transformers' CausalLMOutputWithPast (only the fields the reference reads)."""
+    logits: torch.Tensor
+    past_key_values: Optional[KVCache] = None
+    loss: Optional[torch.Tensor] = None
+
+
+@dataclass
+class GenerateOutput:
+    """Stand-in for GenerateDecoderOnlyOutput: ``.sequences`` [B, P+T], ``.scores`` tuple of T x [B, V] fp32."""
+    sequences: torch.Tensor
+    scores: Optional[Tuple[torch.Tensor, ...]] = None
+
+
+class _ModelView:
+    """What ``get_model()`` returns in the reference: the inner model carrying ``point_backbone_config``."""
+
+    def __init__(self, outer: "TrajPointLLMForCausalLM"):
+        self._outer = outer
+        self.point_backbone_config = outer.point_backbone_config
+
+
+class TrajPointLLMForCausalLM(ParamTree):
+    def __init__(self, cfg: TrajVLMConfig, device="cuda", unfreeze_pc_encoder: bool = False,
+                 unfreeze_language_model: bool = False):
+        super().__init__(cfg, device)
+        self.cfg = cfg
+        self.dev = torch.device(device)
+        p = cfg.point
+        # pointllm.py:49-59 + 281-300 (ids are fixed by the vocabulary layout of builder.py:33-46)
+        self.point_backbone_config = {
+            "point_cloud_dim": p.point_dims, "backbone_output_dim": p.trans_dim * (2 if p.use_max_pool else 1),
+            "project_output_dim": cfg.hidden_size, "point_token_len": p.point_token_len,
+            "mm_use_point_start_end": cfg.mm_use_point_start_end, "projection_hidden_layer": len(p.projection_hidden_dim),
+            "use_max_pool": p.use_max_pool, "default_point_patch_token": "<point_patch>",
+            "default_point_start_token": "<point_start>", "default_point_end_token": "<point_end>",
+            "point_patch_token": POINT_PATCH_TOKEN_ID, "point_start_token": POINT_START_TOKEN_ID,
+            "point_end_token": POINT_END_TOKEN_ID,
+        }
+        self.unfreeze_pc_encoder = unfreeze_pc_encoder
+        self.unfreeze_language_model = unfreeze_language_model
+        self._configure_trainable_parameters()
+        self._packed_encoder: Optional[PackedPointEncoder] = None
+        self._packed_proj: Optional[PackedProjector] = None
+        self._trunk: Optional[LlamaTrunk] = None
+        self._lm_head_T: Optional[torch.Tensor] = None
+        self.v_pad = (cfg.vocab_size + 7) // 8 * 8          # logits leading dimension (16-byte rows)
+
+    # ------------------------------------------------------------------ reference API surface
+    def get_model(self) -> _ModelView:
+        return _ModelView(self)
+
+    def _configure_trainable_parameters(self):
+        """model_arch.py:33-51: everything trainable except LLM layers / point encoder unless un-frozen."""
+        for n, q in self.named_parameters():
+            if n.startswith("model.point_backbone."):
+                q.requires_grad = bool(self.unfreeze_pc_encoder)
+            elif n.startswith("model.layers."):
+                q.requires_grad = bool(self.unfreeze_language_model)
+            else:
+                q.requires_grad = True
+
+    def train(self, mode: bool = True):
+        """model_arch.py:110-124: frozen sub-modules stay in eval.  The CUDA path has no dropout and uses BatchNorm
+        running statistics only, which is exactly the reference behaviour while the encoder is frozen."""
+        super().train(mode)
+        if mode and self.unfreeze_pc_encoder:
+            raise NotImplementedError("training the point encoder (--unfreeze_pc_encoder) is not built yet")
+        return self
+
+    def trainable_names(self) -> List[str]:
+        return [n for n, q in self.named_parameters() if q.requires_grad]
+
+    # ------------------------------------------------------------------ operand packing
+    def repack(self):
+        """(Re)build kernel operands from the parameters: call after load_state_dict / optimizer steps on the
+        projector / lm_head.  Trunk weights are the parameters themselves (views), nothing is copied."""
+        named = self.named()
+        self._packed_encoder = PackedPointEncoder(self.cfg, named)
+        pw = [named[w] for w, _ in self.projector_params()]
+        pb = [named[b] for _, b in self.projector_params()]
+        self._packed_proj = PackedProjector(pw, pb)
+        layers = []
+        for i in range(self.cfg.num_hidden_layers):
+            pre = f"model.layers.{i}."
+            layers.append(LayerWeights(self.wqkv[i], named[pre + "self_attn.o_proj.weight"].detach(), self.wgu[i],
+                                       named[pre + "mlp.down_proj.weight"].detach(),
+                                       named[pre + "input_layernorm.weight"].detach(),
+                                       named[pre + "post_attention_layernorm.weight"].detach()))
+        self._trunk = LlamaTrunk(self.cfg, layers, self.dev)
+        self._lm_head_T = None
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        r = super().load_state_dict(state_dict, strict=strict, assign=False)
+        self.repack()
+        return r
+
+    @property
+    def trunk(self) -> LlamaTrunk:
+        if self._trunk is None:
+            self.repack()
+        return self._trunk
+
+    def lm_head_T(self) -> torch.Tensor:
+        """[d, V] copy of lm_head for the data-gradient GEMM (refreshed by the trainer after each step)."""
+        if self._lm_head_T is None:
+            self._lm_head_T = ops.transpose(self.lm_head.weight.detach())
+        return self._lm_head_T
+
+    # ------------------------------------------------------------------ pieces of the forward
+    @staticmethod
+    def draw_fps_start(n_points: int, batch: int) -> torch.Tensor:
+        """The draw pointbert/misc.py:52 makes on the CPU generator (same stream consumption as the reference)."""
+        return torch.randint(0, n_points, (batch,), dtype=torch.long)
+
+    def point_features(self, point_clouds: torch.Tensor, fps_start: Optional[torch.Tensor] = None,
+                       save: Optional[list] = None) -> torch.Tensor:
+        """pointllm.py:124-129: point_backbone -> point_proj.  [B,N,C] fp32 -> [B, Np, d] bf16."""
+        if self._packed_encoder is None:
+            self.repack()
+        B, N, _ = point_clouds.shape
+        if fps_start is None:
+            fps_start = self.draw_fps_start(N, B)
+        fps_start = fps_start.to(self.dev)
+        pts = point_clouds.to(self.dev, torch.float32)
+        tok = point_encoder_forward(self._packed_encoder, pts, fps_start)
+        Np, T = tok.shape[1], tok.shape[2]
+        out = projector_forward(self._packed_proj, tok.view(B * Np, T), save)
+        return out.view(B, Np, self.cfg.hidden_size)
+
+    def splice_positions(self, input_ids: torch.Tensor) -> torch.Tensor:
+        """Validation of pointllm.py:136-164 (same ValueErrors) -> int32 [B] first point-feature position (-1: none).
+        One small D2H read, like the reference's own host-side checks."""
+        c = self.point_backbone_config
+        n = c["point_token_len"]
+        info_d = ops.point_layout(input_ids, c["point_patch_token"], c["point_start_token"], c["point_end_token"], n)
+        info = info_d.cpu()
+        pos = torch.full((input_ids.shape[0],), -1, dtype=torch.int32)
+        for b in range(input_ids.shape[0]):
+            n_start, n_end, n_patch, first_start, end_ok, consecutive, first_patch = info[b, :7].tolist()
+            if n_patch == 0:
+                continue                                            # pointllm.py:138-142 (dummy projection only)
+            if c["mm_use_point_start_end"]:
+                if n_start != n_end:
+                    raise ValueError("The number of point start tokens and point end tokens should be the same.")
+                if n_start > 1:
+                    raise ValueError("egoscaler_b200 supports one point block per sample.")
+                if not end_ok:
+                    raise ValueError("The point end token should follow the point start token.")
+                pos[b] = first_start + 1
+            else:
+                if n_patch != n:
+                    raise ValueError("The number of point patch tokens should be the same as the number of point patches.")
+                if not consecutive:
+                    raise ValueError("The point patch tokens should be consecutive.")
+                pos[b] = first_patch
+        return pos.to(self.dev)
+
+    @staticmethod
+    def _kmask(attention_mask: Optional[torch.Tensor], dev) -> Optional[torch.Tensor]:
+        if attention_mask is None:
+            return None
+        return attention_mask.to(dev).to(torch.uint8).contiguous()
+
+    def hidden_states(self, input_ids, attention_mask=None, point_clouds=None, fps_start=None, cache: Optional[KVCache] = None,
+                      saved=None, proj_saved=None, splice_pos=None):
+        """Everything up to (not including) the final norm.  Returns (hidden [B*L, d], splice_pos)."""
+        input_ids = input_ids.to(self.dev)
+        B, L = input_ids.shape
+        pos0 = cache.length if cache is not None else 0
+        feats = None
+        if (L != 1 or self.training) and point_clouds is not None:       # pointllm.py:112
+            feats = self.point_features(point_clouds, fps_start, proj_saved)
+            if splice_pos is None:
+                splice_pos = self.splice_positions(input_ids)
+        x = ops.embed_splice(input_ids, self.model.embed_tokens.weight.detach(), feats, splice_pos if feats is not None else None,
+                             self.point_backbone_config["point_token_len"])
+        h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved)
+        if cache is not None:
+            cache.length = pos0 + L
+        return h, splice_pos
+
+    def logits_from_hidden(self, h: torch.Tensor) -> torch.Tensor:
+        """final RMSNorm + lm_head (pointllm.py:227-228) -> [rows, V] view of a [rows, v_pad] bf16 buffer."""
+        hn = ops.rmsnorm(h, self.model.norm.weight.detach(), self.cfg.rms_norm_eps)
+        buf = torch.empty(h.shape[0], self.v_pad, device=h.device, dtype=torch.bfloat16)
+        out = buf[:, :self.cfg.vocab_size]
+        ops.gemm(hn, self.lm_head.weight.detach(), out=out)
+        return out
+
+    # ------------------------------------------------------------------ forward / generate (reference signatures)
+    @torch.no_grad()
+    def forward(self, input_ids=None, attention_mask=None, past_key_values: Optional[KVCache] = None, inputs_embeds=None,
+                labels=None, use_cache=None, output_attentions=None, output_hidden_states=None, point_clouds=None,
+                return_dict=None, fps_start=None) -> CausalLMOutput:
+        """model_arch.py:53-75 -> pointllm.py:195-253.  Logits for all positions, bf16 (what autocast gives the
+        reference on GPU).  ``past_key_values`` follows the parent class' semantics."""
+        if inputs_embeds is not None or labels is not None:
+            raise NotImplementedError("inputs_embeds / labels are never passed by the reference entry points")
+        cache = past_key_values
+        B, L = input_ids.shape
+        if use_cache and cache is None:
+            cache = KVCache.allocate(self.cfg, B, max(self.cfg.max_position_embeddings, L), self.dev)
+        h, _ = self.hidden_states(input_ids, attention_mask, point_clouds, fps_start, cache)
+        logits = self.logits_from_hidden(h).view(B, L, self.cfg.vocab_size)
+        return CausalLMOutput(logits=logits, past_key_values=cache)
+
+    __call__ = forward

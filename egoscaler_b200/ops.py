@@ -104,3 +104,283 @@ def traj_ids_to_poses(ids: torch.Tensor, max_steps: int, num_bins: int = 256, ba
     _l.call("esb_traj_ids_to_poses", ids.data_ptr(), B, T, num_bins, base_id, tsep_id, eos_id, scale, float(d_max),
             float(d_min), max_steps, 1 if pad_repeat else 0, out.data_ptr(), cnt.data_ptr(), _stream())
     return out, cnt
+
+
+# ------------------------------------------------------------------------------------------------ norms
+def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float, want_rstd: bool = False):
+    """HF LlamaRMSNorm (modeling_llama.py:53-67). x [rows, d] bf16 (row stride multiple of 8), w [d] bf16."""
+    _chk(x, torch.bfloat16, "rmsnorm.x"); _chk(w, torch.bfloat16, "rmsnorm.w")
+    assert x.dim() == 2 and x.stride(1) == 1
+    rows, d = x.shape
+    y = torch.empty(rows, d, device=x.device, dtype=torch.bfloat16)
+    rstd = torch.empty(rows, device=x.device, dtype=torch.float32) if want_rstd else None
+    _l.call("esb_rmsnorm_fwd", x.data_ptr(), x.stride(0), w.data_ptr(), y.data_ptr(), d, _p(rstd), rows, d, float(eps), _stream())
+    return (y, rstd) if want_rstd else y
+
+
+def rmsnorm_bwd(dy, x, w, rstd, dres=None, dw: Optional[torch.Tensor] = None):
+    for t, n in ((dy, "dy"), (x, "x"), (w, "w")):
+        _chk(t, torch.bfloat16, "rmsnorm_bwd." + n)
+    assert dy.is_contiguous() and x.is_contiguous()
+    rows, d = x.shape
+    dx = torch.empty_like(x)
+    _l.call("esb_rmsnorm_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(), rstd.data_ptr(), _p(dres), dx.data_ptr(), _p(dw),
+            rows, d, _stream())
+    return dx
+
+
+def layernorm(x, gamma, beta, eps: float = 1e-5, add=None, sum_out=None):
+    """nn.LayerNorm over the last dim of x [rows, d] bf16; optional fused ``s = x + add`` (sum written to sum_out)."""
+    _chk(x, torch.bfloat16, "layernorm.x"); _chk(gamma, torch.float32, "layernorm.gamma"); _chk(beta, torch.float32, "layernorm.beta")
+    assert x.is_contiguous()
+    rows, d = x.shape
+    y = torch.empty_like(x)
+    period = 0
+    if add is not None:
+        _chk(add, torch.bfloat16, "layernorm.add")
+        assert add.is_contiguous() and add.shape[-1] == d
+        period = add.numel() // d
+    _l.call("esb_layernorm_fwd", x.data_ptr(), _p(add), period, gamma.data_ptr(), beta.data_ptr(), _p(sum_out), y.data_ptr(),
+            rows, d, float(eps), _stream())
+    return y
+
+
+# ------------------------------------------------------------------------------------------------ element-wise
+def rope_(buf: torch.Tensor, L: int, n_heads: int, hd: int, cos_tab, sin_tab, pos0: int = 0, inverse: bool = False,
+          kcache=None, vcache=None, kv_head0: int = 0, kv_heads: int = 0, v_col0: int = 0, cache_len: int = 0):
+    _chk(buf, torch.bfloat16, "rope.buf")
+    assert buf.dim() == 2 and buf.stride(1) == 1
+    _l.call("esb_rope", buf.data_ptr(), buf.stride(0), buf.shape[0], L, n_heads, hd, cos_tab.data_ptr(), sin_tab.data_ptr(),
+            pos0, 1 if inverse else 0, _p(kcache), _p(vcache), kv_head0, kv_heads, v_col0, cache_len, _stream())
+    return buf
+
+
+def silu_mul(gu: torch.Tensor) -> torch.Tensor:
+    _chk(gu, torch.bfloat16, "silu_mul.gu")
+    assert gu.is_contiguous()
+    rows, f2 = gu.shape
+    act = torch.empty(rows, f2 // 2, device=gu.device, dtype=torch.bfloat16)
+    _l.call("esb_silu_mul_fwd", gu.data_ptr(), act.data_ptr(), rows, f2 // 2, _stream())
+    return act
+
+
+def silu_mul_bwd(gu: torch.Tensor, dact: torch.Tensor) -> torch.Tensor:
+    assert gu.is_contiguous() and dact.is_contiguous()
+    dgu = torch.empty_like(gu)
+    _l.call("esb_silu_mul_bwd", gu.data_ptr(), dact.data_ptr(), dgu.data_ptr(), gu.shape[0], gu.shape[1] // 2, _stream())
+    return dgu
+
+
+def gelu(z: torch.Tensor) -> torch.Tensor:
+    _chk(z, torch.bfloat16, "gelu.z")
+    assert z.is_contiguous()
+    y = torch.empty_like(z)
+    _l.call("esb_gelu", z.data_ptr(), None, y.data_ptr(), z.numel(), 0, _stream())
+    return y
+
+
+def gelu_bwd(z: torch.Tensor, dy: torch.Tensor) -> torch.Tensor:
+    assert z.is_contiguous() and dy.is_contiguous()
+    dz = torch.empty_like(z)
+    _l.call("esb_gelu", z.data_ptr(), dy.data_ptr(), dz.data_ptr(), z.numel(), 1, _stream())
+    return dz
+
+
+# ------------------------------------------------------------------------------------------------ gather / layout
+def point_layout(ids: torch.Tensor, patch_id: int, start_id: int, end_id: int, n_point: int) -> torch.Tensor:
+    _chk(ids, torch.int64, "point_layout.ids")
+    ids = ids.contiguous()
+    B, L = ids.shape
+    info = torch.empty(B, 8, device=ids.device, dtype=torch.int32)
+    _l.call("esb_point_layout", ids.data_ptr(), B, L, patch_id, start_id, end_id, n_point, info.data_ptr(), _stream())
+    return info
+
+
+def embed_splice(ids, embed, feats, splice_pos, n_point: int) -> torch.Tensor:
+    _chk(ids, torch.int64, "embed_splice.ids"); _chk(embed, torch.bfloat16, "embed_splice.embed")
+    ids = ids.contiguous()
+    B, L = ids.shape
+    d = embed.shape[1]
+    x = torch.empty(B * L, d, device=ids.device, dtype=torch.bfloat16)
+    _l.call("esb_embed_splice_fwd", ids.data_ptr(), embed.data_ptr(), _p(feats), _p(splice_pos), n_point, x.data_ptr(), B, L, d, _stream())
+    return x
+
+
+def embed_splice_bwd(ids, dx, splice_pos, n_point: int, dembed, dfeats, padding_idx: int):
+    ids = ids.contiguous()
+    B, L = ids.shape
+    d = dx.shape[-1]
+    assert dx.is_contiguous()
+    _l.call("esb_embed_splice_bwd", ids.data_ptr(), dx.data_ptr(), _p(splice_pos), n_point, _p(dembed), _p(dfeats), padding_idx,
+            B, L, d, _stream())
+
+
+def copy_rows(src: torch.Tensor, dst: torch.Tensor):
+    """dst[b, r, :] = src[b, r, :] for 3-D views whose last dim is contiguous (any batch/row strides)."""
+    assert src.dim() == 3 and dst.shape == src.shape and src.stride(2) == 1 and dst.stride(2) == 1 and src.dtype == dst.dtype
+    es = src.element_size()
+    Bn, R, Cn = src.shape
+    _l.call("esb_copy_rows", src.data_ptr(), src.stride(0) * es, src.stride(1) * es, dst.data_ptr(), dst.stride(0) * es,
+            dst.stride(1) * es, Bn, R, Cn * es, _stream())
+    return dst
+
+
+def transpose(x: torch.Tensor, out: Optional[torch.Tensor] = None, pad_to: int = 8) -> torch.Tensor:
+    """[R, C] bf16 -> [C, R] (leading dimension padded to a multiple of ``pad_to``; returns the [C, R] view)."""
+    _chk(x, torch.bfloat16, "transpose.x")
+    assert x.dim() == 2 and x.stride(1) == 1
+    R, C = x.shape
+    if out is None:
+        ld = (R + pad_to - 1) // pad_to * pad_to
+        out = torch.zeros(C, ld, device=x.device, dtype=torch.bfloat16)[:, :R] if ld != R else \
+            torch.empty(C, R, device=x.device, dtype=torch.bfloat16)
+    _l.call("esb_transpose_bf16", x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), R, C, _stream())
+    return out
+
+
+def colsum(x: torch.Tensor, out: torch.Tensor):
+    _chk(x, torch.bfloat16, "colsum.x"); _chk(out, torch.float32, "colsum.out")
+    M, N = x.shape
+    _l.call("esb_colsum_bf16", x.data_ptr(), x.stride(0), M, N, out.data_ptr(), _stream())
+    return out
+
+
+def group_maxpool(f: torch.Tensor, n: int, concat: bool) -> torch.Tensor:
+    _chk(f, torch.bfloat16, "group_maxpool.f")
+    assert f.is_contiguous()
+    rows, C = f.shape
+    groups = rows // n
+    out = torch.empty((rows, 2 * C) if concat else (groups, C), device=f.device, dtype=torch.bfloat16)
+    _l.call("esb_group_maxpool", f.data_ptr(), out.data_ptr(), groups, n, C, 1 if concat else 0, _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ loss / sampling / optimizer
+def cross_entropy(logits: torch.Tensor, V: int, targets: torch.Tensor, ignore_index: int, write_grad: bool):
+    """Mean CE over non-ignored rows (train.py:177-181). logits [rows, ld>=V] bf16 are overwritten with dlogits when
+    ``write_grad``.  Returns a 1-element fp32 tensor."""
+    _chk(logits, torch.bfloat16, "cross_entropy.logits"); _chk(targets, torch.int64, "cross_entropy.targets")
+    assert logits.dim() == 2 and logits.stride(1) == 1 and targets.is_contiguous()
+    rows = logits.shape[0]
+    row_loss = torch.empty(rows, device=logits.device, dtype=torch.float32)
+    scratch = torch.empty(1, device=logits.device, dtype=torch.float32)
+    loss = torch.empty(1, device=logits.device, dtype=torch.float32)
+    _l.call("esb_cross_entropy", logits.data_ptr(), logits.stride(0), rows, V, targets.data_ptr(), ignore_index,
+            row_loss.data_ptr(), scratch.data_ptr(), loss.data_ptr(), 1 if write_grad else 0, _stream())
+    return loss
+
+
+def argmax_rows(logits: torch.Tensor, V: int, scores: Optional[torch.Tensor] = None, suppress_col: int = -1,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _chk(logits, torch.bfloat16, "argmax_rows.logits")
+    rows = logits.shape[0]
+    if out is None:
+        out = torch.empty(rows, device=logits.device, dtype=torch.int64)
+    _l.call("esb_argmax_rows", logits.data_ptr(), logits.stride(0), rows, V, out.data_ptr(), _p(scores),
+            0 if scores is None else scores.stride(0), suppress_col, _stream())
+    return out
+
+
+def greedy_update(nxt, tokens_out, unfinished, sequences, cur_len: int, mask, eos: int, pad: int):
+    B = nxt.shape[0]
+    _l.call("esb_greedy_update", nxt.data_ptr(), tokens_out.data_ptr(), unfinished.data_ptr(), sequences.data_ptr(),
+            sequences.stride(0), cur_len, _p(mask), 0 if mask is None else mask.stride(0), eos, pad, B, _stream())
+
+
+def adamw_(p, g, m, v, p_bf16, lr, beta1, beta2, eps, wd, step: int, grad_scale: float = 1.0):
+    for t, n in ((p, "p"), (g, "g"), (m, "m"), (v, "v")):
+        _chk(t, torch.float32, "adamw." + n)
+        assert t.is_contiguous()
+    _l.call("esb_adamw", p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), _p(p_bf16), p.numel(), float(lr), float(beta1),
+            float(beta2), float(eps), float(wd), int(step), float(grad_scale), _stream())
+
+
+def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _chk(x, torch.float32, "cast_bf16.x")
+    x = x.contiguous()
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    _l.call("esb_cast_f32_bf16", x.data_ptr(), out.data_ptr(), x.numel(), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ attention
+def _bls(t: torch.Tensor):
+    """(batch stride, row stride) of a [B, L, H, hd] view whose (H, hd) block is contiguous."""
+    assert t.dim() == 4 and t.stride(3) == 1 and t.stride(2) == t.shape[3]
+    return t.stride(0), t.stride(1)
+
+
+def attention(q, k, v, causal: bool, kmask: Optional[torch.Tensor] = None, q_pos0: int = 0, scale: Optional[float] = None,
+              want_lse: bool = False, out: Optional[torch.Tensor] = None):
+    """q [B,Lq,H,hd], k/v [B,Lk,H,hd] bf16 views (strided OK) -> o [B,Lq,H*hd] (+ lse [B,H,Lq])."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, torch.bfloat16, "attention." + n)
+    B, Lq, H, hd = q.shape
+    Lk = k.shape[1]
+    if out is None:
+        out = torch.empty(B, Lq, H * hd, device=q.device, dtype=torch.bfloat16)
+    lse = torch.empty(B, H, Lq, device=q.device, dtype=torch.float32) if want_lse else None
+    if kmask is not None:
+        assert kmask.dtype == torch.uint8 and kmask.stride(1) == 1 and kmask.shape[1] >= Lk
+    qs, ks, vs = _bls(q), _bls(k), _bls(v)
+    _l.call("esb_attn_fwd", q.data_ptr(), qs[0], qs[1], k.data_ptr(), ks[0], ks[1], v.data_ptr(), vs[0], vs[1],
+            out.data_ptr(), out.stride(0), out.stride(1), _p(lse), _p(kmask), 0 if kmask is None else kmask.stride(0),
+            B, H, Lq, Lk, hd, 1 if causal else 0, q_pos0, float(scale if scale is not None else hd ** -0.5), _stream())
+    return (out, lse) if want_lse else out
+
+
+def attention_decode(q, kcache, vcache, H: int, hd: int, kmask=None, len_ptr=None, len_static: int = 0,
+                     scale: Optional[float] = None, out: Optional[torch.Tensor] = None):
+    """q [B, >=H*hd] (row stride any), caches [B, Lmax, H*hd] -> o [B, H*hd]."""
+    B = q.shape[0]
+    if out is None:
+        out = torch.empty(B, H * hd, device=q.device, dtype=torch.bfloat16)
+    _l.call("esb_attn_decode", q.data_ptr(), q.stride(0), kcache.data_ptr(), vcache.data_ptr(), kcache.stride(0), kcache.stride(1),
+            out.data_ptr(), out.stride(0), _p(kmask), 0 if kmask is None else kmask.stride(0), _p(len_ptr), len_static, B, H, hd,
+            float(scale if scale is not None else hd ** -0.5), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ point cloud
+def fps(pts: torch.Tensor, G: int, start: torch.Tensor, pad_ld: int = 64):
+    """-> (centers [B,G,3] fp32, center_idx [B,G] int32, centers_pad [B*G, pad_ld] bf16)."""
+    _chk(pts, torch.float32, "fps.pts"); _chk(start, torch.int64, "fps.start")
+    pts = pts.contiguous()
+    B, N, C = pts.shape
+    centers = torch.empty(B, G, 3, device=pts.device, dtype=torch.float32)
+    idx = torch.empty(B, G, device=pts.device, dtype=torch.int32)
+    cpad = torch.empty(B * G, pad_ld, device=pts.device, dtype=torch.bfloat16)
+    _l.call("esb_fps", pts.data_ptr(), B, N, C, G, start.data_ptr(), centers.data_ptr(), idx.data_ptr(), cpad.data_ptr(),
+            pad_ld, _stream())
+    return centers, idx, cpad
+
+
+def knn_group(pts: torch.Tensor, centers: torch.Tensor, K: int, out_ld: int = 64, want_idx: bool = False):
+    pts = pts.contiguous()
+    B, N, C = pts.shape
+    G = centers.shape[1]
+    nb = torch.empty(B * G * K, out_ld, device=pts.device, dtype=torch.bfloat16)
+    idx = torch.empty(B, G, K, device=pts.device, dtype=torch.int32) if want_idx else None
+    _l.call("esb_knn_group", pts.data_ptr(), centers.data_ptr(), B, N, C, G, K, out_ld, nb.data_ptr(), _p(idx), _stream())
+    return (nb, idx) if want_idx else nb
+
+
+def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, causal: bool,
+                  kmask: Optional[torch.Tensor] = None, scale: Optional[float] = None) -> torch.Tensor:
+    """Self-attention backward on a packed projection: qkv [B,L,3,H,hd], o/dout [B,L,H*hd], lse [B,H,L]
+    -> dqkv [B,L,3,H,hd] (gradients w.r.t. the post-RoPE q,k and v)."""
+    _chk(qkv, torch.bfloat16, "attention_bwd.qkv"); _chk(dout, torch.bfloat16, "attention_bwd.dout")
+    B, L, three, H, hd = qkv.shape
+    assert three == 3 and qkv.is_contiguous() and o.stride(2) == 1 and dout.stride(2) == 1
+    dqkv = torch.empty_like(qkv)
+    dvec = torch.empty(B, H, L, device=qkv.device, dtype=torch.float32)
+    bs, rs = qkv.stride(0), qkv.stride(1)
+    es = qkv.element_size()
+    d = H * hd
+    _l.call("esb_attn_bwd", qkv.data_ptr(), bs, rs, qkv.data_ptr() + d * es, bs, rs, qkv.data_ptr() + 2 * d * es, bs, rs,
+            o.data_ptr(), o.stride(0), o.stride(1), dout.data_ptr(), dout.stride(0), dout.stride(1), lse.data_ptr(),
+            dvec.data_ptr(), dqkv.data_ptr(), bs, rs, dqkv.data_ptr() + d * es, bs, rs, dqkv.data_ptr() + 2 * d * es, bs, rs,
+            _p(kmask), 0 if kmask is None else kmask.stride(0), B, H, L, L, hd, 1 if causal else 0, 0,
+            float(scale if scale is not None else hd ** -0.5), _stream())
+    return dqkv

@@ -1,0 +1,139 @@
+"""Training step of the trajectory VLM on the CUDA path (forward + hand-written backward + fused AdamW), with
+data-parallel gradient all-reduce over NCCL overlapped with the backward.
+
+Reference: train.py:153-197 -- forward under autocast(bf16) (:166-172), loss on ``logits[:, P-1:-1]`` vs
+``tokens[:, P:]`` with ``ignore_index=pad`` (:174-181), ``model_engine.backward`` / ``.step`` (:183-184) with
+torch.optim.AdamW defaults (:113), linear warm-up schedule (:114-117), DeepSpeed ZeRO-1 bf16 data parallelism
+(:92-125).  Default trainable set (model_arch.py:33-51): embed_tokens, lm_head, point_proj, model.norm.
+
+Only the T = L - P trajectory rows go through lm_head (the loss never reads the others).  Data parallelism: one
+process per GPU, batch sharded by rank, trainable gradients summed with ``torch.distributed.all_reduce`` (NCCL over
+NVLink); the lm_head/norm gradients -- half of the bytes -- are reduced while the 32-layer backward is still running.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from .encoder import projector_backward
+from .model import TrajPointLLMForCausalLM
+
+
+def linear_warmup_lr(base_lr: float, step: int, warmup: int, total: int) -> float:
+    """transformers.get_linear_schedule_with_warmup (train.py:114-117); ``step`` counts completed optimizer steps."""
+    if total <= 0:
+        return base_lr
+    if step < warmup:
+        return base_lr * step / max(1, warmup)
+    return base_lr * max(0.0, (total - step) / max(1, total - warmup))
+
+
+class Trainer:
+    def __init__(self, model: TrajPointLLMForCausalLM, lr: float = 2e-5, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.01, warmup_steps: int = 0, total_steps: int = 0, process_group=None,
+                 world_size: int = 1):
+        if model.unfreeze_language_model or model.unfreeze_pc_encoder:
+            raise NotImplementedError("only the default freezing recipe (model_arch.py:33-51) is built")
+        self.model = model
+        self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
+        self.warmup, self.total = warmup_steps, total_steps
+        self.pg, self.world = process_group, world_size
+        self.step_count = 0
+        named = dict(model.named_parameters())
+        self.names: List[str] = model.trainable_names()
+        self.param: Dict[str, torch.Tensor] = {n: named[n] for n in self.names}
+        # fp32 master weights + moments (DeepSpeed bf16 optimizer keeps the same)
+        self.master = {n: p.detach().float().clone() for n, p in self.param.items()}
+        self.m = {n: torch.zeros_like(t) for n, t in self.master.items()}
+        self.v = {n: torch.zeros_like(t) for n, t in self.master.items()}
+        self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
+        self.last_loss: Optional[torch.Tensor] = None
+
+    def zero_grad(self):
+        for g in self.grad.values():
+            g.zero_()
+
+    # ------------------------------------------------------------------ forward + backward
+    def forward_backward(self, tokens: torch.Tensor, attention_masks: torch.Tensor, pcrgbs: torch.Tensor, prompt_len: int,
+                         fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
+        m, cfg = self.model, self.model.cfg
+        dev = m.dev
+        tokens = tokens.to(dev)
+        B, L = tokens.shape
+        P, d, V = int(prompt_len), cfg.hidden_size, cfg.vocab_size
+        Tn = L - P
+        n_point = m.point_backbone_config["point_token_len"]
+        kmask = m._kmask(attention_masks, dev)
+        saved, proj_saved = [], []
+        h, splice_pos = m.hidden_states(tokens, attention_masks, pcrgbs, fps_start, None, saved, proj_saved)
+        # ---- head: rows P-1 .. L-2 only (train.py:174)
+        hs = torch.empty(B, Tn, d, device=dev, dtype=torch.bfloat16)
+        ops.copy_rows(h.view(B, L, d)[:, P - 1:L - 1, :], hs)
+        hs2 = hs.view(B * Tn, d)
+        norm_w = m.model.norm.weight.detach()
+        hn, rstd = ops.rmsnorm(hs2, norm_w, cfg.rms_norm_eps, want_rstd=True)
+        lbuf = torch.empty(B * Tn, m.v_pad, device=dev, dtype=torch.bfloat16)
+        logits = lbuf[:, :V]
+        ops.gemm(hn, m.lm_head.weight.detach(), out=logits)
+        targets = tokens[:, P:].contiguous().view(-1)
+        loss = ops.cross_entropy(logits, V, targets, cfg.pad_token_id, write_grad=True)      # logits <- dlogits
+        # ---- head backward
+        ops.gemm(ops.transpose(logits), ops.transpose(hn), out=self.grad["lm_head.weight"], accumulate=True)
+        dhn = ops.gemm(logits, m.lm_head_T())
+        dhs = ops.rmsnorm_bwd(dhn, hs2, norm_w, rstd, dw=self.grad["model.norm.weight"])
+        self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
+        dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)
+        ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
+        # ---- trunk backward (data gradients through the frozen layers)
+        dx = m.trunk.backward(dh.view(B * L, d), B, L, kmask, saved)
+        # ---- embedding scatter + projector
+        dfeats = torch.empty(B, n_point, d, device=dev, dtype=torch.bfloat16)
+        ops.embed_splice_bwd(tokens, dx, splice_pos, n_point, self.grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id)
+        pw = [w for w, _ in m.projector_params()]
+        pb = [b for _, b in m.projector_params()]
+        projector_backward(m._packed_proj, proj_saved, dfeats.view(B * n_point, d), [self.grad[n] for n in pw],
+                           [self.grad[n] for n in pb])
+        self._reduce_async(["model.embed_tokens.weight"] + pw + pb)
+        self.last_loss = loss
+        return loss
+
+    # ------------------------------------------------------------------ data parallel
+    def _reduce_async(self, names: List[str]):
+        if self.world <= 1:
+            return
+        import torch.distributed as dist
+        if not hasattr(self, "_pending"):
+            self._pending = []
+        for n in names:
+            self._pending.append(dist.all_reduce(self.grad[n], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
+    def _wait_reduce(self):
+        for w in getattr(self, "_pending", []):
+            w.wait()
+        self._pending = []
+
+    # ------------------------------------------------------------------ optimizer
+    def optimizer_step(self):
+        self._wait_reduce()
+        lr = linear_warmup_lr(self.lr, self.step_count, self.warmup, self.total) if self.total > 0 else self.lr
+        self.step_count += 1
+        scale = 1.0 / self.world                                   # mean over ranks (DDP semantics)
+        for n in self.names:
+            p = self.param[n]
+            ops.adamw_(self.master[n], self.grad[n], self.m[n], self.v[n], p.detach() if p.dtype == torch.bfloat16 else None,
+                       lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_count, scale)
+            if p.dtype != torch.bfloat16:
+                p.detach().copy_(self.master[n])
+        # refresh derived operands of the trainable tensors
+        self.model._lm_head_T = None
+        self.model._packed_proj.refresh()
+
+    def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One iteration of train.py:157-184 on a collate_fn-shaped batch (dataset.py:184-194)."""
+        self.zero_grad()
+        loss = self.forward_backward(batch["tokens"], batch["attention_masks"], batch["pcrgbs"], batch["prompts"].shape[1],
+                                     fps_start)
+        self.optimizer_step()
+        return loss

@@ -74,6 +74,112 @@ int esb_traj_ids_to_poses(const int64_t* ids, int B, int T, int num_bins, int64_
                           int64_t eos_id, int scale_mode, double d_max, double d_min, int max_steps, int pad_repeat,
                           float* out, int32_t* count, void* stream);
 
+/* ------------------------------------------------------------------------------------------------ norms
+ * HF LlamaRMSNorm.forward (modeling_llama.py:53-67; call sites input_layernorm / post_attention_layernorm / model.norm
+ * reached from pointllm/model/pointllm.py:173-178): y = w * bf16(x * rsqrt(mean(x^2) + eps)).  rstd [rows] fp32 is kept
+ * for the backward.  x, w, y bf16; d, ldx, ldy multiples of 8. */
+int esb_rmsnorm_fwd(const void* x, int64_t ldx, const void* w, void* y, int64_t ldy, float* rstd, int64_t rows, int d,
+                    float eps, void* stream);
+/* Backward of the above (autograd of modeling_llama.py:53-67): dx = d(rmsnorm)/dx . dy (+ dres if not NULL);
+ * dw (fp32 [d], accumulated with atomics) only when not NULL (model.norm is trainable, model_arch.py:33-51). */
+int esb_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, const void* dres, void* dx, float* dw,
+                    int64_t rows, int d, void* stream);
+/* nn.LayerNorm(eps) of PointBERT (pointbert/point_encoder.py:62,66,142) with the per-block `x + pos`
+ * (point_encoder.py:96-97) fused: s = x + add[row % add_period] (written to sum_out when not NULL), y = LN(s). */
+int esb_layernorm_fwd(const void* x, const void* add, int64_t add_period, const float* gamma, const float* beta,
+                      void* sum_out, void* y, int64_t rows, int d, float eps, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ element-wise
+ * HF apply_rotary_pos_emb (modeling_llama.py:138-168) in place on `n_heads` heads of width hd starting at column 0 of
+ * buf [rows, ld] (q and k heads of the packed qkv projection); position of row r is pos0 + r % L; cos/sin tables
+ * [max_pos, hd/2] bf16 (LlamaRotaryEmbedding, :117-135).  inverse=1 applies the transposed rotation (backward).
+ * When kcache != NULL the rotated K heads [kv_head0, kv_head0+kv_heads) and the V heads at column v_col0 are also
+ * written to kcache/vcache [B, cache_len, kv_heads*hd] at position pos0 + r % L (DynamicCache.update, :269-270). */
+int esb_rope(void* buf, int64_t ld, int64_t rows, int L, int n_heads, int hd, const void* cos_tab, const void* sin_tab,
+             int pos0, int inverse, void* kcache, void* vcache, int kv_head0, int kv_heads, int64_t v_col0, int cache_len,
+             void* stream);
+/* HF LlamaMLP act_fn(gate_proj(x)) * up_proj(x) (modeling_llama.py:171-184) on gu [rows, 2f] = (gate | up). */
+int esb_silu_mul_fwd(const void* gu, void* act, int64_t rows, int f, void* stream);
+int esb_silu_mul_bwd(const void* gu, const void* dact, void* dgu, int64_t rows, int f, void* stream);
+/* nn.GELU() (exact erf) of point_proj (pointllm/model/pointllm.py:72-79): backward=0: y = gelu(z);
+ * backward=1: y = dy * gelu'(z).  n multiple of 8. */
+int esb_gelu(const void* z, const void* dy, void* y, int64_t n, int backward, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ embedding + splice
+ * Device-side version of the validation scans at pointllm/model/pointllm.py:138-164.
+ * info[b] = {n_start, n_end, n_patch, first_start_pos, end_follows_start, patches_consecutive, first_patch_pos, 0}. */
+int esb_point_layout(const int64_t* ids, int B, int L, int64_t patch_id, int64_t start_id, int64_t end_id, int n_point,
+                     int32_t* info, void* stream);
+/* embed_tokens(input_ids) (pointllm.py:107) + splice of the projected point tokens (pointllm.py:134-171):
+ * x[b,l] = feats[b, l - pos[b]] inside [pos[b], pos[b]+n_point), embed[ids[b,l]] elsewhere (pos[b] < 0: no splice). */
+int esb_embed_splice_fwd(const int64_t* ids, const void* embed, const void* feats, const int32_t* splice_pos, int n_point,
+                         void* x, int B, int L, int d, void* stream);
+/* Backward: point rows -> dfeats (bf16 copy), other rows scatter-added into dembed (fp32, row padding_idx skipped as
+ * nn.Embedding(padding_idx) does). */
+int esb_embed_splice_bwd(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, float* dembed,
+                         void* dfeats, int64_t padding_idx, int B, int L, int d, void* stream);
+/* Batched strided row copy (logits slice train.py:174-175, hidden-row gathers); all byte strides multiples of 16. */
+int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
+                  int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream);
+/* out[c, r] = in[r, c] (bf16): operand re-layout for the weight-gradient GEMMs. */
+int esb_transpose_bf16(const void* in, int64_t ld_in, void* out, int64_t ld_out, int R, int C, void* stream);
+/* out[n] += sum_m in[m, n]: bias gradients of point_proj. */
+int esb_colsum_bf16(const void* in, int64_t ld, int M, int N, float* out, void* stream);
+/* mini-PointNet pooling (pointbert/dvae.py:211-215,219): f [groups*n, C] -> concat=0: max over n [groups, C];
+ * concat=1: [groups*n, 2C] = (max over n broadcast | f). */
+int esb_group_maxpool(const void* f, void* out, int64_t groups, int n, int C, int concat, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ loss / sampling / optimizer
+ * train.py:174-181: mean cross-entropy over rows whose target != ignore_index; logits [rows, ld] bf16 (V valid columns).
+ * write_grad=1 overwrites logits with dloss/dlogits (bf16).  row_loss [rows], scratch [1], loss [1] fp32 device. */
+int esb_cross_entropy(void* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int64_t ignore_index,
+                      float* row_loss, float* scratch, float* loss, int write_grad, void* stream);
+/* Greedy step (HF generation/utils.py:2762-2806 via model_arch.py:94-108): first-max argmax per row of bf16 logits,
+ * optional fp32 `scores` copy, optional suppressed column (-1: none). */
+int esb_argmax_rows(const void* logits, int64_t ld, int64_t rows, int V, int64_t* out_idx, float* scores,
+                    int64_t scores_ld, int suppress_col, void* stream);
+/* Finished-row bookkeeping of the same loop: finished rows emit pad, EOS finishes a row, token appended to
+ * sequences[:, cur_len], attention mask grown by one. */
+int esb_greedy_update(const int64_t* next, int64_t* tokens_out, int32_t* unfinished, int64_t* sequences, int64_t seq_ld,
+                      int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, void* stream);
+/* torch.optim.AdamW step (train.py:107-113,184) on fp32 master weights; refreshes the bf16 model copy. */
+int esb_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr, float beta1, float beta2,
+              float eps, float weight_decay, int step, float grad_scale, void* stream);
+int esb_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ attention
+ * softmax(Q K^T * scale + mask) V, fp32 softmax.  LLaMA: HF sdpa path (integrations/sdpa_attention.py:40-98) with
+ * causal AND key-padding mask; PointBERT: pointbert/point_encoder.py:43-55 (causal=0, kmask=NULL).
+ * Element (b,l,h,e) at ptr + b*bs + l*rs + h*hd + e.  lse [B,H,Lq] fp32 (NULL to skip).  hd in {64,128}. */
+int esb_attn_fwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64_t k_bs, int64_t k_rs, const void* v,
+                 int64_t v_bs, int64_t v_rs, void* o, int64_t o_bs, int64_t o_rs, float* lse, const uint8_t* kmask,
+                 int64_t kmask_ld, int B, int H, int Lq, int Lk, int hd, int causal, int q_pos0, float scale, void* stream);
+/* Backward of esb_attn_fwd (autograd of the sdpa attention above; needed through all frozen layers because
+ * embed_tokens / point_proj are trainable, model_arch.py:33-51).  dvec [B,H,Lq] fp32 is scratch (rowsum(dO o O)).
+ * dq/dk/dv use the same (bs, rs) addressing as q/k/v, so they can be the three slices of one packed [B,L,3,H,hd] buffer. */
+int esb_attn_bwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64_t k_bs, int64_t k_rs, const void* v,
+                 int64_t v_bs, int64_t v_rs, const void* o, int64_t o_bs, int64_t o_rs, const void* dout, int64_t do_bs,
+                 int64_t do_rs, const float* lse, float* dvec, void* dq, int64_t dq_bs, int64_t dq_rs, void* dk, int64_t dk_bs,
+                 int64_t dk_rs, void* dv, int64_t dv_bs, int64_t dv_rs, const uint8_t* kmask, int64_t kmask_ld, int B, int H,
+                 int Lq, int Lk, int hd, int causal, int q_pos0, float scale, void* stream);
+/* One query token per sequence against the KV cache (the per-token step of generate, pointllm.py:255-275).
+ * Context length read from *len_ptr when not NULL (CUDA-graph friendly) else len_static. */
+int esb_attn_decode(const void* q, int64_t q_bs, const void* k, const void* v, int64_t kv_bs, int64_t kv_rs, void* o,
+                    int64_t o_bs, const uint8_t* kmask, int64_t kmask_ld, const int32_t* len_ptr, int len_static, int B,
+                    int H, int hd, float scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ point cloud
+ * pointbert/misc.py:40-60 fps: pts [B,N,C] fp32 (xyz first), start [B] = the torch.randint draw of misc.py:52;
+ * centers [B,G,3] fp32, center_idx [B,G].  Index-exact with the reference's fp32 arithmetic.
+ * centers_bf16_pad (optional) [B*G, pad_ld] bf16 = (x, y, z, 0...) rows, the A operand of pos_embed.0
+ * (pointbert/point_encoder.py:126-130). */
+int esb_fps(const float* pts, int B, int N, int C, int G, const int64_t* start, float* centers, int32_t* center_idx,
+            void* centers_bf16_pad, int pad_ld, void* stream);
+/* pointbert/dvae.py:107-140,150-187: k nearest points of every centre, xyz re-centred, emitted as bf16 rows
+ * [B*G*K, out_ld] (columns >= C zero) in ascending point-index order; idx_out [B,G,K] optional. */
+int esb_knn_group(const float* pts, const float* centers, int B, int N, int C, int G, int K, int out_ld, void* nb_out,
+                  int32_t* idx_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,226 @@
+"""GPU: op-level numerics of the floating-point kernels against plain fp32 torch references of the same op
+(RMSNorm / LayerNorm / RoPE / SwiGLU / GELU / attention fwd+bwd+decode / CE / AdamW / splice / pooling)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from egoscaler_b200 import ops
+from egoscaler_b200.llm import rope_tables
+
+
+def rnd(*shape, seed=0, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, device="cuda", generator=g) * scale).bfloat16()
+
+
+def close(a, b, tol):
+    a, b = a.float(), b.float()
+    err = (a - b).abs().max().item()
+    ref = b.abs().max().item()
+    assert err <= tol * max(ref, 1e-6), (err, ref)
+
+
+@pytest.mark.parametrize("rows,d", [(7, 256), (1392, 4096), (33, 688)])
+def test_rmsnorm_fwd_bwd(rows, d):
+    x, w, dy, dres = rnd(rows, d, seed=1), (1 + 0.1 * rnd(d, seed=2).float()).bfloat16(), rnd(rows, d, seed=3), rnd(rows, d, seed=4)
+    y, rstd = ops.rmsnorm(x, w, 1e-6, want_rstd=True)
+    xf = x.float().requires_grad_(True)
+    wf = w.float().requires_grad_(True)
+    ref = wf * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6))
+    close(y, ref, 1e-2)
+    ref.backward(dy.float())
+    dw = torch.zeros(d, device="cuda")
+    dx = ops.rmsnorm_bwd(dy, x, w, rstd, dres=dres, dw=dw)
+    close(dx, xf.grad + dres.float(), 1.5e-2)
+    close(dw, wf.grad, 1e-2)
+    # strided input rows
+    big = rnd(rows, 2 * d, seed=5)
+    close(ops.rmsnorm(big[:, :d], w, 1e-6), ops.rmsnorm(big[:, :d].contiguous(), w, 1e-6), 0.0)
+
+
+@pytest.mark.parametrize("rows,d", [(1026, 384), (50, 1152)])
+def test_layernorm_fused_add(rows, d):
+    x, add = rnd(rows, d, seed=1), rnd(rows, d, seed=2)
+    g, b = 1 + 0.1 * torch.randn(d, device="cuda"), 0.1 * torch.randn(d, device="cuda")
+    s_ref = (x.float() + add.float()).bfloat16()
+    xs = x.clone()
+    y = ops.layernorm(xs, g, b, add=add, sum_out=xs)
+    assert torch.equal(xs, s_ref)
+    close(y, F.layer_norm(s_ref.float(), (d,), g, b, 1e-5), 1e-2)
+    close(ops.layernorm(x, g, b), F.layer_norm(x.float(), (d,), g, b, 1e-5), 1e-2)
+
+
+@pytest.mark.parametrize("hd,H", [(64, 4), (128, 2)])
+def test_rope_forward_inverse_and_cache(hd, H):
+    B, L, d = 2, 37, H * hd
+    cos, sin = rope_tables(hd, 10000.0, 128, "cuda")
+    qkv = rnd(B * L, 3 * d, seed=3)
+    ref = qkv.clone().float().view(B, L, 3, H, hd)
+    c = torch.cat((cos, cos), -1)[None, 5:5 + L, None, :].float()
+    s = torch.cat((sin, sin), -1)[None, 5:5 + L, None, :].float()
+    rot = lambda t: torch.cat((-t[..., hd // 2:], t[..., :hd // 2]), -1)
+    for j in (0, 1):
+        ref[:, :, j] = ref[:, :, j] * c + rot(ref[:, :, j]) * s
+    kc = torch.zeros(B, 64, d, device="cuda", dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    out = ops.rope_(qkv.clone(), L, 2 * H, hd, cos, sin, pos0=5, kcache=kc, vcache=vc, kv_head0=H, kv_heads=H, v_col0=2 * d,
+                    cache_len=64)
+    close(out.view(B, L, 3, H, hd), ref, 1.2e-2)
+    assert torch.equal(kc[:, 5:5 + L].reshape(B, L, d), out.view(B, L, 3, d)[:, :, 1])
+    assert torch.equal(vc[:, 5:5 + L].reshape(B, L, d), qkv.view(B, L, 3, d)[:, :, 2])
+    back = ops.rope_(out.clone(), L, 2 * H, hd, cos, sin, pos0=5, inverse=True)
+    close(back.view(B, L, 3, d)[:, :, :2], qkv.view(B, L, 3, d)[:, :, :2], 2e-2)
+
+
+def test_swiglu_and_gelu():
+    rows, f = 300, 688
+    gu, da = rnd(rows, 2 * f, seed=1), rnd(rows, f, seed=2)
+    guf = gu.float().requires_grad_(True)
+    ref = F.silu(guf[:, :f]) * guf[:, f:]
+    close(ops.silu_mul(gu), ref, 1e-2)
+    ref.backward(da.float())
+    close(ops.silu_mul_bwd(gu, da), guf.grad, 1.5e-2)
+    z, dy = rnd(64, 1024, seed=3), rnd(64, 1024, seed=4)
+    zf = z.float().requires_grad_(True)
+    r = F.gelu(zf)
+    close(ops.gelu(z), r, 1e-2)
+    r.backward(dy.float())
+    close(ops.gelu_bwd(z, dy), zf.grad, 1.5e-2)
+
+
+def _attn_ref(q, k, v, causal, kmask, q_pos0=0):
+    B, Lq, H, hd = q.shape
+    Lk = k.shape[1]
+    s = torch.einsum("bihe,bjhe->bhij", q.float(), k.float()) * hd ** -0.5
+    m = torch.ones(B, 1, Lq, Lk, dtype=torch.bool, device=q.device)
+    if causal:
+        m = m & (torch.arange(Lk, device=q.device)[None, :] <= (torch.arange(Lq, device=q.device)[:, None] + q_pos0))[None, None]
+    if kmask is not None:
+        m = m & kmask[:, None, None, :Lk].bool()
+    s = s.masked_fill(~m, float("-inf"))
+    p = torch.softmax(s, -1)
+    return torch.einsum("bhij,bjhe->bihe", p, v.float()).reshape(B, Lq, H * hd), torch.logsumexp(s, -1)
+
+
+@pytest.mark.parametrize("hd,H,L,causal", [(64, 4, 696, True), (128, 2, 200, True), (64, 6, 513, False), (128, 3, 64, True), (64, 2, 77, True)])
+def test_attention_fwd_bwd(hd, H, L, causal):
+    B, d = 2, H * hd
+    qkv = rnd(B, L, 3, H, hd, seed=7)
+    kmask = None
+    if causal:
+        kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+        kmask[0, L // 2:L // 2 + 5] = 0                           # mid-sequence padding like collate_fn
+        kmask[1, L - 9:] = 0
+    o, lse = ops.attention(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal=causal, kmask=kmask, want_lse=True)
+    qf = qkv.float().requires_grad_(True)
+    ref_o, ref_lse = _attn_ref(qf[:, :, 0], qf[:, :, 1], qf[:, :, 2], causal, kmask)
+    close(o, ref_o, 1.5e-2)
+    assert (lse - ref_lse).abs().max() < 2e-2
+    do = rnd(B, L, d, seed=8)
+    ref_o.backward(do.float())
+    dqkv = ops.attention_bwd(qkv, o, lse, do, causal=causal, kmask=kmask)
+    for j, name in enumerate("qkv"):
+        close(dqkv[:, :, j], qf.grad[:, :, j], 2.5e-2)
+
+
+@pytest.mark.parametrize("hd,H", [(64, 4), (128, 32)])
+def test_attention_prefill_with_cache_and_decode(hd, H):
+    B, d, Lmax, P = 3, H * hd, 96, 70
+    kc, vc = rnd(B, Lmax, d, seed=1), rnd(B, Lmax, d, seed=2)
+    kmask = torch.ones(B, Lmax, device="cuda", dtype=torch.uint8)
+    kmask[1, 10:14] = 0
+    # chunked prefill: 6 new queries at positions P-6..P-1 against the cache
+    q = rnd(B, 6, H, hd, seed=3)
+    o = ops.attention(q, kc[:, :P].view(B, P, H, hd), vc[:, :P].view(B, P, H, hd), causal=True, kmask=kmask, q_pos0=P - 6)
+    ref, _ = _attn_ref(q, kc[:, :P].view(B, P, H, hd), vc[:, :P].view(B, P, H, hd), True, kmask, P - 6)
+    close(o, ref, 1.5e-2)
+    # single-token decode
+    q1 = rnd(B, 3 * d, seed=4)
+    od = ops.attention_decode(q1, kc, vc, H, hd, kmask=kmask, len_static=P)
+    ref1, _ = _attn_ref(q1[:, :d].reshape(B, 1, H, hd), kc[:, :P].view(B, P, H, hd), vc[:, :P].view(B, P, H, hd), False, kmask)
+    close(od, ref1.view(B, d), 1.5e-2)
+    ln = torch.tensor([P], device="cuda", dtype=torch.int32)
+    assert torch.equal(ops.attention_decode(q1, kc, vc, H, hd, kmask=kmask, len_ptr=ln), od)
+
+
+def test_cross_entropy_and_argmax():
+    rows, V, ld = 304, 32262, 32264
+    buf = rnd(rows, ld, seed=5, scale=2.0)
+    logits = buf[:, :V]
+    tg = torch.randint(3, V, (rows,), device="cuda")
+    tg[::7] = 0
+    lf = logits.float().requires_grad_(True)
+    ref = F.cross_entropy(lf, tg, ignore_index=0)
+    ref.backward()
+    am = ops.argmax_rows(logits, V)
+    assert torch.equal(am, logits.float().argmax(-1))
+    sc = torch.empty(rows, V, device="cuda")
+    am2 = ops.argmax_rows(logits, V, scores=sc, suppress_col=int(am[0]))
+    assert am2[0] != am[0] and torch.isinf(sc[0, int(am[0])]) and torch.equal(sc[1], logits[1].float())
+    loss = ops.cross_entropy(logits, V, tg, 0, write_grad=True)
+    assert abs(float(loss) - float(ref)) < 2e-3 * float(ref)
+    close(logits, lf.grad, 1e-2)
+    # tie -> first index
+    t = torch.zeros(2, 64, device="cuda", dtype=torch.bfloat16)
+    t[0, 5] = t[0, 9] = 3.0
+    assert ops.argmax_rows(t, 64).tolist() == [5, 0]
+
+
+def test_adamw_matches_torch():
+    n = 10007
+    p0, g = torch.randn(n, device="cuda"), torch.randn(n, device="cuda")
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([ref], lr=2e-3)
+    p, m, v = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    pb = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    for step in range(1, 4):
+        ref.grad = g * step
+        opt.step()
+        ops.adamw_(p, g * step * 2, m, v, pb, 2e-3, 0.9, 0.999, 1e-8, 0.01, step, grad_scale=0.5)
+    torch.testing.assert_close(p, ref.detach(), atol=1e-6, rtol=1e-5)
+    assert torch.equal(pb, p.bfloat16())
+
+
+def test_embed_splice_fwd_bwd_and_layout():
+    B, L, d, V, Np = 2, 40, 64, 100, 9
+    ids = torch.randint(3, 90, (B, L), device="cuda")
+    ids[:, 2] = 97; ids[:, 3:3 + Np] = 96; ids[:, 3 + Np] = 98; ids[1, 30:] = 0
+    info = ops.point_layout(ids, 96, 97, 98, Np).cpu()
+    assert info[0, :7].tolist() == [1, 1, Np, 2, 1, 1, 3]
+    emb, feats = rnd(V, d, seed=1), rnd(B, Np, d, seed=2)
+    pos = torch.tensor([3, 3], device="cuda", dtype=torch.int32)
+    x = ops.embed_splice(ids, emb, feats, pos, Np).view(B, L, d)
+    ref = emb[ids]
+    ref[:, 3:3 + Np] = feats
+    assert torch.equal(x, ref)
+    dx = rnd(B * L, d, seed=3)
+    dE = torch.zeros(V, d, device="cuda")
+    dF = torch.empty(B, Np, d, device="cuda", dtype=torch.bfloat16)
+    ops.embed_splice_bwd(ids, dx, pos, Np, dE, dF, 0)
+    assert torch.equal(dF, dx.view(B, L, d)[:, 3:3 + Np])
+    refE = torch.zeros(V, d, device="cuda")
+    keep = torch.ones(B, L, dtype=torch.bool, device="cuda"); keep[:, 3:3 + Np] = False; keep &= ids != 0
+    refE.index_put_((ids[keep],), dx.view(B, L, d)[keep].float(), accumulate=True)
+    torch.testing.assert_close(dE, refE, atol=1e-4, rtol=1e-4)
+    assert float(dE[0].abs().max()) == 0.0
+
+
+def test_pool_transpose_colsum_copy():
+    f = rnd(8 * 32, 256, seed=1)
+    mx = f.view(8, 32, 256).float().max(1).values
+    assert torch.equal(ops.group_maxpool(f, 32, False).float(), mx)
+    cat = ops.group_maxpool(f, 32, True)
+    assert torch.equal(cat[:, 256:], f) and torch.equal(cat[:, :256].float(), mx.repeat_interleave(32, 0))
+    x = rnd(77, 130, seed=2)
+    assert torch.equal(ops.transpose(x), x.t())
+    cs = torch.zeros(130, device="cuda")
+    ops.colsum(x, cs)
+    torch.testing.assert_close(cs, x.float().sum(0), atol=1e-3, rtol=1e-4)
+    src = rnd(3, 20, 64, seed=3)
+    dst = torch.zeros(3, 5, 64, device="cuda", dtype=torch.bfloat16)
+    ops.copy_rows(src[:, 7:12, :], dst)
+    assert torch.equal(dst, src[:, 7:12])
