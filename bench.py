@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""Benchmark of the trajectory-VLM training step (BASELINE.json configs[1]: full-size traj-VLM bf16 training step,
+LLaMA-7B dims + PointBERT v1.2, per-GPU batch 8, L=696, P=544, default freezing) on N B200s of one node.
+
+    python bench.py --gpus N --steps K --warmup W            # our CUDA path (one JSON line on rank 0)
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU oracle port on the host cores (rank 0 only)
+
+A "step" = forward + backward + gradient all-reduce (N>1) + AdamW on one synthetic collate_fn-shaped batch.
+`value` = samples/s with the batch already resident in HBM; `e2e` = the same step fed from pinned HOST buffers
+(H2D of tokens / masks / clouds inside the timed region) with the loss read back (D2H) every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "train samples/s"
+UNIT = "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="full", choices=["full", "tiny"])
+    ap.add_argument("--batch", type=int, default=8, help="per-GPU batch (train.py --bs 8)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=200.0)
+    return ap.parse_args()
+
+
+def workload_name(cfgname, B):
+    if cfgname == "full":
+        return f"full-size traj-VLM bf16 training step (LLaMA-7B dims, PointBERT v1.2, B={B}/GPU, L=696, P=544, default freezing)"
+    return f"tiny traj-VLM training step (d=256, 2 layers, B={B}/GPU, L=696)"
+
+
+def flops_per_sample_train(cfg, L=696, T=152):
+    """forward + data-gradients through the trunk/attention, head on T rows fwd+dgrad+wgrad, projector
+    fwd+dgrad+wgrad, encoder forward only."""
+    d, f, n, V = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers, cfg.vocab_size
+    lin = 2 * L * n * (4 * d * d + 3 * d * f)
+    att = 2 * L * L * d * n
+    head = 2 * T * d * V
+    p = cfg.point
+    Np = p.point_token_len
+    dims = [p.trans_dim] + list(p.projection_hidden_dim) + [d]
+    proj = sum(2 * Np * a * b for a, b in zip(dims[:-1], dims[1:]))
+    enc = 2 * Np * p.depth * 12 * p.trans_dim ** 2 + 4 * Np * Np * p.trans_dim * p.depth \
+        + 2 * p.num_group * p.group_size * (p.point_dims * 128 + 128 * 256 + 512 * 512 + 512 * p.encoder_dims)
+    return 2 * (lin + att) + 3 * (head + proj) + enc
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap", nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+class GemmTimer:
+    """CUDA-event pairs around every GEMM launch of the timed region (same stream as the launches)."""
+
+    def __init__(self, torch):
+        self.torch, self.pairs, self.flops, self.n = torch, [], 0.0, 0
+        self.pool = []
+
+    def before(self, M, N, K):
+        t = self.torch
+        a = t.cuda.Event(enable_timing=True)
+        b = t.cuda.Event(enable_timing=True)
+        a.record()
+        self.pairs.append((a, b))
+        self.flops += 2.0 * M * N * K
+        self.n += 1
+
+    def after(self):
+        self.pairs[-1][1].record()
+
+    def total_ms(self):
+        return sum(a.elapsed_time(b) for a, b in self.pairs)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def build_model(torch, cfg, device):
+    """Random-init weights of the named architecture (no checkpoint is available offline): N(0, 0.02) for the LLM /
+    embeddings / head (HF initializer_range), fan-in scaled for the point encoder and projector, identity norms."""
+    from egoscaler_b200.model import TrajPointLLMForCausalLM
+    from egoscaler_b200 import decode  # noqa: F401
+    m = TrajPointLLMForCausalLM(cfg, device)
+    g = torch.Generator(device=device).manual_seed(0)
+    with torch.no_grad():
+        for name, p in list(m.named_parameters()) + list(m.named_buffers()):
+            leaf = name.rsplit(".", 1)[-1]
+            if leaf == "num_batches_tracked":
+                continue
+            if leaf == "running_var" or ("norm" in name and leaf == "weight") or (".1.weight" in name and "conv" in name):
+                p.fill_(1.0)
+            elif leaf in ("running_mean", "bias"):
+                p.zero_()
+            elif p.dim() >= 2 and ("point_backbone" in name or "point_proj" in name):
+                p.normal_(0.0, 1.0 / (p.shape[1] ** 0.5), generator=g)
+            else:
+                p.normal_(0.0, 0.02, generator=g)
+    m.repack()
+    return m
+
+
+def host_batches(torch, cfg, B, n, seed0):
+    from egoscaler_b200 import synth
+    out = []
+    for i in range(n):
+        bt = synth.make_batch(cfg, B, seed=seed0 + i, random_desc_len=True)
+        out.append({k: v.pin_memory() for k, v in bt.items()})
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from egoscaler_b200 import lib as esb_lib, ops
+    from egoscaler_b200.config import TrajVLMConfig
+    from egoscaler_b200.trainer import Trainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = TrajVLMConfig.full() if args.config == "full" else TrajVLMConfig.tiny()
+    B = args.batch
+    model = build_model(torch, cfg, dev)
+    model.train()
+    tr = Trainer(model, lr=2e-5, world_size=world)
+    nb = 4
+    hb = host_batches(torch, cfg, B, nb, seed0=1000 * (rank + 1))          # different data per rank, same weights
+    P = hb[0]["prompts"].shape[1]
+    L = hb[0]["tokens"].shape[1]
+    dbatches = [{k: v.to(dev) for k, v in b.items()} for b in hb]
+    n_pts = hb[0]["pcrgbs"].shape[1]
+    starts = [torch.randint(0, n_pts, (B,), generator=torch.Generator().manual_seed(7 + i)).pin_memory() for i in range(nb)]
+    dstarts = [s.to(dev) for s in starts]
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step_resident(i):
+        return tr.train_step(dbatches[i % nb], dstarts[i % nb])
+
+    stage = {k: torch.empty_like(v, device=dev) for k, v in hb[0].items()}
+    stage_start = torch.empty(B, device=dev, dtype=torch.long)
+
+    def step_e2e(i):
+        b = hb[i % nb]
+        for k in ("tokens", "attention_masks", "pcrgbs", "prompts"):
+            stage[k].copy_(b[k], non_blocking=True)
+        stage_start.copy_(starts[i % nb], non_blocking=True)
+        loss = tr.train_step(stage, stage_start)
+        return float(loss.cpu())                                           # D2H read of the loss, every step
+
+    def timed(fn, steps):
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for i in range(steps):
+            last = fn(i)
+        e1.record()
+        sync_all()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms), last
+
+    for i in range(max(args.warmup, 3)):
+        step_resident(i)
+    sampler = ClockSampler(local)
+    sampler.start()
+    timer = GemmTimer(torch)
+    ops.gemm_timer = timer
+    l0 = esb_lib.launch_count
+    ms_res, loss_res = timed(step_resident, args.steps)
+    launches = (esb_lib.launch_count - l0) // args.steps
+    ops.gemm_timer = None
+    torch.cuda.synchronize()
+    gemm_ms = timer.total_ms()
+    for i in range(2):
+        step_e2e(i)
+    ms_e2e, loss_e2e = timed(step_e2e, args.steps)
+    clocks = sampler.stop()
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if "bf16_tflops_sustained" in peaks else "fallback 1.4 PFLOP/s sustained"
+    achieved_tf = timer.flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    samples = B * world * args.steps
+    value = samples / (ms_res * 1e-3)
+    e2e = samples / (ms_e2e * 1e-3)
+    h2d = sum(hb[0][k].numel() * hb[0][k].element_size() for k in ("tokens", "attention_masks", "pcrgbs", "prompts")) + B * 8
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms_res / args.steps, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic (collate_fn-shaped batches, random-init weights)",
+        "config": {"workload": workload_name(args.config, B), "per_gpu_batch": B, "global_batch": B * world, "seq_len": L,
+                   "prompt_len": P, "parallelism": f"dp{world}", "l2": "working set (13.5 GB of weights per pass) >> 126 MB L2"},
+        "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+                "ms_per_step": round(ms_e2e / args.steps, 3)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel", "achieved": round(achieved_tf, 1), "peak": peak_tf,
+                     "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": None, "peak_source": peak_src,
+                     "launches_per_step": timer.n // args.steps, "gemm_ms_per_step": round(gemm_ms / args.steps, 3),
+                     "gemm_share_of_step": round(gemm_ms / ms_res, 4),
+                     "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
+        "loss": round(float(loss_res), 4),
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_reference_step(args, budget_s=min(args.cpu_budget_s, 60.0), max_steps=1)
+            except Exception as e:  # the baseline is informative; the GPU numbers stand without it
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "error": repr(e)[:200]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------ CPU oracle port
+def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 0):
+    """Times the reference algorithm's training step (oracle/traj_vlm.py, plain fp32 PyTorch restatement of
+    pointllm.py:181-253 + train.py:166-184) on the host cores, on a bounded sample of the workload: ONE sample
+    (B=1) of the same config per step.  kind="port": /root/reference does not exist on the GPU box."""
+    import psutil
+    import torch
+    from egoscaler_b200 import synth
+    from egoscaler_b200.config import TrajVLMConfig
+    from oracle.traj_vlm import LlmCfg, PointCfg, TrajVLMOracle, train_loss
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = TrajVLMConfig.full() if args.config == "full" else TrajVLMConfig.tiny()
+    llm = LlmCfg.full() if args.config == "full" else LlmCfg.tiny()
+    layers = llm.num_layers
+    need_gb = 4e-9 * (llm.num_layers * (4 * llm.hidden_size ** 2 + 3 * llm.hidden_size * llm.intermediate_size)
+                      + 2 * llm.vocab_size * llm.hidden_size) * 1.35 + 8
+    avail_gb = psutil.virtual_memory().available / 1e9
+    note = ""
+    if need_gb > avail_gb:                      # not enough host RAM for 27 GB of fp32 weights: fewer layers, say so
+        layers = max(1, int(llm.num_layers * (avail_gb - 12) / need_gb))
+        llm.num_layers = layers
+        note = f" (host RAM {avail_gb:.0f} GB: {layers} of {cfg.num_hidden_layers} layers)"
+    with torch.device("meta"):
+        m = TrajVLMOracle(llm, PointCfg())
+    m = m.to_empty(device="cpu")
+    with torch.no_grad():
+        for n_, p in list(m.named_parameters()) + list(m.named_buffers()):
+            if not p.dtype.is_floating_point:
+                p.zero_()
+            elif n_.endswith("running_var") or (p.dim() == 1 and not n_.endswith("bias") and not n_.endswith("running_mean")):
+                p.fill_(1.0)
+            elif p.dim() == 1:
+                p.zero_()
+            else:
+                p.uniform_(-0.035, 0.035)
+    m.configure_trainable()
+    m.train()
+    m.model.layers.eval()
+    m.model.point_backbone.eval()
+    opt = torch.optim.AdamW([q for q in m.parameters() if q.requires_grad], lr=2e-5)
+    bt = synth.make_batch(cfg, 1, seed=5)
+    P = bt["prompts"].shape[1]
+    times = []
+    t_begin = time.time()
+    for i in range(warmup + max_steps):
+        t0 = time.time()
+        opt.zero_grad(set_to_none=True)
+        logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=torch.zeros(1, dtype=torch.long), training=True)
+        loss = train_loss(logits, bt["tokens"], P, cfg.pad_token_id)
+        loss.backward()
+        opt.step()
+        dt = time.time() - t0
+        if i >= warmup:
+            times.append(dt)
+        if time.time() - t_begin > budget_s and times:
+            break
+    t = sum(times) / len(times)
+    return {"value": round(1.0 / t, 5), "unit": UNIT, "cores": cores, "kind": "port", "steps_timed": len(times),
+            "s_per_step": round(t, 3),
+            "sample": f"1 sample (B=1) per step of the same workload, fp32, torch {torch.__version__} CPU, "
+                      f"{torch.get_num_threads()} threads{note}"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # keep the whole run within a few minutes whatever K/W the driver asks for
+    warm = 1 if args.warmup > 0 else 0
+    cb = cpu_reference_step(args, budget_s=args.cpu_budget_s, max_steps=max(1, args.steps), warmup=warm)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world,
+        "steps": cb["steps_timed"], "steps_requested": args.steps, "warmup": warm,
+        "ms_per_step": round(cb["s_per_step"] * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic (collate_fn-shaped batch, random-init weights)",
+        "config": {"workload": workload_name(args.config, args.batch), "sample": cb["sample"]},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -82,6 +82,9 @@ class _Lib:
 
 
 _lib = None
+# kernels launched per entry point (everything else launches exactly one); bench.py reports the total
+KERNELS_PER_CALL = {"esb_cross_entropy": 3, "esb_attn_bwd": 3}
+launch_count = 0
 
 
 def lib() -> _Lib:
@@ -92,4 +95,6 @@ def lib() -> _Lib:
 
 
 def call(name, *args):
+    global launch_count
+    launch_count += KERNELS_PER_CALL.get(name, 1)
     return lib().call(name, *args)

@@ -195,9 +195,9 @@ class TrajPointLLMForCausalLM(ParamTree):
         pos0 = cache.length if cache is not None else 0
         feats = None
         if (L != 1 or self.training) and point_clouds is not None:       # pointllm.py:112
+            if splice_pos is None:                                       # host-side checks first: the (async)
+                splice_pos = self.splice_positions(input_ids)            # encoder launches then queue without a sync
             feats = self.point_features(point_clouds, fps_start, proj_saved)
-            if splice_pos is None:
-                splice_pos = self.splice_positions(input_ids)
         x = ops.embed_splice(input_ids, self.model.embed_tokens.weight.detach(), feats, splice_pos if feats is not None else None,
                              self.point_backbone_config["point_token_len"])
         h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved)

@@ -13,6 +13,7 @@ import torch
 from . import lib as _l
 
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
+gemm_timer = None      # bench.py installs an object with .before(M, N, K) / .after() to time the GEMM launches
 SCALE_NONE, SCALE_RT2, SCALE_SIMPLE, SCALE_DENORM = 0, 1, 2, 3
 
 
@@ -54,9 +55,13 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
         _chk(residual, torch.bfloat16, "gemm.residual")
         assert residual.shape == (M, N) and residual.stride(1) == 1
         ldr = residual.stride(0)
+    if gemm_timer is not None:
+        gemm_timer.before(M, N, K)
     _l.call("esb_gemm_bf16", a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), out.data_ptr(), out.stride(0),
             M, N, K, _p(bias), _p(residual), ldr, act, 1 if out.dtype == torch.float32 else 0,
             1 if accumulate else 0, float(alpha), force_bn, _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
     return out
 
 
