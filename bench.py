@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--config", default="full", choices=["full", "tiny"])
     ap.add_argument("--batch", type=int, default=8, help="per-GPU batch (train.py --bs 8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-decode", action="store_true", help="skip the batched greedy-decode measurement")
+    ap.add_argument("--decode-batch", type=int, default=32, help="sequences per GPU (BASELINE configs[3]: 256 / 8 GPUs)")
     ap.add_argument("--cpu-budget-s", type=float, default=200.0)
     return ap.parse_args()
 
@@ -266,6 +268,10 @@ def run_b200(args):
                      "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
         "loss": round(float(loss_res), 4),
     }
+    if not args.no_decode:
+        del tr
+        torch.cuda.empty_cache()
+        line["decode"] = decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             try:
@@ -275,6 +281,52 @@ def run_b200(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks):
+    """BASELINE configs[3]: batched greedy trajectory generation with the static KV cache, batch-sharded (no
+    collective): `--decode-batch` prompts per GPU of P=544 tokens (point block + description + first pose), T=152 new
+    tokens, EOS suppressed so every sequence runs full length.  traj/s = sequences / wall of
+    generate() (prefill incl. point encoder + T cached steps), timed with CUDA events, max over ranks."""
+    from egoscaler_b200 import synth
+    Bd = args.decode_batch
+    bt = synth.make_batch(cfg, Bd, seed=77 + rank)
+    prompts, pmask, clouds = bt["prompts"].to(dev), bt["prompt_masks"].to(dev), bt["pcrgbs"].to(dev)
+    P = prompts.shape[1]
+    T = bt["tokens"].shape[1] - P
+    start = torch.randint(0, clouds.shape[1], (Bd,), generator=torch.Generator().manual_seed(3)).to(dev)
+    model.eval()
+
+    def run(t_new):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = model.generate(input_ids=prompts, attention_mask=pmask, point_clouds=clouds, max_length=t_new, do_sample=False,
+                             fps_start=start, suppress_eos=True)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms), out
+
+    run(4)                                                                  # warm-up (allocator, lazy operands)
+    ms1, _ = run(1)
+    ms_full = min(run(T)[0] for _ in range(2))
+    d, f, n, V = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers, cfg.vocab_size
+    per_tok_ms = (ms_full - ms1) / max(1, T - 1)
+    ctx_mean = P + T / 2.0
+    step_bytes = 2.0 * (n * (4 * d * d + 3 * d * f) + d * V) + Bd * 2 * n * d * 2 * ctx_mean     # weights + mean KV
+    hbm = float(peaks.get("hbm_gbs", 6400.0))
+    ach = step_bytes / (per_tok_ms * 1e-3) / 1e9 if per_tok_ms > 0 else 0.0
+    return {"metric": "traj decode/s", "value": round(Bd * world / (ms_full * 1e-3), 3), "unit": "traj/s",
+            "tok_per_s": round(Bd * world * T / (ms_full * 1e-3), 1), "batch_per_gpu": Bd, "global_batch": Bd * world,
+            "prompt_len": P, "new_tokens": T, "mode": "greedy, KV cache, EOS suppressed", "ms_total": round(ms_full, 2),
+            "ms_prefill_plus_first_token": round(ms1, 2), "ms_per_token_step": round(per_tok_ms, 3),
+            "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
+                         "bytes_per_step": int(step_bytes)}}
 
 
 # ------------------------------------------------------------------------------------------------ CPU oracle port
