@@ -21,9 +21,9 @@ int esb_layernorm_fwd(const void* x, const void* add, int64_t add_period, const 
 }
 int esb_rope(void* buf, int64_t ld, int64_t rows, int L, int n_heads, int hd, const void* cos_tab, const void* sin_tab,
              int pos0, int inverse, void* kcache, void* vcache, int kv_head0, int kv_heads, int64_t v_col0, int cache_len,
-             void* stream) {
+             const int32_t* pos_ptr, void* stream) {
     return rope(buf, ld, rows, L, n_heads, hd, cos_tab, sin_tab, pos0, inverse, kcache, vcache, kv_head0, kv_heads, v_col0,
-                cache_len, ST(stream));
+                cache_len, pos_ptr, ST(stream));
 }
 int esb_silu_mul_fwd(const void* gu, void* act, int64_t rows, int f, void* stream) { return silu_mul_fwd(gu, act, rows, f, ST(stream)); }
 int esb_silu_mul_bwd(const void* gu, const void* dact, void* dgu, int64_t rows, int f, void* stream) {
@@ -60,12 +60,15 @@ int esb_cross_entropy(void* logits, int64_t ld, int64_t rows, int V, const int64
     return cross_entropy(logits, ld, rows, V, CLLP(targets), ignore_index, row_loss, scratch, loss, write_grad, ST(stream));
 }
 int esb_argmax_rows(const void* logits, int64_t ld, int64_t rows, int V, int64_t* out_idx, float* scores,
-                    int64_t scores_ld, int suppress_col, void* stream) {
-    return argmax_rows(logits, ld, rows, V, LLP(out_idx), scores, scores_ld, suppress_col, ST(stream));
+                    int64_t scores_ld, int suppress_col, const int32_t* step_ptr, int step_off, int64_t scores_step_stride,
+                    void* stream) {
+    return argmax_rows(logits, ld, rows, V, LLP(out_idx), scores, scores_ld, suppress_col, step_ptr, step_off, scores_step_stride,
+                       ST(stream));
 }
 int esb_greedy_update(const int64_t* next, int64_t* tokens_out, int32_t* unfinished, int64_t* sequences, int64_t seq_ld,
-                      int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, void* stream) {
-    return greedy_update(CLLP(next), LLP(tokens_out), unfinished, LLP(sequences), seq_ld, cur_len, mask, mask_ld, eos, pad, B, ST(stream));
+                      int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, int32_t* pos_ptr, void* stream) {
+    return greedy_update(CLLP(next), LLP(tokens_out), unfinished, LLP(sequences), seq_ld, cur_len, mask, mask_ld, eos, pad, B, pos_ptr,
+                         ST(stream));
 }
 int esb_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr, float beta1, float beta2,
               float eps, float weight_decay, int step, float grad_scale, void* stream) {

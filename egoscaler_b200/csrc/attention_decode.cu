@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const __nv_bfl
     __shared__ float s_m[DEC_GROUPS], s_l[DEC_GROUPS];
     const int h = blockIdx.x, b = blockIdx.y;
     const int grp = threadIdx.x >> 3, sub = threadIdx.x & 7;
-    const int Lk = len_ptr ? *len_ptr : len_static;
+    const int Lk = len_static + (len_ptr ? *len_ptr : 0);
 
     float qv[EPL];
     {

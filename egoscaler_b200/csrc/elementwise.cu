@@ -25,11 +25,12 @@ static inline int ew_grid(long long items, int block) {
 // kcache/vcache [B, cache_len, kv_heads*hd] at position pos0 + l.
 __global__ void __launch_bounds__(256) rope_kernel(__nv_bfloat16* __restrict__ buf, long long ld, int L, int n_heads, int hd,
                                                    const __nv_bfloat16* __restrict__ cos_tab, const __nv_bfloat16* __restrict__ sin_tab,
-                                                   int pos0, float sign, long long rows,
+                                                   int pos0, const int* __restrict__ pos_ptr, float sign, long long rows,
                                                    __nv_bfloat16* __restrict__ kcache, __nv_bfloat16* __restrict__ vcache,
                                                    int kv_head0, int kv_heads, long long v_col0, int cache_len) {
     const int half = hd >> 1;
     const int vec_per_head = half >> 3;
+    if (pos_ptr) pos0 += *pos_ptr;                 // device-side position (CUDA-graph replay of the decode step)
     const long long total = rows * n_heads * vec_per_head;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
     for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += stride) {
@@ -78,13 +79,13 @@ __global__ void __launch_bounds__(256) rope_kernel(__nv_bfloat16* __restrict__ b
 
 int rope(void* buf, long long ld, long long rows, int L, int n_heads, int hd, const void* cos_tab, const void* sin_tab,
          int pos0, int inverse, void* kcache, void* vcache, int kv_head0, int kv_heads, long long v_col0, int cache_len,
-         cudaStream_t s) {
+         const int* pos_ptr, cudaStream_t s) {
     if (rows <= 0) return ESB_OK;
     if ((hd & 15) || (ld & 7)) { set_last_error("rope: head_dim must be a multiple of 16 and ld of 8"); return ESB_ERR_INVALID_ARG; }
     const long long total = rows * n_heads * (hd / 16);
     rope_kernel<<<ew_grid(total, 256), 256, 0, s>>>(static_cast<__nv_bfloat16*>(buf), ld, L, n_heads, hd,
                                                     static_cast<const __nv_bfloat16*>(cos_tab), static_cast<const __nv_bfloat16*>(sin_tab),
-                                                    pos0, inverse ? -1.0f : 1.0f, rows, static_cast<__nv_bfloat16*>(kcache),
+                                                    pos0, pos_ptr, inverse ? -1.0f : 1.0f, rows, static_cast<__nv_bfloat16*>(kcache),
                                                     static_cast<__nv_bfloat16*>(vcache), kv_head0, kv_heads, v_col0, cache_len);
     return check_launch("rope");
 }

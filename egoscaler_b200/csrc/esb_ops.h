@@ -26,7 +26,7 @@ int layernorm_fwd(const void* x, const void* add, long long add_period, const fl
 // elementwise.cu
 int rope(void* buf, long long ld, long long rows, int L, int n_heads, int hd, const void* cos_tab, const void* sin_tab,
          int pos0, int inverse, void* kcache, void* vcache, int kv_head0, int kv_heads, long long v_col0, int cache_len,
-         cudaStream_t s);
+         const int* pos_ptr, cudaStream_t s);
 int silu_mul_fwd(const void* gu, void* act, long long rows, int f, cudaStream_t s);
 int silu_mul_bwd(const void* gu, const void* dact, void* dgu, long long rows, int f, cudaStream_t s);
 int gelu(const void* z, const void* dy, void* y, long long n, int backward, cudaStream_t s);
@@ -48,9 +48,9 @@ int group_maxpool(const void* f, void* out, long long groups, int n, int C, int 
 int cross_entropy(void* logits, long long ld, long long rows, int V, const long long* targets, long long ignore_index,
                   float* row_loss, float* scratch_inv_count, float* loss, int write_grad, cudaStream_t s);
 int argmax_rows(const void* logits, long long ld, long long rows, int V, long long* out_idx, float* scores, long long scores_ld,
-                int suppress_col, cudaStream_t s);
+                int suppress_col, const int* step_ptr, int step_off, long long scores_step_stride, cudaStream_t s);
 int greedy_update(const long long* next, long long* tokens_out, int* unfinished, long long* sequences, long long seq_ld,
-                  int cur_len, uint8_t* mask, long long mask_ld, long long eos, long long pad, int B, cudaStream_t s);
+                  int cur_len, uint8_t* mask, long long mask_ld, long long eos, long long pad, int B, int* pos_ptr, cudaStream_t s);
 int adamw(float* p, const float* g, float* m, float* v, void* p_bf16, long long n, float lr, float beta1, float beta2, float eps,
           float wd, int step, float grad_scale, cudaStream_t s);
 int cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t s);

@@ -100,11 +100,13 @@ int cross_entropy(void* logits, long long ld, long long rows, int V, const long 
 // optional suppressed column (set to -inf before the argmax, e.g. EOS in the throughput benchmark).
 __global__ void __launch_bounds__(256) argmax_rows_kernel(const __nv_bfloat16* __restrict__ logits, long long ld, int V,
                                                           long long* __restrict__ out_idx, float* __restrict__ scores,
-                                                          long long scores_ld, int suppress_col) {
+                                                          long long scores_ld, int suppress_col, const int* __restrict__ step_ptr,
+                                                          int step_off, long long scores_step_stride) {
     __shared__ float s_val[8];
     __shared__ int s_idx[8];
     const long long row = blockIdx.x;
     const __nv_bfloat16* lp = logits + row * ld;
+    if (scores && step_ptr) scores += (static_cast<long long>(*step_ptr) + step_off) * scores_step_stride;
     float best = -INFINITY;
     int bi = 0x7fffffff;
     for (int i = threadIdx.x; i < V; i += blockDim.x) {
@@ -128,9 +130,10 @@ __global__ void __launch_bounds__(256) argmax_rows_kernel(const __nv_bfloat16* _
     }
 }
 int argmax_rows(const void* logits, long long ld, long long rows, int V, long long* out_idx, float* scores, long long scores_ld,
-                int suppress_col, cudaStream_t s) {
+                int suppress_col, const int* step_ptr, int step_off, long long scores_step_stride, cudaStream_t s) {
     if (rows <= 0) return ESB_OK;
-    argmax_rows_kernel<<<static_cast<unsigned>(rows), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(logits), ld, V, out_idx, scores, scores_ld, suppress_col);
+    argmax_rows_kernel<<<static_cast<unsigned>(rows), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(logits), ld, V, out_idx, scores, scores_ld, suppress_col,
+                                                                   step_ptr, step_off, scores_step_stride);
     return check_launch("argmax_rows");
 }
 
@@ -138,20 +141,25 @@ int argmax_rows(const void* logits, long long ld, long long rows, int V, long lo
 // appends the token to `sequences[:, cur_len]` and sets attention mask 1.
 __global__ void greedy_update_kernel(const long long* __restrict__ next, long long* __restrict__ tokens_out, int* __restrict__ unfinished,
                                      long long* __restrict__ sequences, long long seq_ld, int cur_len,
-                                     uint8_t* __restrict__ mask, long long mask_ld, long long eos, long long pad, int B) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    const int uf = unfinished[b];
-    const long long t = uf ? next[b] : pad;
-    tokens_out[b] = t;
-    sequences[b * seq_ld + cur_len] = t;
-    if (mask) mask[b * mask_ld + cur_len] = 1;
-    unfinished[b] = uf && (t != eos);
+                                     uint8_t* __restrict__ mask, long long mask_ld, long long eos, long long pad, int B,
+                                     int* __restrict__ pos_ptr) {
+    // single CTA: with pos_ptr the write position is cur_len + *pos_ptr and the counter is advanced afterwards
+    if (pos_ptr) cur_len += *pos_ptr;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        const int uf = unfinished[b];
+        const long long t = uf ? next[b] : pad;
+        tokens_out[b] = t;
+        sequences[b * seq_ld + cur_len] = t;
+        if (mask) mask[b * mask_ld + cur_len] = 1;
+        unfinished[b] = uf && (t != eos);
+    }
+    __syncthreads();
+    if (pos_ptr && threadIdx.x == 0) *pos_ptr += 1;
 }
 int greedy_update(const long long* next, long long* tokens_out, int* unfinished, long long* sequences, long long seq_ld,
-                  int cur_len, uint8_t* mask, long long mask_ld, long long eos, long long pad, int B, cudaStream_t s) {
+                  int cur_len, uint8_t* mask, long long mask_ld, long long eos, long long pad, int B, int* pos_ptr, cudaStream_t s) {
     if (B <= 0) return ESB_OK;
-    greedy_update_kernel<<<(B + 127) / 128, 128, 0, s>>>(next, tokens_out, unfinished, sequences, seq_ld, cur_len, mask, mask_ld, eos, pad, B);
+    greedy_update_kernel<<<1, 256, 0, s>>>(next, tokens_out, unfinished, sequences, seq_ld, cur_len, mask, mask_ld, eos, pad, B, pos_ptr);
     return check_launch("greedy_update");
 }
 

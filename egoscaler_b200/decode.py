@@ -24,7 +24,7 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
              point_clouds: Optional[torch.Tensor] = None, max_length: int = 20, temperature: float = 1.0, top_k: int = 50,
              top_p: float = 0.95, repetition_penalty: float = 1.0, do_sample: bool = True, num_return_sequences: int = 1,
              fps_start: Optional[torch.Tensor] = None, suppress_eos: bool = False, output_scores: bool = True,
-             eos_check_every: int = 16, **kwargs) -> GenerateOutput:
+             eos_check_every: int = 16, use_cuda_graph: bool = True, **kwargs) -> GenerateOutput:
     if do_sample:
         raise NotImplementedError("sampling decode (top-k/top-p/multinomial, SURVEY 8f N1) is not built; pass do_sample=False")
     if num_return_sequences != 1 or repetition_penalty != 1.0:
@@ -48,17 +48,35 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
     last = torch.empty(B, 1, d, device=dev, dtype=torch.bfloat16)
     sup = cfg.eos_token_id if suppress_eos else -1
 
+    # Device-side cache-length counter: lets ONE captured CUDA graph of the single-token step (32 layers x 9 kernels +
+    # head + argmax + bookkeeping, ~300 launches) be replayed for every generated token, so the step is bound by HBM
+    # and not by launch latency.  Step 0 (prefill incl. the point encoder) and step 1 run eagerly.
+    pos_dev = torch.full((1,), P, device=dev, dtype=torch.int32)
+
+    def token_step():
+        hl_, _ = model.hidden_states(tok, mask, None, None, cache, pos_dev=pos_dev)
+        lg = model.logits_from_hidden(hl_)
+        ops.argmax_rows(lg, V, scores=scores, suppress_col=sup, out=nxt, step_ptr=pos_dev, step_off=1 - P,
+                        scores_step_stride=B * V)
+        ops.greedy_update(nxt, tok.view(B), unfinished, seq, 1, mask, cfg.eos_token_id, cfg.pad_token_id, pos_ptr=pos_dev)
+
+    graph = None
     steps_done = 0
     for s in range(T):
         if s == 0:
             h, _ = model.hidden_states(input_ids, mask[:, :P], point_clouds, fps_start, cache)
             ops.copy_rows(h.view(B, P, d)[:, P - 1:P, :], last)
-            hl = last.view(B, d)
+            logits = model.logits_from_hidden(last.view(B, d))
+            ops.argmax_rows(logits, V, scores=None if scores is None else scores[0], suppress_col=sup, out=nxt)
+            ops.greedy_update(nxt, tok.view(B), unfinished, seq, P, mask, cfg.eos_token_id, cfg.pad_token_id)
+        elif s == 1 or not use_cuda_graph:
+            token_step()
         else:
-            hl, _ = model.hidden_states(tok, mask, None, None, cache)
-        logits = model.logits_from_hidden(hl)
-        ops.argmax_rows(logits, V, scores=None if scores is None else scores[s], suppress_col=sup, out=nxt)
-        ops.greedy_update(nxt, tok.view(B), unfinished, seq, P + s, mask, cfg.eos_token_id, cfg.pad_token_id)
+            if graph is None:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    token_step()
+            graph.replay()
         steps_done = s + 1
         if not suppress_eos and eos_check_every > 0 and (s + 1) % eos_check_every == 0:
             if int(unfinished.max().item()) == 0:        # the reference checks every step (one sync per token)

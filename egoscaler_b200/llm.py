@@ -92,12 +92,15 @@ class LlamaTrunk:
 
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], pos0: int = 0,
-                cache: Optional[KVCache] = None, saved: Optional[List[LayerSaved]] = None) -> torch.Tensor:
+                cache: Optional[KVCache] = None, saved: Optional[List[LayerSaved]] = None,
+                pos_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
         """x [B*L, d] bf16 -> hidden [B*L, d] (before the final norm).  kmask uint8 [B, >= pos0+L] or None.
         With ``cache``: K/V of these L tokens are written at pos0.. and attention runs over cache[:pos0+L]."""
         c = self.cfg
         d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
-        decode = cache is not None and L == 1 and pos0 > 0
+        decode = cache is not None and L == 1 and (pos0 > 0 or pos_dev is not None)
+        if pos_dev is not None:          # graph-replayed decode step: the position lives in a device counter
+            assert decode and pos0 == 0
         for li, w in enumerate(self.layers):
             if saved is not None:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
@@ -106,12 +109,12 @@ class LlamaTrunk:
             qkv = ops.gemm(xn, w.wqkv)                                            # [T, 3d]
             if cache is not None:
                 ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
-                          kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len)
+                          kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len, pos_ptr=pos_dev)
             else:
                 ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0)
             lse = None
             if decode:
-                o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_static=pos0 + 1)
+                o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_ptr=pos_dev, len_static=pos0 + 1)
             else:
                 q4 = qkv.view(B, L, 3, H, hd)
                 if cache is not None:

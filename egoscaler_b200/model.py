@@ -188,11 +188,11 @@ class TrajPointLLMForCausalLM(ParamTree):
         return attention_mask.to(dev).to(torch.uint8).contiguous()
 
     def hidden_states(self, input_ids, attention_mask=None, point_clouds=None, fps_start=None, cache: Optional[KVCache] = None,
-                      saved=None, proj_saved=None, splice_pos=None):
+                      saved=None, proj_saved=None, splice_pos=None, pos_dev=None):
         """Everything up to (not including) the final norm.  Returns (hidden [B*L, d], splice_pos)."""
         input_ids = input_ids.to(self.dev)
         B, L = input_ids.shape
-        pos0 = cache.length if cache is not None else 0
+        pos0 = cache.length if (cache is not None and pos_dev is None) else 0
         feats = None
         if (L != 1 or self.training) and point_clouds is not None:       # pointllm.py:112
             if splice_pos is None:                                       # host-side checks first: the (async)
@@ -200,9 +200,9 @@ class TrajPointLLMForCausalLM(ParamTree):
             feats = self.point_features(point_clouds, fps_start, proj_saved)
         x = ops.embed_splice(input_ids, self.model.embed_tokens.weight.detach(), feats, splice_pos if feats is not None else None,
                              self.point_backbone_config["point_token_len"])
-        h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved)
+        h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved, pos_dev)
         if cache is not None:
-            cache.length = pos0 + L
+            cache.length = cache.length + L
         return h, splice_pos
 
     def logits_from_hidden(self, h: torch.Tensor) -> torch.Tensor:

@@ -152,11 +152,11 @@ def layernorm(x, gamma, beta, eps: float = 1e-5, add=None, sum_out=None):
 
 # ------------------------------------------------------------------------------------------------ element-wise
 def rope_(buf: torch.Tensor, L: int, n_heads: int, hd: int, cos_tab, sin_tab, pos0: int = 0, inverse: bool = False,
-          kcache=None, vcache=None, kv_head0: int = 0, kv_heads: int = 0, v_col0: int = 0, cache_len: int = 0):
+          kcache=None, vcache=None, kv_head0: int = 0, kv_heads: int = 0, v_col0: int = 0, cache_len: int = 0, pos_ptr=None):
     _chk(buf, torch.bfloat16, "rope.buf")
     assert buf.dim() == 2 and buf.stride(1) == 1
     _l.call("esb_rope", buf.data_ptr(), buf.stride(0), buf.shape[0], L, n_heads, hd, cos_tab.data_ptr(), sin_tab.data_ptr(),
-            pos0, 1 if inverse else 0, _p(kcache), _p(vcache), kv_head0, kv_heads, v_col0, cache_len, _stream())
+            pos0, 1 if inverse else 0, _p(kcache), _p(vcache), kv_head0, kv_heads, v_col0, cache_len, _p(pos_ptr), _stream())
     return buf
 
 
@@ -276,20 +276,20 @@ def cross_entropy(logits: torch.Tensor, V: int, targets: torch.Tensor, ignore_in
 
 
 def argmax_rows(logits: torch.Tensor, V: int, scores: Optional[torch.Tensor] = None, suppress_col: int = -1,
-                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, step_ptr=None, step_off: int = 0, scores_step_stride: int = 0) -> torch.Tensor:
     _chk(logits, torch.bfloat16, "argmax_rows.logits")
     rows = logits.shape[0]
     if out is None:
         out = torch.empty(rows, device=logits.device, dtype=torch.int64)
     _l.call("esb_argmax_rows", logits.data_ptr(), logits.stride(0), rows, V, out.data_ptr(), _p(scores),
-            0 if scores is None else scores.stride(0), suppress_col, _stream())
+            0 if scores is None else scores.stride(-2), suppress_col, _p(step_ptr), step_off, scores_step_stride, _stream())
     return out
 
 
-def greedy_update(nxt, tokens_out, unfinished, sequences, cur_len: int, mask, eos: int, pad: int):
+def greedy_update(nxt, tokens_out, unfinished, sequences, cur_len: int, mask, eos: int, pad: int, pos_ptr=None):
     B = nxt.shape[0]
     _l.call("esb_greedy_update", nxt.data_ptr(), tokens_out.data_ptr(), unfinished.data_ptr(), sequences.data_ptr(),
-            sequences.stride(0), cur_len, _p(mask), 0 if mask is None else mask.stride(0), eos, pad, B, _stream())
+            sequences.stride(0), cur_len, _p(mask), 0 if mask is None else mask.stride(0), eos, pad, B, _p(pos_ptr), _stream())
 
 
 def adamw_(p, g, m, v, p_bf16, lr, beta1, beta2, eps, wd, step: int, grad_scale: float = 1.0):

@@ -94,10 +94,12 @@ int esb_layernorm_fwd(const void* x, const void* add, int64_t add_period, const 
  * buf [rows, ld] (q and k heads of the packed qkv projection); position of row r is pos0 + r % L; cos/sin tables
  * [max_pos, hd/2] bf16 (LlamaRotaryEmbedding, :117-135).  inverse=1 applies the transposed rotation (backward).
  * When kcache != NULL the rotated K heads [kv_head0, kv_head0+kv_heads) and the V heads at column v_col0 are also
- * written to kcache/vcache [B, cache_len, kv_heads*hd] at position pos0 + r % L (DynamicCache.update, :269-270). */
+ * written to kcache/vcache [B, cache_len, kv_heads*hd] at position pos0 + r % L (DynamicCache.update, :269-270).
+ * pos_ptr (device, optional): *pos_ptr is added to pos0 at run time, so a captured CUDA graph of the decode step can
+ * be replayed for every token. */
 int esb_rope(void* buf, int64_t ld, int64_t rows, int L, int n_heads, int hd, const void* cos_tab, const void* sin_tab,
              int pos0, int inverse, void* kcache, void* vcache, int kv_head0, int kv_heads, int64_t v_col0, int cache_len,
-             void* stream);
+             const int32_t* pos_ptr, void* stream);
 /* HF LlamaMLP act_fn(gate_proj(x)) * up_proj(x) (modeling_llama.py:171-184) on gu [rows, 2f] = (gate | up). */
 int esb_silu_mul_fwd(const void* gu, void* act, int64_t rows, int f, void* stream);
 int esb_silu_mul_bwd(const void* gu, const void* dact, void* dgu, int64_t rows, int f, void* stream);
@@ -135,13 +137,17 @@ int esb_group_maxpool(const void* f, void* out, int64_t groups, int n, int C, in
 int esb_cross_entropy(void* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int64_t ignore_index,
                       float* row_loss, float* scratch, float* loss, int write_grad, void* stream);
 /* Greedy step (HF generation/utils.py:2762-2806 via model_arch.py:94-108): first-max argmax per row of bf16 logits,
- * optional fp32 `scores` copy, optional suppressed column (-1: none). */
+ * optional fp32 `scores` copy, optional suppressed column (-1: none).  With step_ptr (device) the scores block written
+ * is scores + (*step_ptr + step_off) * scores_step_stride (one [rows, V] block per generated token). */
 int esb_argmax_rows(const void* logits, int64_t ld, int64_t rows, int V, int64_t* out_idx, float* scores,
-                    int64_t scores_ld, int suppress_col, void* stream);
+                    int64_t scores_ld, int suppress_col, const int32_t* step_ptr, int step_off, int64_t scores_step_stride,
+                    void* stream);
 /* Finished-row bookkeeping of the same loop: finished rows emit pad, EOS finishes a row, token appended to
- * sequences[:, cur_len], attention mask grown by one. */
+ * sequences[:, cur_len], attention mask grown by one.  With pos_ptr (device) the column is cur_len + *pos_ptr and
+ * *pos_ptr is incremented afterwards (the cache-length counter of the graph-replayed decode step). */
 int esb_greedy_update(const int64_t* next, int64_t* tokens_out, int32_t* unfinished, int64_t* sequences, int64_t seq_ld,
-                      int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, void* stream);
+                      int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, int32_t* pos_ptr,
+                      void* stream);
 /* torch.optim.AdamW step (train.py:107-113,184) on fp32 master weights; refreshes the bf16 model copy. */
 int esb_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr, float beta1, float beta2,
               float eps, float weight_decay, int step, float grad_scale, void* stream);
@@ -163,7 +169,7 @@ int esb_attn_bwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64
                  int64_t dk_rs, void* dv, int64_t dv_bs, int64_t dv_rs, const uint8_t* kmask, int64_t kmask_ld, int B, int H,
                  int Lq, int Lk, int hd, int causal, int q_pos0, float scale, void* stream);
 /* One query token per sequence against the KV cache (the per-token step of generate, pointllm.py:255-275).
- * Context length read from *len_ptr when not NULL (CUDA-graph friendly) else len_static. */
+ * Context length = len_static + (*len_ptr when not NULL), so a captured graph follows a device-side counter. */
 int esb_attn_decode(const void* q, int64_t q_bs, const void* k, const void* v, int64_t kv_bs, int64_t kv_rs, void* o,
                     int64_t o_bs, const uint8_t* kmask, int64_t kmask_ld, const int32_t* len_ptr, int len_static, int B,
                     int H, int hd, float scale, void* stream);

@@ -145,6 +145,8 @@ def test_attention_prefill_with_cache_and_decode(hd, H):
     close(od, ref1.view(B, d), 1.5e-2)
     ln = torch.tensor([P], device="cuda", dtype=torch.int32)
     assert torch.equal(ops.attention_decode(q1, kc, vc, H, hd, kmask=kmask, len_ptr=ln), od)
+    ln2 = torch.tensor([P - 5], device="cuda", dtype=torch.int32)        # context = len_static + *len_ptr
+    assert torch.equal(ops.attention_decode(q1, kc, vc, H, hd, kmask=kmask, len_ptr=ln2, len_static=5), od)
 
 
 def test_cross_entropy_and_argmax():
