@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=8, help="per-GPU batch (train.py --bs 8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-decode", action="store_true", help="skip the batched greedy-decode measurement")
+    ap.add_argument("--decode-only", action="store_true", help="profiling aid: build the model and run only the decode measurement")
     ap.add_argument("--decode-batch", type=int, default=32, help="sequences per GPU (BASELINE configs[3]: 256 / 8 GPUs)")
     ap.add_argument("--cpu-budget-s", type=float, default=200.0)
     return ap.parse_args()
@@ -101,6 +102,14 @@ class ClockSampler(threading.Thread):
         self.join(timeout=2)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def gemm_traffic():
+    """dram read+write bytes of the largest GEMM launch from the committed `ncu --set full` capture (profiles/)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "gemm_traffic.json")))
+    except Exception:
+        return None
 
 
 class GemmTimer:
@@ -177,6 +186,12 @@ def run_b200(args):
     cfg = TrajVLMConfig.full() if args.config == "full" else TrajVLMConfig.tiny()
     B = args.batch
     model = build_model(torch, cfg, dev)
+    if args.decode_only:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        d = decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks)
+        if rank == 0:
+            print(json.dumps(d), flush=True)
+        return
     model.train()
     tr = Trainer(model, lr=2e-5, world_size=world)
     nb = 4
@@ -262,7 +277,7 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel", "achieved": round(achieved_tf, 1), "peak": peak_tf,
-                     "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": None, "peak_source": peak_src,
+                     "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": gemm_traffic(), "peak_source": peak_src,
                      "launches_per_step": timer.n // args.steps, "gemm_ms_per_step": round(gemm_ms / args.steps, 3),
                      "gemm_share_of_step": round(gemm_ms / ms_res, 4),
                      "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
