@@ -201,7 +201,9 @@ int attn_fwd(const void* q, long long q_bs, long long q_rs, const void* k, long 
     p.q_bs = q_bs; p.q_rs = q_rs; p.k_bs = k_bs; p.k_rs = k_rs; p.v_bs = v_bs; p.v_rs = v_rs; p.o_bs = o_bs; p.o_rs = o_rs;
     p.kmask_ld = kmask_ld; p.B = B; p.H = H; p.Lq = Lq; p.Lk = Lk; p.causal = causal; p.q_pos0 = q_pos0; p.scale = scale;
     if (hd == 64) return launch_attn_fwd<64>(p, s);
-    if (hd == 128) return launch_attn_fwd<128>(p, s);
+    if (hd == 128)      // tcgen05 / TMEM / TMA kernel (attention_fwd_tc.cu); the mma.sync kernel below serves head_dim 64 only
+        return attn_fwd_tc128(q, q_bs, q_rs, k, k_bs, k_rs, v, v_bs, v_rs, o, o_bs, o_rs, lse, kmask, kmask_ld, B, H, Lq, Lk, causal,
+                              q_pos0, scale, s);
     set_last_error("attn_fwd: head_dim %d unsupported (64, 128)", hd);
     return ESB_ERR_UNSUPPORTED;
 }

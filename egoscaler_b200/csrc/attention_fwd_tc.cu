@@ -1,0 +1,346 @@
+// Fused attention forward on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), head_dim 128.
+//
+// Reference semantics: HF LlamaAttention -> sdpa_attention_forward (transformers integrations/sdpa_attention.py:40-98,
+// modeling_llama.py:253-290) reached from pointllm/model/pointllm.py:173-178: softmax(Q K^T * hd^-0.5 + mask) V with
+// mask = causal AND key-padding, fp32 softmax statistics, probabilities rounded to bf16 before P@V.
+//
+// One CTA = one (batch, head, 128-query tile); 128 threads, thread t owns query row t (= TMEM lane t), so the softmax
+// needs no shuffles.  Per 64-key block j:
+//     S_j = Q K_j^T        tcgen05.mma 128x64x16 (x8), both operands K-major from TMA-written 128B-swizzled smem,
+//                          fp32 result in TMEM (two S buffers, so S_{j+1} is computed while block j is in softmax)
+//     P_j = exp2(S_j*c-m)  tcgen05.ld -> registers -> bf16 -> smem in the K-major SW128 operand layout
+//     O  += P_j V_j        tcgen05.mma 128x128x16 (x4), A = P (K-major), B = V_j as stored ([key, hd] = MN-major)
+// O stays in TMEM for the whole tile; it is only rescaled when a row maximum grows by more than 2^8 (lazy rescale),
+// which keeps exp2 arguments bounded and makes the correction pass rare.  Two CTAs are co-resident per SM (112 KB smem,
+// 256 TMEM columns each), so one CTA's softmax overlaps the other's MMAs.
+#include "common.cuh"
+#include "esb_internal.h"
+#include "esb_ops.h"
+
+namespace esb {
+
+namespace {
+
+constexpr int FA_BM = 128;          // queries per CTA
+constexpr int FA_BN = 64;           // keys per block
+constexpr int FA_HD = 128;
+constexpr int FA_THREADS = 128;
+constexpr int Q_BYTES = FA_BM * FA_HD * 2;        // 32 KB : 2 chunks [128 rows x 64 hd]
+constexpr int K_BYTES = FA_BN * FA_HD * 2;        // 16 KB : 2 chunks [64 keys x 64 hd]
+constexpr int V_BYTES = FA_BN * FA_HD * 2;        // 16 KB : 2 chunks [64 keys x 64 hd] (chunk = hd half)
+constexpr int P_BYTES = FA_BM * FA_BN * 2;        // 16 KB : [128 rows x 64 keys]
+// 2 CTAs/SM: 2 * (FA_SMEM + 1 KB driver reserve) must stay <= 228 KB -> exactly 1 KB for barriers (128 B) + alignment slack
+// (the dynamic smem base is at least 128-byte aligned, so 896 B of slack always reaches the next 1 KB boundary).
+constexpr int FA_SMEM = Q_BYTES + 2 * K_BYTES + 2 * V_BYTES + P_BYTES + 128 + 896;
+constexpr uint32_t TMEM_COLS = 256;               // S0 [0,64) S1 [64,128) O [128,256)
+constexpr float RESCALE_THRESHOLD = 8.0f;         // log2 units
+
+struct FaParams {
+    __nv_bfloat16* o;
+    float* lse;
+    const uint8_t* kmask;
+    long long o_bs, o_rs, kmask_ld;
+    int H, Lq, Lk, causal, q_pos0;
+    float scale_log2;        // scale * log2(e)
+};
+
+// 32 lanes x 32 columns store (inverse of tmem_ld_32x32)
+ESB_DEVICE void tmem_st_32x32(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+ESB_DEVICE void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// MN-major operand, 128-byte swizzle: 64 contiguous MN elements (128 B) per row, rows = K index 128 B apart,
+// 8-row groups SBO = 1024 B apart, next 64 MN elements LBO bytes away (canonical ((8,n),(8,k)):((1,LBO),(8,SBO))).
+ESB_DEVICE uint64_t umma_desc_mnmajor_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+ESB_DEVICE constexpr uint32_t umma_idesc_bf16_bmn(uint32_t M, uint32_t N) {      // B operand MN-major
+    return umma_idesc_bf16(M, N) | (1u << 16);
+}
+
+ESB_DEVICE void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+__global__ void __launch_bounds__(FA_THREADS, 2)
+attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
+                   const __grid_constant__ CUtensorMap tv, const FaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + Q_BYTES;                 // 2 stages
+    uint8_t* sV = sK + 2 * K_BYTES;             // 2 stages
+    uint8_t* sP = sV + 2 * V_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + P_BYTES);
+    uint64_t* bar_q = bars;                     // Q landed
+    uint64_t* bar_k = bars + 1;                 // [2] K stage landed
+    uint64_t* bar_v = bars + 3;                 // [2] V stage landed
+    uint64_t* bar_s = bars + 5;                 // [2] S buffer computed
+    uint64_t* bar_o = bars + 7;                 // P V of the previous block retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    uint32_t* s_maskbits = tmem_slot + 2;       // [2] key-validity bits of the current block
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int qt = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);   // heavy (late) tiles first
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int m0 = qt * FA_BM;
+
+    int kv_end = p.Lk;
+    if (p.causal) kv_end = min(p.Lk, m0 + FA_BM + p.q_pos0);
+    const int nblk = (kv_end + FA_BN - 1) / FA_BN;
+
+    if (tid == 0) {
+        tma_prefetch_desc(&tq); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
+        mbar_init(bar_q, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&bar_k[i], 1); mbar_init(&bar_v[i], 1); mbar_init(&bar_s[i], 1); }
+        mbar_init(bar_o, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_lane = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+    const uint32_t tmem_o = 128;
+
+    constexpr uint32_t idesc_s = umma_idesc_bf16(FA_BM, FA_BN);
+    constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(FA_BM, FA_HD);
+    const int hcol = h * FA_HD;
+
+    auto load_k = [&](int j) {
+        const int st = j & 1;
+        mbar_arrive_expect_tx(&bar_k[st], K_BYTES);
+        tma_load_3d(sK + st * K_BYTES, &tk, &bar_k[st], hcol, j * FA_BN, b);
+        tma_load_3d(sK + st * K_BYTES + K_BYTES / 2, &tk, &bar_k[st], hcol + 64, j * FA_BN, b);
+    };
+    auto load_v = [&](int j) {
+        const int st = j & 1;
+        mbar_arrive_expect_tx(&bar_v[st], V_BYTES);
+        tma_load_3d(sV + st * V_BYTES, &tv, &bar_v[st], hcol, j * FA_BN, b);
+        tma_load_3d(sV + st * V_BYTES + V_BYTES / 2, &tv, &bar_v[st], hcol + 64, j * FA_BN, b);
+    };
+    auto issue_s = [&](int j) {              // S_j = Q K_j^T  -> TMEM S buffer j&1
+        const int st = j & 1;
+        mbar_wait(&bar_k[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t aq = smem_u32(sQ), ak = smem_u32(sK + st * K_BYTES);
+#pragma unroll
+        for (int ks = 0; ks < FA_HD / 16; ++ks) {
+            const uint64_t da = umma_desc_kmajor_sw128(aq + (ks >> 2) * (Q_BYTES / 2)) + static_cast<uint64_t>(2 * (ks & 3));
+            const uint64_t db = umma_desc_kmajor_sw128(ak + (ks >> 2) * (K_BYTES / 2)) + static_cast<uint64_t>(2 * (ks & 3));
+            umma_bf16_ss(tmem_base + static_cast<uint32_t>(st * FA_BN), da, db, idesc_s, ks != 0 ? 1u : 0u);
+        }
+        umma_commit(&bar_s[st]);
+    };
+
+    if (tid == 0 && nblk > 0) {
+        mbar_arrive_expect_tx(bar_q, Q_BYTES);
+        tma_load_3d(sQ, &tq, bar_q, hcol, m0, b);
+        tma_load_3d(sQ + Q_BYTES / 2, &tq, bar_q, hcol + 64, m0, b);
+        load_k(0);
+        load_v(0);
+        if (nblk > 1) load_k(1);
+        mbar_wait(bar_q, 0);
+        issue_s(0);
+        if (nblk > 1) issue_s(1);
+    }
+
+    const int qrow = m0 + tid;                          // this thread's query row
+    const int qpos = qrow + p.q_pos0;                   // last visible key index (causal)
+    const uint8_t* km = p.kmask ? p.kmask + static_cast<long long>(b) * p.kmask_ld : nullptr;
+    float m_used = -INFINITY, l_run = 0.0f;
+
+    for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        const int kbase = j * FA_BN;
+        // ---- key-validity bits for this block (length + padding mask), one ballot per 32 keys
+        if (warp < 2) {
+            const int key = kbase + warp * 32 + lane;
+            bool ok = key < p.Lk;
+            if (ok && km) ok = km[key] != 0;
+            const uint32_t bits = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) s_maskbits[warp] = bits;
+        }
+        // ---- S_j ready?
+        mbar_wait(&bar_s[st], (j >> 1) & 1);
+        tc_fence_after();
+        if (tid == 0 && j + 2 < nblk) load_k(j + 2);    // K stage st is free once S_j has been computed
+        uint32_t sr[FA_BN];
+        tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(st * FA_BN), sr);
+        tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(st * FA_BN + 32), sr + 32);
+        tmem_ld_wait();
+        __syncthreads();                                 // s_maskbits visible (also orders the S reads of all warps)
+        const uint32_t mb0 = s_maskbits[0], mb1 = s_maskbits[1];
+        // causal limit inside this block: keys kbase .. qpos are visible
+        uint32_t vb0 = mb0, vb1 = mb1;
+        if (p.causal) {
+            const int nvis = qpos - kbase + 1;           // number of visible keys in this block (may be <=0 or >=64)
+            const uint32_t c0 = nvis >= 32 ? 0xffffffffu : (nvis <= 0 ? 0u : ((1u << nvis) - 1u));
+            const uint32_t c1 = nvis >= 64 ? 0xffffffffu : (nvis <= 32 ? 0u : ((1u << (nvis - 32)) - 1u));
+            vb0 &= c0; vb1 &= c1;
+        }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < FA_BN; ++c) {
+            const bool ok = ((c < 32 ? vb0 : vb1) >> (c & 31)) & 1u;
+            const float v = ok ? __uint_as_float(sr[c]) * p.scale_log2 : -INFINITY;
+            sr[c] = __float_as_uint(v);
+            mx = fmaxf(mx, v);
+        }
+        // ---- lazy rescale decision
+        float corr = 1.0f;
+        if (mx > m_used + RESCALE_THRESHOLD || m_used == -INFINITY) {
+            if (mx != -INFINITY) {
+                corr = (m_used == -INFINITY) ? 0.0f : exp2f(m_used - mx);
+                m_used = mx;
+            }
+        }
+        float ls = 0.0f;
+        uint32_t pk[FA_BN / 2];
+#pragma unroll
+        for (int c = 0; c < FA_BN; c += 2) {
+            const float p0 = (m_used == -INFINITY) ? 0.0f : exp2f(__uint_as_float(sr[c]) - m_used);
+            const float p1 = (m_used == -INFINITY) ? 0.0f : exp2f(__uint_as_float(sr[c + 1]) - m_used);
+            ls += p0 + p1;
+            pk[c >> 1] = pack_bf16x2(p0, p1);
+        }
+        l_run = l_run * corr + ls;
+        // ---- previous P V must have retired before P / O / the other V stage are touched
+        if (j > 0) {
+            mbar_wait(bar_o, (j - 1) & 1);
+            tc_fence_after();
+        }
+        if (tid == 0 && j + 1 < nblk) load_v(j + 1);
+        if (j > 0 && __any_sync(0xffffffffu, corr != 1.0f)) {
+#pragma unroll 1
+            for (int c = 0; c < FA_HD / 32; ++c) {
+                uint32_t orr[32];
+                tmem_ld_32x32(tmem_lane + tmem_o + static_cast<uint32_t>(c * 32), orr);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) orr[i] = __float_as_uint(__uint_as_float(orr[i]) * corr);
+                tmem_st_32x32(tmem_lane + tmem_o + static_cast<uint32_t>(c * 32), orr);
+            }
+            tmem_st_wait();
+        }
+        // ---- P -> smem (K-major, 128B swizzle: 16-byte unit u of row r lives at unit u ^ (r & 7))
+        {
+            uint8_t* prow = sP + tid * 128;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint4 val = make_uint4(pk[u * 4 + 0], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+                *reinterpret_cast<uint4*>(prow + ((u ^ (tid & 7)) << 4)) = val;
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc_fence_after();
+            mbar_wait(&bar_v[st], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t ap = smem_u32(sP), av = smem_u32(sV + st * V_BYTES);
+#pragma unroll
+            for (int ks = 0; ks < FA_BN / 16; ++ks) {
+                const uint64_t da = umma_desc_kmajor_sw128(ap) + static_cast<uint64_t>(2 * ks);
+                const uint64_t db = umma_desc_mnmajor_sw128(av + ks * 2048, V_BYTES / 2);
+                umma_bf16_ss(tmem_base + tmem_o, da, db, idesc_o, (j | ks) != 0 ? 1u : 0u);
+            }
+            umma_commit(bar_o);
+            if (j + 2 < nblk) issue_s(j + 2);            // S buffer st was fully read before the barrier above
+        }
+    }
+
+    // ---- epilogue: O / l -> bf16 global, lse
+    if (nblk > 0) {
+        mbar_wait(bar_o, (nblk - 1) & 1);
+        tc_fence_after();
+    }
+    const float inv = l_run > 0.0f ? 1.0f / l_run : 0.0f;
+    __nv_bfloat16* op = p.o + static_cast<long long>(b) * p.o_bs + static_cast<long long>(qrow) * p.o_rs + static_cast<long long>(h) * FA_HD;
+#pragma unroll 1
+    for (int c = 0; c < FA_HD / 32; ++c) {
+        uint32_t orr[32];
+        if (nblk > 0) {
+            tmem_ld_32x32(tmem_lane + tmem_o + static_cast<uint32_t>(c * 32), orr);
+            tmem_ld_wait();
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) orr[i] = 0u;
+        }
+        if (qrow < p.Lq) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                uint4 u;
+                u.x = pack_bf16x2(__uint_as_float(orr[g * 8 + 0]) * inv, __uint_as_float(orr[g * 8 + 1]) * inv);
+                u.y = pack_bf16x2(__uint_as_float(orr[g * 8 + 2]) * inv, __uint_as_float(orr[g * 8 + 3]) * inv);
+                u.z = pack_bf16x2(__uint_as_float(orr[g * 8 + 4]) * inv, __uint_as_float(orr[g * 8 + 5]) * inv);
+                u.w = pack_bf16x2(__uint_as_float(orr[g * 8 + 6]) * inv, __uint_as_float(orr[g * 8 + 7]) * inv);
+                *reinterpret_cast<uint4*>(op + c * 32 + g * 8) = u;
+            }
+        }
+    }
+    if (p.lse && qrow < p.Lq)
+        p.lse[(static_cast<long long>(b) * p.H + h) * p.Lq + qrow] =
+            l_run > 0.0f ? (m_used + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+}  // namespace
+
+// q/k/v element (b, l, h, e) at ptr + b*bs + l*rs + h*128 + e.
+int attn_fwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k, long long k_bs, long long k_rs, const void* v,
+                   long long v_bs, long long v_rs, void* o, long long o_bs, long long o_rs, float* lse, const uint8_t* kmask,
+                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s) {
+    if ((o_rs & 7) || (o_bs & 7) || (reinterpret_cast<uintptr_t>(o) & 15)) {
+        set_last_error("attn_fwd: output must keep 16-byte alignment");
+        return ESB_ERR_INVALID_ARG;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM);
+        if (e != cudaSuccess) { set_last_error("attn_fwd_tc attr: %s", cudaGetErrorString(e)); return ESB_ERR_CUDA; }
+        attr_set = true;
+    }
+    CUtensorMap tq, tk, tv;
+    int rc = make_tma_3d_bf16(&tq, q, static_cast<long long>(H) * FA_HD, Lq, B, q_rs, q_bs, 64, FA_BM);
+    if (rc) return rc;
+    rc = make_tma_3d_bf16(&tk, k, static_cast<long long>(H) * FA_HD, Lk, B, k_rs, k_bs, 64, FA_BN);
+    if (rc) return rc;
+    rc = make_tma_3d_bf16(&tv, v, static_cast<long long>(H) * FA_HD, Lk, B, v_rs, v_bs, 64, FA_BN);
+    if (rc) return rc;
+    FaParams p;
+    p.o = static_cast<__nv_bfloat16*>(o); p.lse = lse; p.kmask = kmask; p.o_bs = o_bs; p.o_rs = o_rs; p.kmask_ld = kmask_ld;
+    p.H = H; p.Lq = Lq; p.Lk = Lk; p.causal = causal; p.q_pos0 = q_pos0; p.scale_log2 = scale * 1.4426950408889634f;
+    dim3 grid((Lq + FA_BM - 1) / FA_BM, H, B);
+    attn_fwd_tc_kernel<<<grid, FA_THREADS, FA_SMEM, s>>>(tq, tk, tv, p);
+    return check_launch("attn_fwd_tc");
+}
+
+}  // namespace esb

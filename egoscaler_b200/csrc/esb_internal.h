@@ -14,6 +14,15 @@ int device_sm_count();
 
 int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
 
+// 3-D bf16 tensor {cols (contiguous), rows, batches} with row / batch strides in elements; box = {box_cols, box_rows, 1},
+// 128-byte swizzle (box_cols * 2 must be 128).
+int make_tma_3d_bf16(CUtensorMap* map, const void* ptr, long long cols, long long rows, long long batches, long long row_stride,
+                     long long batch_stride, int box_cols, int box_rows);
+
+int attn_fwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k, long long k_bs, long long k_rs, const void* v,
+                   long long v_bs, long long v_rs, void* o, long long o_bs, long long o_rs, float* lse, const uint8_t* kmask,
+                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s);
+
 int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* C, long long ldc, int M, int N, int K,
               const float* bias, const void* residual, long long ldr, int act, int out_fp32, int accumulate, float alpha,
               int force_bn, cudaStream_t stream);

@@ -292,6 +292,29 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, long long rows, long lon
     return ESB_OK;
 }
 
+int make_tma_3d_bf16(CUtensorMap* map, const void* ptr, long long cols, long long rows, long long batches, long long row_stride,
+                     long long batch_stride, int box_cols, int box_rows) {
+    std::call_once(g_encode_once, load_encode);
+    if (!g_encode) {
+        set_last_error("cuTensorMapEncodeTiled entry point unavailable");
+        return ESB_ERR_DRIVER;
+    }
+    if (batches <= 1) batch_stride = rows * row_stride;        // any legal stride: the coordinate is always 0
+    cuuint64_t gdim[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(batches < 1 ? 1 : batches)};
+    cuuint64_t gstride[2] = {static_cast<cuuint64_t>(row_stride) * 2, static_cast<cuuint64_t>(batch_stride) * 2};
+    cuuint32_t box[3] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows), 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_last_error("cuTensorMapEncodeTiled(3d) failed (%d) cols=%lld rows=%lld batches=%lld rs=%lld bs=%lld ptr=%p", (int)r, cols,
+                       rows, batches, row_stride, batch_stride, ptr);
+        return ESB_ERR_DRIVER;
+    }
+    return ESB_OK;
+}
+
 template <int BN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
     using S = GemmSmem<BN>;
