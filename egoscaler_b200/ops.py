@@ -379,7 +379,7 @@ def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: t
     B, L, three, H, hd = qkv.shape
     assert three == 3 and qkv.is_contiguous() and o.stride(2) == 1 and dout.stride(2) == 1
     dqkv = torch.empty_like(qkv)
-    dvec = torch.empty(B, H, L, device=qkv.device, dtype=torch.float32)
+    dvec = torch.empty(2 * B * H * ((L + 63) // 64 * 64), device=qkv.device, dtype=torch.float32)   # (lse, D) workspace
     bs, rs = qkv.stride(0), qkv.stride(1)
     es = qkv.element_size()
     d = H * hd

@@ -161,7 +161,8 @@ int esb_attn_fwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64
                  int64_t v_bs, int64_t v_rs, void* o, int64_t o_bs, int64_t o_rs, float* lse, const uint8_t* kmask,
                  int64_t kmask_ld, int B, int H, int Lq, int Lk, int hd, int causal, int q_pos0, float scale, void* stream);
 /* Backward of esb_attn_fwd (autograd of the sdpa attention above; needed through all frozen layers because
- * embed_tokens / point_proj are trainable, model_arch.py:33-51).  dvec [B,H,Lq] fp32 is scratch (rowsum(dO o O)).
+ * embed_tokens / point_proj are trainable, model_arch.py:33-51).  dvec is fp32 scratch of 2*B*H*round_up(Lq,64) floats
+ * (per-row (lse, rowsum(dO o O)) pairs).
  * dq/dk/dv use the same (bs, rs) addressing as q/k/v, so they can be the three slices of one packed [B,L,3,H,hd] buffer. */
 int esb_attn_bwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64_t k_bs, int64_t k_rs, const void* v,
                  int64_t v_bs, int64_t v_rs, const void* o, int64_t o_bs, int64_t o_rs, const void* dout, int64_t do_bs,
