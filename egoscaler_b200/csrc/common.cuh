@@ -105,6 +105,14 @@ ESB_DEVICE void tma_load_2d_hint(void* smem_dst, const CUtensorMap* m, uint64_t*
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer), "l"(policy)
         : "memory");
 }
+// 1-D bulk copy global -> shared (contiguous bytes, multiple of 16, 16-byte aligned both sides).
+ESB_DEVICE void bulk_load_1d_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
 ESB_DEVICE void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c_inner, int c_outer) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                      reinterpret_cast<uint64_t>(m)),

@@ -33,4 +33,11 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
               const float* bias, const void* residual, long long ldr, int act, int out_fp32, int accumulate, float alpha,
               int force_bn, cudaStream_t stream);
 
+long long gemm_skinny_workspace_bytes(int M, int N, int K);
+int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                     const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,
+                     int w_tiled, cudaStream_t stream);
+long long retiled_weight_elems(int N, int K);
+int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cudaStream_t stream);
+
 }  // namespace esb

@@ -1,0 +1,399 @@
+// Skinny bf16 GEMM for the single-token decode step:  C[M,N] = X[M,K] * W[N,K]^T (+ residual),  M <= 64.
+//
+// Reference call sites: the seven Linear layers of HF LlamaDecoderLayer and lm_head when generate() feeds ONE new
+// token per sequence against the KV cache (pointllm/model/pointllm.py:255-275 -> :173-178, :228; callers
+// model_arch.py:94-108).  With M = batch (32 per GPU in BASELINE configs[3]) the contraction is a weight-streaming
+// problem: every byte of W is read once, so the bound is HBM, not the tensor pipe.
+//
+// Design (differs from gemm_tcgen05.cu on purpose):
+//   * operands swapped: the 128-row WEIGHT tile is the UMMA "A" operand (M=128) and the <=64 tokens are the "B"
+//     operand (N = BT), so no tensor-core rows are wasted on padding and a smem stage is 16 KB of weights + 4 KB of X;
+//   * split-K: work unit = (128 weight rows, K/S slice); the host picks S so that units ~ a multiple of the SM count
+//     (N = 4096 has only 32 row tiles - without split-K 116 of 148 SMs would idle and HBM could not be saturated);
+//   * two persistent CTAs per SM walk units round-robin, each with a 4-stage TMA ring that runs ahead across unit
+//     boundaries; two TMEM accumulator stages decouple the MMA from the epilogue;
+//   * deterministic reduction without a second launch: every unit stores its fp32 partial to a workspace, bumps a
+//     per-tile counter, and the LAST arriving unit of a tile sums the S partials in fixed order s = 0..S-1, adds the
+//     residual and writes bf16.  Counters are left at zero, so the kernel is CUDA-graph replay safe.
+//   * W is streamed with an evict-first L2 hint, X (re-read by every CTA) with evict-last.
+#include "common.cuh"
+#include "esb_internal.h"
+
+
+namespace esb {
+
+namespace {
+
+constexpr int SK_ROWS = 128;      // weight rows per tile = UMMA M
+constexpr int SK_BK = 64;         // 64 bf16 = one 128-byte swizzle row
+constexpr int SK_THREADS = 192;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int SK_COUNTER_BYTES = 16384;
+
+struct SkinnyParams {
+    int M, N, K;
+    __nv_bfloat16* C;
+    long long ldc;
+    const __nv_bfloat16* res;
+    long long ldr;
+    int n_tiles, splits, kb_per, num_kb;
+    const uint8_t* w_tiles;
+    int w_tiled;      // 1: W is pre-tiled [n_tiles][num_kb][128][64] (esb_retile_weight_bf16), every stage one contiguous 16 KB
+    float* partial;   // [n_tiles][splits][BT][128] fp32
+    int* counters;    // [n_tiles], zero on entry and on exit
+};
+
+template <int BT, int SK_STAGES>
+struct SkinnySmem {
+    static constexpr int W_BYTES = SK_ROWS * SK_BK * 2;
+    static constexpr int X_BYTES = BT * SK_BK * 2;
+    static constexpr int STAGE_BYTES = W_BYTES + X_BYTES;
+    static constexpr int TOTAL = SK_STAGES * STAGE_BYTES + 1024 + 1024;
+};
+
+ESB_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+template <int BT, int SK_STAGES>
+__global__ void __launch_bounds__(SK_THREADS, SK_STAGES <= 4 ? 2 : 1)
+gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x,
+                           const SkinnyParams p) {
+    using S = SkinnySmem<BT, SK_STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SK_STAGES * S::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + SK_STAGES;
+    uint64_t* tmem_full = bars + 2 * SK_STAGES;
+    uint64_t* tmem_empty = bars + 2 * SK_STAGES + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * SK_STAGES + 4);
+    volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int units = p.n_tiles * p.splits;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_w);
+        tma_prefetch_desc(&tma_x);
+        for (int i = 0; i < SK_STAGES; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 128);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 2 * BT);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===================== TMA producer: runs ahead across unit boundaries
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int tile = u / p.splits, s = u - tile * p.splits;
+                const int kb0 = s * p.kb_per;
+                const int kb1 = min(p.num_kb, kb0 + p.kb_per);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    uint8_t* sw = smem + stage * S::STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+                    if (p.w_tiled)
+                        bulk_load_1d_hint(sw, p.w_tiles + (static_cast<size_t>(tile) * p.num_kb + kb) * S::W_BYTES, S::W_BYTES,
+                                          &full_bar[stage], kEvictFirst);
+                    else
+                        tma_load_2d_hint(sw, &tma_w, &full_bar[stage], kb * SK_BK, tile * SK_ROWS, kEvictFirst);
+                    tma_load_2d_hint(sw + S::W_BYTES, &tma_x, &full_bar[stage], kb * SK_BK, 0, kEvictLast);
+                    if (++stage == SK_STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===================== MMA issuer: D[128 weight rows, BT tokens] += W_tile * X_tile^T
+            constexpr uint32_t idesc = umma_idesc_bf16(SK_ROWS, BT);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int u = blockIdx.x; u < units; u += gridDim.x) {
+                const int tile = u / p.splits, s = u - tile * p.splits;
+                const int kb0 = s * p.kb_per;
+                const int kb1 = min(p.num_kb, kb0 + p.kb_per);
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BT);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sw = smem_u32(smem + stage * S::STAGE_BYTES);
+                    const uint64_t da = umma_desc_kmajor_sw128(sw);
+                    const uint64_t db = umma_desc_kmajor_sw128(sw + S::W_BYTES);
+#pragma unroll
+                    for (int k = 0; k < SK_BK / 16; ++k)
+                        umma_bf16_ss(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k), idesc,
+                                     (kb != kb0 || k != 0) ? 1u : 0u);
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == SK_STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(&tmem_full[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else {
+        // ===================== epilogue (4 warps): thread <-> one weight row n, registers <-> tokens
+        const int q = warp & 3;
+        const int nl = q * 32 + lane;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int tile = u / p.splits, s = u - tile * p.splits;
+            const int n = tile * SK_ROWS + nl;
+            const bool n_ok = n < p.N;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BT);
+            float* part = p.partial + (static_cast<size_t>(tile) * p.splits + s) * (BT * SK_ROWS) + nl;
+#pragma unroll 1
+            for (int c = 0; c < BT / 32; ++c) {
+                if (c * 32 >= p.M) break;
+                uint32_t r[32];
+                tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
+                tmem_ld_wait();
+                if (p.splits == 1) {
+                    if (n_ok) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int m = c * 32 + j;
+                            if (m < p.M) {
+                                float v = __uint_as_float(r[j]);
+                                if (p.res) v += __bfloat162float(p.res[static_cast<long long>(m) * p.ldr + n]);
+                                p.C[static_cast<long long>(m) * p.ldc + n] = __float2bfloat16_rn(v);
+                            }
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (c * 32 + j < p.M) part[(c * 32 + j) * SK_ROWS] = __uint_as_float(r[j]);
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&tmem_empty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1u;
+            if (p.splits > 1) {
+                __threadfence();
+                epi_bar_sync();
+                if (nl == 0) {
+                    const int prev = atomicAdd(&p.counters[tile], 1);
+                    const int last = (prev == p.splits - 1) ? 1 : 0;
+                    if (last) p.counters[tile] = 0;           // nobody else touches this counter again in this launch
+                    *last_flag = last;
+                }
+                epi_bar_sync();
+                if (*last_flag) {
+                    __threadfence();
+                    if (n_ok) {
+                        // fixed summation order s = 0..S-1 per element; 16 tokens x 4 slices of loads in flight
+                        const float* base = p.partial + static_cast<size_t>(tile) * p.splits * (BT * SK_ROWS) + nl;
+#pragma unroll 1
+                        for (int m0 = 0; m0 < p.M; m0 += 16) {
+                            float v[16];
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = 0.0f;
+                            int s2 = 0;
+#pragma unroll 1
+                            for (; s2 + 4 <= p.splits; s2 += 4) {
+                                float t[4][16];
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j)
+                                        t[i][j] = __ldcg(base + (static_cast<size_t>(s2 + i) * BT + m0 + j) * SK_ROWS);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) v[j] += t[i][j];
+                            }
+#pragma unroll 1
+                            for (; s2 < p.splits; ++s2) {
+                                float t[16];
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) t[j] = __ldcg(base + (static_cast<size_t>(s2) * BT + m0 + j) * SK_ROWS);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) v[j] += t[j];
+                            }
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const int m = m0 + j;
+                                if (m < p.M) {
+                                    float o = v[j];
+                                    if (p.res) o += __bfloat162float(p.res[static_cast<long long>(m) * p.ldr + n]);
+                                    p.C[static_cast<long long>(m) * p.ldc + n] = __float2bfloat16_rn(o);
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 2 * BT);
+    }
+}
+
+template <int BT, int SK_STAGES>
+int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyParams& p, int grid, cudaStream_t stream) {
+    using S = SkinnySmem<BT, SK_STAGES>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_skinny_tcgen05_kernel<BT, SK_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        if (e != cudaSuccess) {
+            set_last_error("cudaFuncSetAttribute(gemm_skinny<%d>): %s", BT, cudaGetErrorString(e));
+            return ESB_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    gemm_skinny_tcgen05_kernel<BT, SK_STAGES><<<grid, SK_THREADS, S::TOTAL, stream>>>(tw, tx, p);
+    return check_launch("gemm_skinny_tcgen05");
+}
+
+}  // namespace
+
+namespace {
+// tile (tile, kb) = W[tile*128 .. +128][kb*64 .. +64] (zero beyond N / K), 16 KiB contiguous, stored as the 128-byte-swizzled
+// shared-memory image tcgen05 expects (16-byte chunk c of row r at chunk c ^ (r & 7)), so a 1-D bulk copy stages it.
+__global__ void retile_weight_kernel(const __nv_bfloat16* __restrict__ W, long long ldw, int N, int K, int num_kb,
+                                     long long total_vec, uint4* __restrict__ out) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total_vec;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int c8 = static_cast<int>(i & 7);
+        const int r = static_cast<int>((i >> 3) & 127);
+        const long long blk = i >> 10;
+        const int kb = static_cast<int>(blk % num_kb);
+        const long long tile = blk / num_kb;
+        const long long n = tile * SK_ROWS + r;
+        const int k = kb * SK_BK + c8 * 8;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (n < N && k + 8 <= K) v = __ldg(reinterpret_cast<const uint4*>(W + n * ldw + k));
+        else if (n < N && k < K) {
+            __nv_bfloat16 t[8];
+            for (int j = 0; j < 8; ++j) t[j] = (k + j < K) ? W[n * ldw + k + j] : __float2bfloat16(0.0f);
+            v = *reinterpret_cast<uint4*>(t);
+        }
+        out[(i & ~7ll) | static_cast<long long>(c8 ^ (r & 7))] = v;     // SWIZZLE_128B image of the smem tile
+    }
+}
+}  // namespace
+
+long long retiled_weight_elems(int N, int K) {
+    return static_cast<long long>((N + SK_ROWS - 1) / SK_ROWS) * ((K + SK_BK - 1) / SK_BK) * SK_ROWS * SK_BK;
+}
+
+int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cudaStream_t stream) {
+    if (N <= 0 || K <= 0 || !W || !out || (ldw & 7) || (reinterpret_cast<uintptr_t>(W) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) {
+        set_last_error("retile_weight_bf16: bad arguments (N=%d K=%d ldw=%lld)", N, K, ldw);
+        return ESB_ERR_INVALID_ARG;
+    }
+    const int num_kb = (K + SK_BK - 1) / SK_BK;
+    const long long total_vec = retiled_weight_elems(N, K) / 8;
+    const int grid = device_sm_count() * 8;
+    retile_weight_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(W), ldw, N, K, num_kb, total_vec,
+                                                   reinterpret_cast<uint4*>(out));
+    return check_launch("retile_weight");
+}
+
+long long gemm_skinny_workspace_bytes(int M, int N, int K) {
+    const int bt = M <= 32 ? 32 : 64;
+    const long long n_tiles = (N + SK_ROWS - 1) / SK_ROWS;
+    return SK_COUNTER_BYTES + n_tiles * 16 * bt * SK_ROWS * 4;     // 16 = largest split factor ever chosen
+}
+
+int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                     const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,
+                     int w_tiled, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return ESB_OK;
+    if (M > 64 || K <= 0 || !X || !W || !C) {
+        set_last_error("gemm_skinny_bf16: bad arguments (M=%d (max 64) N=%d K=%d)", M, N, K);
+        return ESB_ERR_INVALID_ARG;
+    }
+    if ((ldx & 7) || (ldw & 7) || (reinterpret_cast<uintptr_t>(X) & 15) || (reinterpret_cast<uintptr_t>(W) & 15)) {
+        set_last_error("gemm_skinny_bf16: X/W must be 16-byte aligned with leading dimensions that are multiples of 8");
+        return ESB_ERR_INVALID_ARG;
+    }
+    const int bt = M <= 32 ? 32 : 64;
+    const int sms = device_sm_count();
+    const int n_tiles = (N + SK_ROWS - 1) / SK_ROWS;
+    const int num_kb = (K + SK_BK - 1) / SK_BK;
+    if (n_tiles * 4 > SK_COUNTER_BYTES) {
+        set_last_error("gemm_skinny_bf16: N=%d too large for the counter block", N);
+        return ESB_ERR_UNSUPPORTED;
+    }
+    const long long part_bytes_per_split = static_cast<long long>(n_tiles) * bt * SK_ROWS * 4;
+    long long max_splits_ws = 1;
+    if (workspace && workspace_bytes > SK_COUNTER_BYTES)
+        max_splits_ws = (workspace_bytes - SK_COUNTER_BYTES) / part_bytes_per_split;
+    // Split factor from a measured model of this kernel on B200 (tools/skinny_bench.py, profiles/r01_skinny_bench.txt):
+    // two CTAs are resident per SM; a CTA streams one 16 KiB k-block in ~0.36 us when few CTAs run and in
+    // ~0.78 us * (resident CTAs / slots) once HBM is the limit; a split costs ~1.5 us + 0.3 us per slice of reduction tail.
+    const int slots = 2 * sms;
+    int best_s = 1;
+    if (force_splits > 0) {
+        best_s = force_splits > 16 ? 16 : force_splits;
+        if (best_s > num_kb) best_s = num_kb;
+        if (best_s > max_splits_ws) best_s = static_cast<int>(max_splits_ws);
+        while (best_s > 1 && static_cast<long long>(best_s - 1) * ((num_kb + best_s - 1) / best_s) >= num_kb) --best_s;
+    } else {
+        double best_cost = -1.0;
+        for (int s = 1; s <= 16 && s <= num_kb; ++s) {
+            const int kb_per = (num_kb + s - 1) / s;
+            if (static_cast<long long>(s - 1) * kb_per >= num_kb) continue;      // an empty slice
+            if (s > 1 && (kb_per < 4 || s > max_splits_ws)) continue;
+            const long long units = static_cast<long long>(n_tiles) * s;
+            const long long rounds = (units + slots - 1) / slots;
+            const double conc = static_cast<double>(units < slots ? units : slots) / slots;
+            const double t_kb = 0.78 * conc > 0.36 ? 0.78 * conc : 0.36;
+            const double cost = rounds * kb_per * t_kb + (s > 1 ? 1.5 + 0.3 * s : 0.0);
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_s = s; }
+        }
+    }
+    const int kb_per = (num_kb + best_s - 1) / best_s;
+    if (static_cast<long long>(best_s - 1) * kb_per >= num_kb || best_s > 16 || (best_s > 1 && best_s > max_splits_ws)) {
+        set_last_error("gemm_skinny_bf16: invalid split factor %d (num_kb=%d, workspace allows %lld)", best_s, num_kb, max_splits_ws);
+        return best_s > max_splits_ws ? ESB_ERR_WORKSPACE : ESB_ERR_INVALID_ARG;
+    }
+    CUtensorMap tw, tx;
+    int rc = w_tiled ? make_tma_2d_bf16(&tw, W, static_cast<long long>(n_tiles) * num_kb * SK_ROWS, SK_BK, SK_BK, SK_ROWS)
+                     : make_tma_2d_bf16(&tw, W, N, K, ldw, SK_ROWS);
+    if (rc) return rc;
+    rc = make_tma_2d_bf16(&tx, X, M, K, ldx, bt);
+    if (rc) return rc;
+    SkinnyParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.C = reinterpret_cast<__nv_bfloat16*>(C); p.ldc = ldc;
+    p.res = reinterpret_cast<const __nv_bfloat16*>(residual); p.ldr = ldr;
+    p.n_tiles = n_tiles; p.splits = best_s; p.kb_per = kb_per; p.num_kb = num_kb; p.w_tiled = w_tiled ? 1 : 0;
+    p.counters = reinterpret_cast<int*>(workspace);
+    p.partial = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_COUNTER_BYTES) : nullptr;
+    p.w_tiles = reinterpret_cast<const uint8_t*>(W);
+    const long long units = static_cast<long long>(n_tiles) * best_s;
+    const int grid = static_cast<int>(units < slots ? units : slots);
+    return bt == 32 ? launch_skinny<32, 4>(tw, tx, p, grid, stream) : launch_skinny<64, 4>(tw, tx, p, grid, stream);
+}
+
+}  // namespace esb

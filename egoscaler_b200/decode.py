@@ -55,7 +55,7 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
 
     def token_step():
         hl_, _ = model.hidden_states(tok, mask, None, None, cache, pos_dev=pos_dev)
-        lg = model.logits_from_hidden(hl_)
+        lg = model.logits_from_hidden(hl_, decode=True)
         ops.argmax_rows(lg, V, scores=scores, suppress_col=sup, out=nxt, step_ptr=pos_dev, step_off=1 - P,
                         scores_step_stride=B * V)
         ops.greedy_update(nxt, tok.view(B), unfinished, seq, 1, mask, cfg.eos_token_id, cfg.pad_token_id, pos_ptr=pos_dev)

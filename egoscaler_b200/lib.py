@@ -29,7 +29,7 @@ def declared_functions(header: str = HEADER_PATH) -> Dict[str, List[str]]:
     src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     out: Dict[str, List[str]] = {}
-    for m in re.finditer(r"(?m)^\s*(int|const char\*)\s+(esb_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.S):
+    for m in re.finditer(r"(?m)^\s*(int64_t|int|const char\*)\s+(esb_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.S):
         ret, name, args = m.group(1), m.group(2), m.group(3)
         types = []
         args = " ".join(args.split())
@@ -64,7 +64,7 @@ class _Lib:
                 continue
             fn = getattr(self._dll, name)          # AttributeError if the .so does not export a declared symbol
             fn.argtypes = [_CTYPE[t] for t in types]
-            fn.restype = ctypes.c_char_p if decl[name + ":ret"][0] == "const char*" else ctypes.c_int
+            fn.restype = {"const char*": ctypes.c_char_p, "int64_t": ctypes.c_int64}.get(decl[name + ":ret"][0], ctypes.c_int)
             self._fns[name] = fn
 
     def raw(self, name):

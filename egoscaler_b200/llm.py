@@ -48,6 +48,19 @@ class LayerWeights:
     wguT: Optional[torch.Tensor] = None
     wdownT: Optional[torch.Tensor] = None
 
+    # decode-layout copies (128x64 tiles, pre-swizzled; ops.retile_weight) streamed by the single-token step
+    tqkv: Optional["ops.TiledWeight"] = None
+    to: Optional["ops.TiledWeight"] = None
+    tgu: Optional["ops.TiledWeight"] = None
+    tdown: Optional["ops.TiledWeight"] = None
+
+    def ensure_tiled(self):
+        if self.tqkv is None:
+            self.tqkv = ops.retile_weight(self.wqkv)
+            self.to = ops.retile_weight(self.wo)
+            self.tgu = ops.retile_weight(self.wgu)
+            self.tdown = ops.retile_weight(self.wdown)
+
     def ensure_transposed(self):
         if self.wqkvT is None:
             self.wqkvT = ops.transpose(self.wqkv)
@@ -98,22 +111,27 @@ class LlamaTrunk:
         With ``cache``: K/V of these L tokens are written at pos0.. and attention runs over cache[:pos0+L]."""
         c = self.cfg
         d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
-        decode = cache is not None and L == 1 and (pos0 > 0 or pos_dev is not None)
+        attn_decode = cache is not None and L == 1 and (pos0 > 0 or pos_dev is not None)
+        decode = attn_decode and B <= ops.SKINNY_MAX_M      # weight-streaming GEMMs on the tiled copies
         if pos_dev is not None:          # graph-replayed decode step: the position lives in a device counter
-            assert decode and pos0 == 0
+            assert attn_decode and pos0 == 0
         for li, w in enumerate(self.layers):
             if saved is not None:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
             else:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps), None
-            qkv = ops.gemm(xn, w.wqkv)                                            # [T, 3d]
+            if decode:
+                w.ensure_tiled()
+                qkv = ops.gemm_skinny(xn, w.tqkv)
+            else:
+                qkv = ops.gemm(xn, w.wqkv)                                        # [T, 3d]
             if cache is not None:
                 ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
                           kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len, pos_ptr=pos_dev)
             else:
                 ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0)
             lse = None
-            if decode:
+            if attn_decode:
                 o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_ptr=pos_dev, len_static=pos0 + 1)
             else:
                 q4 = qkv.view(B, L, 3, H, hd)
@@ -125,14 +143,14 @@ class LlamaTrunk:
                 r = ops.attention(q4[:, :, 0], k4, v4, causal=True, kmask=kmask, q_pos0=pos0, want_lse=saved is not None)
                 o, lse = r if saved is not None else (r, None)
                 o = o.view(B * L, d)
-            h = ops.gemm(o, w.wo, residual=x)
+            h = ops.gemm_skinny(o, w.to, residual=x) if decode else ops.gemm(o, w.wo, residual=x)
             if saved is not None:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps, want_rstd=True)
             else:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps), None
-            gu = ops.gemm(hn, w.wgu)
+            gu = ops.gemm_skinny(hn, w.tgu) if decode else ops.gemm(hn, w.wgu)
             a = ops.silu_mul(gu)
-            out = ops.gemm(a, w.wdown, residual=h)
+            out = ops.gemm_skinny(a, w.tdown, residual=h) if decode else ops.gemm(a, w.wdown, residual=h)
             if saved is not None:
                 saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu))
             x = out

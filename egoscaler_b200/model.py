@@ -69,6 +69,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         self._packed_proj: Optional[PackedProjector] = None
         self._trunk: Optional[LlamaTrunk] = None
         self._lm_head_T: Optional[torch.Tensor] = None
+        self._lm_head_tiled = None                          # decode-layout copy of lm_head (ops.retile_weight)
         self.v_pad = (cfg.vocab_size + 7) // 8 * 8          # logits leading dimension (16-byte rows)
 
     # ------------------------------------------------------------------ reference API surface
@@ -114,6 +115,7 @@ class TrajPointLLMForCausalLM(ParamTree):
                                        named[pre + "post_attention_layernorm.weight"].detach()))
         self._trunk = LlamaTrunk(self.cfg, layers, self.dev)
         self._lm_head_T = None
+        self._lm_head_tiled = None
 
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
         r = super().load_state_dict(state_dict, strict=strict, assign=False)
@@ -205,12 +207,17 @@ class TrajPointLLMForCausalLM(ParamTree):
             cache.length = cache.length + L
         return h, splice_pos
 
-    def logits_from_hidden(self, h: torch.Tensor) -> torch.Tensor:
+    def logits_from_hidden(self, h: torch.Tensor, decode: bool = False) -> torch.Tensor:
         """final RMSNorm + lm_head (pointllm.py:227-228) -> [rows, V] view of a [rows, v_pad] bf16 buffer."""
         hn = ops.rmsnorm(h, self.model.norm.weight.detach(), self.cfg.rms_norm_eps)
         buf = torch.empty(h.shape[0], self.v_pad, device=h.device, dtype=torch.bfloat16)
         out = buf[:, :self.cfg.vocab_size]
-        ops.gemm(hn, self.lm_head.weight.detach(), out=out)
+        if decode and h.shape[0] <= ops.SKINNY_MAX_M:       # cached single-token step: stream the tiled copy
+            if self._lm_head_tiled is None:
+                self._lm_head_tiled = ops.retile_weight(self.lm_head.weight.detach())
+            ops.gemm_skinny(hn, self._lm_head_tiled, out=out)
+        else:
+            ops.gemm(hn, self.lm_head.weight.detach(), out=out)
         return out
 
     # ------------------------------------------------------------------ forward / generate (reference signatures)

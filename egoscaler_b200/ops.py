@@ -33,6 +33,66 @@ def _chk(t: torch.Tensor, dtype, name: str):
 
 
 # ------------------------------------------------------------------------------------------------ GEMM
+SKINNY_MAX_M = 64
+skinny_enabled = True
+_SKINNY_WS_BYTES = 96 << 20        # counters (16 KiB, zero) + fp32 split-K partials; lm_head at 9 splits needs ~37 MB
+_skinny_ws = {}
+
+
+def _skinny_workspace(device) -> torch.Tensor:
+    """Per-device workspace of esb_gemm_skinny_bf16 (zeroed once; the kernel leaves its counters at zero)."""
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    ws = _skinny_ws.get(key)
+    if ws is None:
+        ws = torch.zeros(_SKINNY_WS_BYTES, device=device, dtype=torch.uint8)
+        _skinny_ws[key] = ws
+    return ws
+
+
+class TiledWeight:
+    """A [N,K] bf16 weight re-laid out once into [ceil(N/128)][ceil(K/64)][128][64] tiles (esb_retile_weight_bf16): the
+    layout the decode-step GEMM streams at HBM speed (one contiguous 16 KiB read per pipeline stage)."""
+    __slots__ = ("data", "N", "K")
+
+    def __init__(self, data: torch.Tensor, N: int, K: int):
+        self.data, self.N, self.K = data, N, K
+
+
+def retile_weight(w: torch.Tensor) -> TiledWeight:
+    _chk(w, torch.bfloat16, "retile_weight.w")
+    assert w.dim() == 2 and w.stride(1) == 1
+    N, K = w.shape
+    n = int(_l.lib().raw("esb_retiled_weight_elems")(N, K))
+    out = torch.empty(n, device=w.device, dtype=torch.bfloat16)
+    _l.call("esb_retile_weight_bf16", w.data_ptr(), w.stride(0), N, K, out.data_ptr(), _stream())
+    return TiledWeight(out, N, K)
+
+
+def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
+                out: Optional[torch.Tensor] = None, force_splits: int = 0) -> torch.Tensor:
+    """``a @ w.T + residual`` for M <= 64 rows through the split-K weight-streaming kernel; ``w`` is a [N,K] bf16
+    tensor or a :class:`TiledWeight`."""
+    _chk(a, torch.bfloat16, "gemm_skinny.a")
+    M, K = a.shape
+    if isinstance(w, TiledWeight):
+        assert w.K == K
+        N, wp, ldw, tiled = w.N, w.data.data_ptr(), 0, 1
+    else:
+        _chk(w, torch.bfloat16, "gemm_skinny.w")
+        N, wp, ldw, tiled = w.shape[0], w.data_ptr(), w.stride(0), 0
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=torch.bfloat16)
+    ws = _skinny_workspace(a.device)
+    if gemm_timer is not None:
+        gemm_timer.before(M, N, K)
+    _l.call("esb_gemm_skinny_bf16", a.data_ptr(), a.stride(0), wp, ldw, out.data_ptr(), out.stride(0),
+            M, N, K, _p(residual), 0 if residual is None else residual.stride(0), ws.data_ptr(), ws.numel(), force_splits,
+            tiled, _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
+    return out
+
+
 def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
          residual: Optional[torch.Tensor] = None, act: int = ACT_NONE, out: Optional[torch.Tensor] = None,
          out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False, alpha: float = 1.0,
@@ -55,6 +115,17 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
         _chk(residual, torch.bfloat16, "gemm.residual")
         assert residual.shape == (M, N) and residual.stride(1) == 1
         ldr = residual.stride(0)
+    if (M <= SKINNY_MAX_M and skinny_enabled and bias is None and act == ACT_NONE and out.dtype == torch.bfloat16
+            and not accumulate and alpha == 1.0 and force_bn == 0 and K >= 256):
+        # cached single-token decode step: weight-streaming split-K kernel (gemm_skinny.cu)
+        ws = _skinny_workspace(a.device)
+        if gemm_timer is not None:
+            gemm_timer.before(M, N, K)
+        _l.call("esb_gemm_skinny_bf16", a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), out.data_ptr(), out.stride(0),
+                M, N, K, _p(residual), ldr, ws.data_ptr(), ws.numel(), 0, 0, _stream())
+        if gemm_timer is not None:
+            gemm_timer.after()
+        return out
     if gemm_timer is not None:
         gemm_timer.before(M, N, K)
     _l.call("esb_gemm_bf16", a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), out.data_ptr(), out.stride(0),

@@ -128,6 +128,7 @@ class Trainer:
                 p.detach().copy_(self.master[n])
         # refresh derived operands of the trainable tensors
         self.model._lm_head_T = None
+        self.model._lm_head_tiled = None
         self.model._packed_proj.refresh()
 
     def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -57,6 +57,22 @@ int esb_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* 
                   const float* bias, const void* residual, int64_t ldr, int act, int out_fp32, int accumulate,
                   float alpha, int force_bn, void* stream);
 
+/* Weight-streaming variant for the cached single-token decode step (M = sequences per GPU <= 64):
+ * C[M,N] = X[M,K] . W[N,K]^T + residual[M,N], bf16 in/out, fp32 accumulation, split-K over the SMs with a
+ * deterministic in-kernel reduction.  Same Linear call sites as esb_gemm_bf16, reached through generate()
+ * (model_arch.py:94-108 -> pointllm.py:255-275).  workspace: device buffer of at least
+ * esb_gemm_skinny_workspace_bytes(M,N,K) bytes whose first 16 KiB are ZERO on first use (the kernel leaves them
+ * zero); it may be shared by all launches on one stream.  force_splits: 0 = auto.
+ * w_tiled = 0: W is the state_dict layout [N,K] (ldw).  w_tiled = 1: W was re-laid out once by
+ * esb_retile_weight_bf16 into [ceil(N/128)][ceil(K/64)][128][64] (zero padded) so that every pipeline stage is one
+ * contiguous 16 KiB read - the HBM-friendly layout for streaming each weight exactly once (ldw ignored). */
+int64_t esb_gemm_skinny_workspace_bytes(int M, int N, int K);
+int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
+                         const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,
+                         int w_tiled, void* stream);
+int64_t esb_retiled_weight_elems(int N, int K);
+int esb_retile_weight_bf16(const void* W, int64_t ldw, int N, int K, void* out, void* stream);
+
 /* ------------------------------------------------------------------------------------------------ trajectory tokens
  * utils/utils.py:13-16 discretize_action: out[i] = np.digitize(x[i], np.linspace(-1,1,num_bins)) - 1 + id_offset
  * (bit-exact incl. edge values, NaN -> num_bins-1, x < -1 -> -1).  x: float32 (is_f64=0) or float64. */

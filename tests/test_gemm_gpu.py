@@ -56,3 +56,44 @@ def test_gemm_epilogues_and_fp32_out():
     w2 = w[:999]
     out3 = ops.gemm(a2, w2, bias=bias[:999].contiguous())
     torch.testing.assert_close(out3.float(), _ref(a2, w2, bias[:999]), atol=3e-2, rtol=1.6e-2)
+
+
+SKINNY = [(32, 4096, 4096), (1, 12288, 4096), (32, 32262, 4096), (64, 22016, 4096), (17, 4096, 11008), (33, 1000, 320),
+          (8, 256, 688), (32, 688, 256)]
+
+
+@pytest.mark.parametrize("M,N,K", SKINNY)
+@pytest.mark.parametrize("splits", [0, 1, 3])
+def test_gemm_skinny_matches_fp32_reference(M, N, K, splits):
+    """Decode-step weight-streaming GEMM (split-K, in-kernel deterministic reduction) vs fp32 torch, with residual."""
+    g = torch.Generator(device="cuda").manual_seed(M * 31 + N * 7 + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    res = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    out = ops.gemm_skinny(a, w, residual=res, force_splits=splits)
+    ref = _ref(a, w, res=res)
+    torch.testing.assert_close(out.float(), ref, atol=3e-2, rtol=1.6e-2)
+    out_nores = ops.gemm_skinny(a, w, force_splits=splits)
+    torch.testing.assert_close(out_nores.float(), _ref(a, w), atol=2e-2, rtol=1.6e-2)
+    # pre-tiled weight layout (the decode path's resident copy): identical arithmetic, identical bits
+    wt = ops.retile_weight(w)
+    assert torch.equal(ops.gemm_skinny(a, wt, residual=res, force_splits=splits), out)
+    # deterministic: the reduction order over K slices is fixed, whichever CTA arrives last
+    for _ in range(3):
+        assert torch.equal(ops.gemm_skinny(a, w, residual=res, force_splits=splits), out)
+    # counters are left at zero (graph-replay safe)
+    assert int(ops._skinny_workspace(a.device)[:16384].max()) == 0
+
+
+def test_gemm_dispatches_skinny_for_decode_rows():
+    g = torch.Generator(device="cuda").manual_seed(3)
+    a = torch.randn(32, 4096, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(4096, 4096, device="cuda", generator=g) / 64).bfloat16()
+    ops.skinny_enabled = True
+    y1 = ops.gemm(a, w)
+    ops.skinny_enabled = False
+    try:
+        y0 = ops.gemm(a, w)
+    finally:
+        ops.skinny_enabled = True
+    torch.testing.assert_close(y1.float(), y0.float(), atol=2e-2, rtol=1.6e-2)
