@@ -65,6 +65,15 @@ int esb_argmax_rows(const void* logits, int64_t ld, int64_t rows, int V, int64_t
     return argmax_rows(logits, ld, rows, V, LLP(out_idx), scores, scores_ld, suppress_col, step_ptr, step_off, scores_step_stride,
                        ST(stream));
 }
+int esb_sample_rows(const void* logits, int64_t ld, int64_t rows, int V, float temperature, int top_k, float top_p,
+                    float penalty, const int64_t* hist, int64_t hist_ld, int hist_len, const int32_t* pos_ptr,
+                    const float* u, int64_t u_step_stride, const int32_t* step_ptr, int step_off, float* scores,
+                    int64_t scores_ld, int64_t scores_step_stride, int suppress_col, int64_t* out_idx, int32_t* n_kept,
+                    void* stream) {
+    return sample_rows(logits, ld, rows, V, temperature, top_k, top_p, penalty, CLLP(hist), hist_ld, hist_len, pos_ptr, u,
+                       u_step_stride, step_ptr, step_off, scores, scores_ld, scores_step_stride, suppress_col, LLP(out_idx), n_kept,
+                       ST(stream));
+}
 int esb_greedy_update(const int64_t* next, int64_t* tokens_out, int32_t* unfinished, int64_t* sequences, int64_t seq_ld,
                       int cur_len, uint8_t* mask, int64_t mask_ld, int64_t eos, int64_t pad, int B, int32_t* pos_ptr, void* stream) {
     return greedy_update(CLLP(next), LLP(tokens_out), unfinished, LLP(sequences), seq_ld, cur_len, mask, mask_ld, eos, pad, B, pos_ptr,

@@ -49,6 +49,11 @@ int cross_entropy(void* logits, long long ld, long long rows, int V, const long 
                   float* row_loss, float* scratch_inv_count, float* loss, int write_grad, cudaStream_t s);
 int argmax_rows(const void* logits, long long ld, long long rows, int V, long long* out_idx, float* scores, long long scores_ld,
                 int suppress_col, const int* step_ptr, int step_off, long long scores_step_stride, cudaStream_t s);
+// sampling.cu
+int sample_rows(const void* logits, long long ld, long long rows, int V, float temperature, int top_k, float top_p, float penalty,
+                const long long* hist, long long hist_ld, int hist_len, const int* pos_ptr, const float* u,
+                long long u_step_stride, const int* step_ptr, int step_off, float* scores, long long scores_ld,
+                long long scores_step_stride, int suppress_col, long long* out_idx, int* n_kept, cudaStream_t s);
 int greedy_update(const long long* next, long long* tokens_out, int* unfinished, long long* sequences, long long seq_ld,
                   int cur_len, uint8_t* mask, long long mask_ld, long long eos, long long pad, int B, int* pos_ptr, cudaStream_t s);
 int adamw(float* p, const float* g, float* m, float* v, void* p_bf16, long long n, float lr, float beta1, float beta2, float eps,

@@ -5,8 +5,11 @@ Reference: ``TrajPointLLMForCausalLM.generate`` (model_arch.py:77-108) -> HF ``G
 encoder, later steps feed one token against the cache; finished rows emit ``pad``; the attention mask grows by ones
 (HF generation/utils.py:2762-2806).  Callers: train.py:221-231, evaluate.py:114-124.
 
-Greedy decoding is the mode with a bit-exact contract (ids from identical logits); the reference's default sampling
-chain (top-k 50 -> top-p 0.95 -> multinomial) is SURVEY 8f row N1 and not built yet.
+Greedy decoding is the mode with a bit-exact contract (ids from identical logits).  ``do_sample=True`` (the reference's
+default) runs HF's processor chain repetition-penalty -> temperature -> top-k -> top-p on device
+(``esb_sample_rows``, csrc/sampling.cu): the surviving ids and their fp32 ``scores`` are HF's on identical logits, the
+draw uses uniforms from a torch generator (``seed=`` / ``generator=``) and is distribution-equal to
+``torch.multinomial``.  ``num_return_sequences`` repeats every prompt like HF ``_expand_inputs_for_generation``.
 """
 from __future__ import annotations
 
@@ -25,14 +28,18 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
              top_p: float = 0.95, repetition_penalty: float = 1.0, do_sample: bool = True, num_return_sequences: int = 1,
              fps_start: Optional[torch.Tensor] = None, suppress_eos: bool = False, output_scores: bool = True,
              eos_check_every: int = 16, use_cuda_graph: bool = True, **kwargs) -> GenerateOutput:
-    if do_sample:
-        raise NotImplementedError("sampling decode (top-k/top-p/multinomial, SURVEY 8f N1) is not built; pass do_sample=False")
-    if num_return_sequences != 1 or repetition_penalty != 1.0:
-        raise NotImplementedError("num_return_sequences != 1 / repetition_penalty != 1 are not built")
+    if do_sample and not (1 <= int(top_k) <= 1024):
+        raise NotImplementedError("sampling decode supports top_k in 1..1024 (the reference uses 50)")
     cfg, dev = model.cfg, model.dev
     was_training = model.training
     model.eval()
     input_ids = input_ids.to(dev)
+    n_ret = int(num_return_sequences)
+    if n_ret > 1:                                         # HF _expand_inputs_for_generation: repeat_interleave on dim 0
+        input_ids = input_ids.repeat_interleave(n_ret, dim=0)
+        attention_mask = None if attention_mask is None else attention_mask.repeat_interleave(n_ret, dim=0)
+        point_clouds = None if point_clouds is None else point_clouds.repeat_interleave(n_ret, dim=0)
+        fps_start = None if fps_start is None else fps_start.repeat_interleave(n_ret, dim=0)
     B, P = input_ids.shape
     T = int(max_length)                                   # model_arch.py:96: max_new_tokens = max_length
     V, d = cfg.vocab_size, cfg.hidden_size
@@ -47,6 +54,23 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
     scores = torch.empty(T, B, V, device=dev, dtype=torch.float32) if output_scores else None
     last = torch.empty(B, 1, d, device=dev, dtype=torch.bfloat16)
     sup = cfg.eos_token_id if suppress_eos else -1
+    u = None
+    if do_sample:
+        gen = kwargs.get("generator")
+        if gen is None and kwargs.get("seed") is not None:
+            gen = torch.Generator(device=dev).manual_seed(int(kwargs["seed"]))
+        u = torch.rand(T, B, device=dev, dtype=torch.float32, generator=gen)
+    pen = float(repetition_penalty)
+
+    def pick(lg, step_off, step_ptr, sc, hist_len, hist_ptr):
+        """next-token choice for logits ``lg``: greedy arg-max, or the HF sampling chain."""
+        if not do_sample:
+            ops.argmax_rows(lg, V, scores=sc, suppress_col=sup, out=nxt, step_ptr=step_ptr, step_off=step_off,
+                            scores_step_stride=B * V)
+        else:
+            ops.sample_rows(lg, V, u, temperature, top_k, top_p, pen, hist=seq if pen != 1.0 else None, hist_len=hist_len,
+                            pos_ptr=hist_ptr, scores=sc, suppress_col=sup, out=nxt, step_ptr=step_ptr, step_off=step_off,
+                            scores_step_stride=B * V, u_step_stride=B)
 
     # Device-side cache-length counter: lets ONE captured CUDA graph of the single-token step (32 layers x 9 kernels +
     # head + argmax + bookkeeping, ~300 launches) be replayed for every generated token, so the step is bound by HBM
@@ -56,8 +80,7 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
     def token_step():
         hl_, _ = model.hidden_states(tok, mask, None, None, cache, pos_dev=pos_dev)
         lg = model.logits_from_hidden(hl_, decode=True)
-        ops.argmax_rows(lg, V, scores=scores, suppress_col=sup, out=nxt, step_ptr=pos_dev, step_off=1 - P,
-                        scores_step_stride=B * V)
+        pick(lg, 1 - P, pos_dev, scores, 1, pos_dev)
         ops.greedy_update(nxt, tok.view(B), unfinished, seq, 1, mask, cfg.eos_token_id, cfg.pad_token_id, pos_ptr=pos_dev)
 
     graph = None
@@ -67,7 +90,7 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
             h, _ = model.hidden_states(input_ids, mask[:, :P], point_clouds, fps_start, cache)
             ops.copy_rows(h.view(B, P, d)[:, P - 1:P, :], last)
             logits = model.logits_from_hidden(last.view(B, d))
-            ops.argmax_rows(logits, V, scores=None if scores is None else scores[0], suppress_col=sup, out=nxt)
+            pick(logits, 0, None, scores, P, None)
             ops.greedy_update(nxt, tok.view(B), unfinished, seq, P, mask, cfg.eos_token_id, cfg.pad_token_id)
         elif s == 1 or not use_cuda_graph:
             token_step()

@@ -357,6 +357,27 @@ def argmax_rows(logits: torch.Tensor, V: int, scores: Optional[torch.Tensor] = N
     return out
 
 
+def sample_rows(logits: torch.Tensor, V: int, u: torch.Tensor, temperature: float = 1.0, top_k: int = 50, top_p: float = 0.95,
+                penalty: float = 1.0, hist: Optional[torch.Tensor] = None, hist_len: int = 0, pos_ptr=None,
+                scores: Optional[torch.Tensor] = None, suppress_col: int = -1, out: Optional[torch.Tensor] = None,
+                step_ptr=None, step_off: int = 0, scores_step_stride: int = 0, u_step_stride: int = 0,
+                n_kept: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """HF sampling chain (repetition penalty -> temperature -> top-k -> top-p -> draw) on bf16 logits [rows, >=V];
+    ``u`` fp32 uniforms ([rows], or [steps, rows] with ``u_step_stride`` and a step counter)."""
+    _chk(logits, torch.bfloat16, "sample_rows.logits")
+    _chk(u, torch.float32, "sample_rows.u")
+    rows = logits.shape[0]
+    if out is None:
+        out = torch.empty(rows, device=logits.device, dtype=torch.int64)
+    if hist is not None:
+        _chk(hist, torch.int64, "sample_rows.hist")
+    _l.call("esb_sample_rows", logits.data_ptr(), logits.stride(0), rows, V, float(temperature), int(top_k), float(top_p),
+            float(penalty), _p(hist), 0 if hist is None else hist.stride(0), int(hist_len), _p(pos_ptr), u.data_ptr(),
+            int(u_step_stride), _p(step_ptr), int(step_off), _p(scores), 0 if scores is None else scores.stride(-2),
+            int(scores_step_stride), int(suppress_col), out.data_ptr(), _p(n_kept), _stream())
+    return out
+
+
 def greedy_update(nxt, tokens_out, unfinished, sequences, cur_len: int, mask, eos: int, pad: int, pos_ptr=None):
     B = nxt.shape[0]
     _l.call("esb_greedy_update", nxt.data_ptr(), tokens_out.data_ptr(), unfinished.data_ptr(), sequences.data_ptr(),

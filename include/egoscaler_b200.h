@@ -158,6 +158,19 @@ int esb_cross_entropy(void* logits, int64_t ld, int64_t rows, int V, const int64
 int esb_argmax_rows(const void* logits, int64_t ld, int64_t rows, int V, int64_t* out_idx, float* scores,
                     int64_t scores_ld, int suppress_col, const int32_t* step_ptr, int step_off, int64_t scores_step_stride,
                     void* stream);
+/* Sampling step, the reference's default decode mode (model_arch.py:77-108: do_sample=True, top_k=50, top_p=0.95,
+ * temperature=1, repetition_penalty=1; HF generation/logits_process.py RepetitionPenalty :302 -> Temperature :236 ->
+ * TopK :536 -> TopP :469, then softmax + draw, generation/utils.py _sample).  logits [rows, ld] bf16.  hist (or NULL):
+ * ids already in each row, [rows, hist_ld], first hist_len (+ *pos_ptr) entries valid.  u: uniform [0,1) draws,
+ * u[step * u_step_stride + row] with step = (*step_ptr or 0) + step_off.  scores (or NULL): processed fp32 scores,
+ * -inf where filtered, block `step` of stride scores_step_stride.  out_idx [rows]; n_kept (or NULL) [rows] = survivors.
+ * top_k in 1..1024.  The survivor set / scores are exactly HF's on identical logits; the draw is an inverse-CDF walk
+ * over survivors in descending-score order (distribution-equal to torch.multinomial, not draw-equal). */
+int esb_sample_rows(const void* logits, int64_t ld, int64_t rows, int V, float temperature, int top_k, float top_p,
+                    float penalty, const int64_t* hist, int64_t hist_ld, int hist_len, const int32_t* pos_ptr,
+                    const float* u, int64_t u_step_stride, const int32_t* step_ptr, int step_off, float* scores,
+                    int64_t scores_ld, int64_t scores_step_stride, int suppress_col, int64_t* out_idx, int32_t* n_kept,
+                    void* stream);
 /* Finished-row bookkeeping of the same loop: finished rows emit pad, EOS finishes a row, token appended to
  * sequences[:, cur_len], attention mask grown by one.  With pos_ptr (device) the column is cur_len + *pos_ptr and
  * *pos_ptr is incremented afterwards (the cache-length counter of the graph-replayed decode step). */

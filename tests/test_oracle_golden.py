@@ -148,3 +148,31 @@ def test_teacher_forced_poses(gm):
         # the prompt holds <ts> + first pose + <tsep>; 19 poses follow, and the trailing "<te>" segment
         # has no match so it repeats the last pose (utils.py:91-93) -> 20 rows
         assert p.shape == (20, 6) and np.array_equal(p[-1], p[-2]) and np.array_equal(p, gm["tf_poses"][b])
+
+
+def test_sampling_filter_matches_hf_processors():
+    """oracle/sampling.py vs the real HF processor classes the reference's generate() drives (model_arch.py:94-108)."""
+    import torch
+    from transformers.generation.logits_process import (RepetitionPenaltyLogitsProcessor, TemperatureLogitsWarper,
+                                                        TopKLogitsWarper, TopPLogitsWarper)
+    from oracle.sampling import hf_filter
+    g = torch.Generator().manual_seed(11)
+    for V, k, p, temp, pen in [(32262, 50, 0.95, 1.0, 1.0), (32262, 50, 0.95, 0.7, 1.3), (1000, 5, 0.5, 1.0, 1.0),
+                               (4096, 200, 0.99, 1.5, 1.1)]:
+        scores = (torch.randn(4, V, generator=g) * 3).bfloat16().float()        # bf16-valued like the reference's logits
+        ids = torch.randint(0, V, (4, 37), generator=g)
+        ref = scores.clone()
+        if pen != 1.0:
+            ref = RepetitionPenaltyLogitsProcessor(pen)(ids, ref)
+        if temp != 1.0:
+            ref = TemperatureLogitsWarper(temp)(ids, ref)
+        ref = TopKLogitsWarper(k)(ids, ref)
+        ref = TopPLogitsWarper(p)(ids, ref)
+        mine = hf_filter(scores, ids, temp, k, p, pen)
+        # value-ties across the top-p boundary are ordered arbitrarily by torch.sort(stable=False): compare per value
+        assert torch.equal(torch.sort(ref, dim=-1)[0], torch.sort(mine, dim=-1)[0])
+        same = (ref == mine) | (torch.isinf(ref) & torch.isinf(mine))
+        for b in range(4):                                   # any disagreement is a tie with the smallest kept value
+            kept_min = ref[b][torch.isfinite(ref[b])].min()
+            pre = hf_filter(scores, ids, temp, k, 1.0, pen)[b]          # before top-p
+            assert bool((pre[~same[b]] == kept_min).all())
