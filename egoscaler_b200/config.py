@@ -72,6 +72,12 @@ class TrajVLMConfig:
         return TrajVLMConfig(hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=4)
 
     @staticmethod
+    def tiny_base() -> "TrajVLMConfig":
+        """Tiny LLM + the base PointBERT encoder (SURVEY 8d config E at parity-test size)."""
+        return TrajVLMConfig(hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=4,
+                             point=PointEncoderConfig.base())
+
+    @staticmethod
     def full() -> "TrajVLMConfig":
         """LLaMA-7B / Vicuna dims used by RunsenXu/PointLLM_7B_v1.2 (train.py:321)."""
         return TrajVLMConfig()

@@ -30,7 +30,7 @@ constexpr int ATT_BM = 64, ATT_BN = 64, ATT_THREADS = 128;
 template <int HD>
 __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const AttnParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int TILE = ATT_BM * HD * 2;
+    constexpr int TILE = ATT_BM * tile_row_bytes<HD>();
     uint8_t* sQ = smem;
     uint8_t* sK = smem + TILE;            // 2 stages
     uint8_t* sV = smem + 3 * TILE;        // 2 stages
@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const AttnParams 
 
 template <int HD>
 static int launch_attn_fwd(const AttnParams& p, cudaStream_t s) {
-    constexpr int SMEM = 5 * ATT_BM * HD * 2;
+    constexpr int SMEM = 5 * ATT_BM * tile_row_bytes<HD>();
     static bool set = false;
     if (!set) {
         cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -201,10 +201,11 @@ int attn_fwd(const void* q, long long q_bs, long long q_rs, const void* k, long 
     p.q_bs = q_bs; p.q_rs = q_rs; p.k_bs = k_bs; p.k_rs = k_rs; p.v_bs = v_bs; p.v_rs = v_rs; p.o_bs = o_bs; p.o_rs = o_rs;
     p.kmask_ld = kmask_ld; p.B = B; p.H = H; p.Lq = Lq; p.Lk = Lk; p.causal = causal; p.q_pos0 = q_pos0; p.scale = scale;
     if (hd == 64) return launch_attn_fwd<64>(p, s);
+    if (hd == 96) return launch_attn_fwd<96>(p, s);     // PointBERT base encoder (trans_dim 1152, 12 heads)
     if (hd == 128)      // tcgen05 / TMEM / TMA kernel (attention_fwd_tc.cu); the mma.sync kernel below serves head_dim 64 only
         return attn_fwd_tc128(q, q_bs, q_rs, k, k_bs, k_rs, v, v_bs, v_rs, o, o_bs, o_rs, lse, kmask, kmask_ld, B, H, Lq, Lk, causal,
                               q_pos0, scale, s);
-    set_last_error("attn_fwd: head_dim %d unsupported (64, 128)", hd);
+    set_last_error("attn_fwd: head_dim %d unsupported (64, 96, 128)", hd);
     return ESB_ERR_UNSUPPORTED;
 }
 

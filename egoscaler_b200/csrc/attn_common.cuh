@@ -26,10 +26,15 @@ ESB_DEVICE void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) 
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-// Shared-memory tile [rows][HD] bf16, 16-byte chunks XOR-swizzled by (row & 7) so ldmatrix is conflict-free.
+// Shared-memory tile [rows][HD] bf16.  Power-of-two HD (64, 128): 16-byte chunks XOR-swizzled by (row & 7) so ldmatrix
+// is conflict-free.  Other HD (96 = PointBERT base, 1152 / 12 heads): rows padded by one 16-byte chunk instead (an odd
+// number of chunks per row spreads 8 consecutive rows over the 8 bank groups).
+template <int HD>
+constexpr int tile_row_bytes() { return (HD & (HD - 1)) == 0 ? HD * 2 : HD * 2 + 16; }
 template <int HD>
 ESB_DEVICE uint32_t tile_off(int row, int chunk) {
-    return static_cast<uint32_t>(row * (HD * 2) + ((chunk ^ (row & 7)) << 4));
+    if constexpr ((HD & (HD - 1)) == 0) return static_cast<uint32_t>(row * (HD * 2) + ((chunk ^ (row & 7)) << 4));
+    else return static_cast<uint32_t>(row * tile_row_bytes<HD>() + (chunk << 4));
 }
 
 // Async load of a [ROWS x HD] tile: global row r is base + (row0 + r) * row_stride (elements); rows >= nrows -> zeros.

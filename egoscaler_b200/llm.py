@@ -61,6 +61,16 @@ class LayerWeights:
             self.tgu = ops.retile_weight(self.wgu)
             self.tdown = ops.retile_weight(self.wdown)
 
+    def refresh_derived(self):
+        """After an optimizer step on the trunk weights (--unfreeze_language_model): rewrite the contraction-major
+        copies in place and drop the decode-layout copies."""
+        if self.wqkvT is not None:
+            ops.transpose(self.wqkv, out=self.wqkvT)
+            ops.transpose(self.wo, out=self.woT)
+            ops.transpose(self.wgu, out=self.wguT)
+            ops.transpose(self.wdown, out=self.wdownT)
+        self.tqkv = self.to = self.tgu = self.tdown = None
+
     def ensure_transposed(self):
         if self.wqkvT is None:
             self.wqkvT = ops.transpose(self.wqkv)
@@ -158,7 +168,7 @@ class LlamaTrunk:
 
     # ------------------------------------------------------------------ backward (data gradients; frozen weights)
     def backward(self, dout: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], saved: List[LayerSaved],
-                 wgrad: Optional[Dict[str, List[torch.Tensor]]] = None) -> torch.Tensor:
+                 wgrad: Optional[Dict[str, List[torch.Tensor]]] = None, on_layer_done=None) -> torch.Tensor:
         """dout [B*L, d] bf16 -> dx [B*L, d].  Default recipe freezes the trunk (model_arch.py:33-51): only data
         gradients flow.  ``wgrad`` (fp32 accumulators per layer) enables the --unfreeze_language_model path."""
         c = self.cfg
@@ -190,4 +200,6 @@ class LlamaTrunk:
             else:
                 dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh)
             saved[li] = None                                                      # free activations as we go
+            if on_layer_done is not None:
+                on_layer_done(li)                                                 # e.g. start this layer's gradient reduction
         return dout

@@ -34,15 +34,38 @@ class Trainer:
     def __init__(self, model: TrajPointLLMForCausalLM, lr: float = 2e-5, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.01, warmup_steps: int = 0, total_steps: int = 0, process_group=None,
                  world_size: int = 1):
-        if model.unfreeze_language_model or model.unfreeze_pc_encoder:
-            raise NotImplementedError("only the default freezing recipe (model_arch.py:33-51) is built")
+        if model.unfreeze_pc_encoder:
+            raise NotImplementedError("--unfreeze_pc_encoder (BatchNorm batch statistics + DropPath in the encoder backward) is not built")
         self.model = model
         self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
         self.warmup, self.total = warmup_steps, total_steps
         self.pg, self.world = process_group, world_size
         self.step_count = 0
         named = dict(model.named_parameters())
-        self.names: List[str] = model.trainable_names()
+        # LLM-layer tensors are optimised as the PACKED kernel operands (q|k|v and gate|up share one buffer each; AdamW is
+        # element-wise, so this equals stepping the reference's separate parameters); everything else by parameter name.
+        self.names: List[str] = [n for n in model.trainable_names() if not n.startswith("model.layers.")]
+        self.rank = 0
+        if world_size > 1:
+            import torch.distributed as dist
+            self.rank = dist.get_rank(process_group)
+        self.trunk_units = []               # (kind, layer, bf16 tensor); --unfreeze_language_model (model_arch.py:40-45)
+        self.wgrad = None
+        if model.unfreeze_language_model:
+            kinds = (("wqkv", "wqkv"), ("wo", "wo"), ("wgu", "wgu"), ("wdown", "wdown"), ("ln1", "ln1"), ("ln2", "ln2"))
+            self.wgrad = {k: [] for k, _ in kinds}
+            for li, lw in enumerate(model.trunk.layers):
+                for k, attr in kinds:
+                    t = getattr(lw, attr)
+                    self.trunk_units.append((k, li, t))
+                    self.wgrad[k].append(torch.zeros(t.shape, device=t.device, dtype=torch.float32))
+            # ZeRO-1 (train.py:99-103): optimizer states of unit u live on rank u % world only
+            self.t_master, self.t_m, self.t_v = {}, {}, {}
+            for u, (k, li, t) in enumerate(self.trunk_units):
+                if u % self.world_size_safe(world_size) == self.rank:
+                    self.t_master[u] = t.detach().float().clone()
+                    self.t_m[u] = torch.zeros_like(self.t_master[u])
+                    self.t_v[u] = torch.zeros_like(self.t_master[u])
         self.param: Dict[str, torch.Tensor] = {n: named[n] for n in self.names}
         # fp32 master weights + moments (DeepSpeed bf16 optimizer keeps the same)
         self.master = {n: p.detach().float().clone() for n, p in self.param.items()}
@@ -51,9 +74,17 @@ class Trainer:
         self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.last_loss: Optional[torch.Tensor] = None
 
+    @staticmethod
+    def world_size_safe(w: int) -> int:
+        return max(1, int(w))
+
     def zero_grad(self):
         for g in self.grad.values():
             g.zero_()
+        if self.wgrad is not None:
+            for lst in self.wgrad.values():
+                for g in lst:
+                    g.zero_()
 
     # ------------------------------------------------------------------ forward + backward
     def forward_backward(self, tokens: torch.Tensor, attention_masks: torch.Tensor, pcrgbs: torch.Tensor, prompt_len: int,
@@ -87,7 +118,8 @@ class Trainer:
         dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)
         ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
         # ---- trunk backward (data gradients through the frozen layers)
-        dx = m.trunk.backward(dh.view(B * L, d), B, L, kmask, saved)
+        dx = m.trunk.backward(dh.view(B * L, d), B, L, kmask, saved, wgrad=self.wgrad,
+                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self.world > 1) else None)
         # ---- embedding scatter + projector
         dfeats = torch.empty(B, n_point, d, device=dev, dtype=torch.bfloat16)
         ops.embed_splice_bwd(tokens, dx, splice_pos, n_point, self.grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id)
@@ -109,6 +141,17 @@ class Trainer:
         for n in names:
             self._pending.append(dist.all_reduce(self.grad[n], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
 
+    def _reduce_layer_async(self, li: int):
+        """ZeRO-1 gradient exchange of one LLM layer, started as soon as its backward has been queued: every unit is
+        sum-reduced to its owner rank only (the reduce-scatter half of an all-reduce), overlapping the remaining layers."""
+        import torch.distributed as dist
+        if not hasattr(self, "_pending"):
+            self._pending = []
+        for u, (k, l2, _) in enumerate(self.trunk_units):
+            if l2 == li:
+                self._pending.append(dist.reduce(self.wgrad[k][li], dst=dist.get_global_rank(self.pg, u % self.world) if self.pg is not None
+                                                 else u % self.world, op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
     def _wait_reduce(self):
         for w in getattr(self, "_pending", []):
             w.wait()
@@ -126,10 +169,34 @@ class Trainer:
                        lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_count, scale)
             if p.dtype != torch.bfloat16:
                 p.detach().copy_(self.master[n])
+        if self.trunk_units:
+            self._trunk_step(lr, scale)
         # refresh derived operands of the trainable tensors
         self.model._lm_head_T = None
         self.model._lm_head_tiled = None
         self.model._packed_proj.refresh()
+
+    def _trunk_step(self, lr: float, scale: float):
+        """AdamW on the LLM-layer units this rank owns, then (N > 1) broadcast of the updated bf16 weights from their
+        owners (the all-gather half of ZeRO-1) and refresh of the contraction-major copies."""
+        for u, (k, li, t) in enumerate(self.trunk_units):
+            if u in self.t_master:
+                ops.adamw_(self.t_master[u].view(-1), self.wgrad[k][li].view(-1), self.t_m[u].view(-1), self.t_v[u].view(-1),
+                           t.view(-1) if t.is_contiguous() else None, lr, self.betas[0], self.betas[1], self.eps, self.wd,
+                           self.step_count, scale)
+                if not t.is_contiguous():
+                    t.copy_(self.t_master[u])
+        if self.world > 1:
+            import torch.distributed as dist
+            hs = []
+            for u, (k, li, t) in enumerate(self.trunk_units):
+                src = u % self.world
+                hs.append(dist.broadcast(t, src=dist.get_global_rank(self.pg, src) if self.pg is not None else src,
+                                         group=self.pg, async_op=True))
+            for h in hs:
+                h.wait()
+        for lw in self.model.trunk.layers:
+            lw.refresh_derived()
 
     def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration of train.py:157-184 on a collate_fn-shaped batch (dataset.py:184-194)."""

@@ -226,8 +226,85 @@ def golden_model(name="traj_vlm_tiny", batch=2, new_tokens=152):
           f"size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
 
 
+def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unfreeze_lm=False, batch=2, new_tokens=24,
+                   point="v12"):
+    """Smaller fixtures for the other recipes of SURVEY 8d: (a) ``--unfreeze_language_model`` (model_arch.py:40-45):
+    gradients of every LLM-layer tensor; (b) config E: the base PointBERT encoder yaml (trans 1152, 12 heads x 96,
+    k=48, enc 512, single-Linear projector) with the default freezing: logits / loss / trainable grads / greedy ids."""
+    llm = LlmCfg.tiny()
+    m = ref_shim.build_reference_model(llm, point_cfg_name)
+    sd = synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True)
+    m.load_state_dict(sd, strict=True)
+    for p in m.model.point_backbone.parameters():
+        p.requires_grad = False
+    for p in m.model.layers.parameters():
+        p.requires_grad = bool(unfreeze_lm)
+    m.train()
+    if not unfreeze_lm:
+        m.model.layers.eval()
+    m.model.point_backbone.eval()
+    cfg = TrajVLMConfig.tiny() if point == "v12" else TrajVLMConfig.tiny_base()
+    bt = synth.make_batch(cfg, batch, seed=1)
+    ids, mask, pc = bt["tokens"], bt["attention_masks"], bt["pcrgbs"]
+    P = bt["prompts"].shape[1]
+    out = dict(fps_seed=np.int64(FPS_SEED), fps_start=_fps_start(pc.shape[1], batch).numpy(), prompt_len=np.int64(P),
+               torch_version=np.array(torch.__version__), transformers_version=np.array(__import__("transformers").__version__))
+    res = _ref_forward(m, ids, mask, pc)
+    logits = res.logits
+    lg = logits[:, P - 1:-1, :]
+    loss = torch.nn.functional.cross_entropy(lg.reshape(-1, lg.shape[-1]), ids[:, P:].flatten(), ignore_index=llm.pad_token_id)
+    loss.backward()
+    L = logits.detach()
+    rng = np.random.default_rng(3)
+    cols = np.sort(np.concatenate([rng.choice(32000, 256, replace=False), np.arange(32000, 32262)]))
+    rows = np.sort(np.concatenate([np.arange(0, 8), np.arange(510, 530), np.arange(P - 4, L.shape[1])]))
+    out.update(logit_rows=rows, logit_cols=cols, logits_sub=L[:, rows][:, :, cols].numpy(), loss=np.float64(loss.item()))
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        g = p.grad.detach()
+        out[f"gradnorm/{k}"] = np.float64(g.norm().item())
+        flat = g.flatten()
+        sel = torch.from_numpy(rng.choice(flat.numel(), min(2048, flat.numel()), replace=False)).long()
+        out[f"gradidx/{k}"] = sel.numpy()
+        out[f"gradval/{k}"] = flat[sel].numpy()
+    with torch.no_grad():
+        torch.manual_seed(FPS_SEED)
+        pf = m.model.point_backbone(pc)
+        out["point_feats_sub"] = pf[:, ::16, ::8].numpy()
+        out["point_proj_sub"] = m.model.point_proj(pf)[:, ::16, ::8].numpy()
+    m.eval()
+    with torch.no_grad():
+        msk = bt["prompt_masks"].clone()
+        r = _ref_forward(m, bt["prompts"].clone(), msk, pc, use_cache=True)
+        past = r.past_key_values
+        step_logits = [r.logits[:, -1].float()]
+        gen = []
+        for t in range(new_tokens):
+            nxt = step_logits[-1].argmax(-1)
+            gen.append(nxt)
+            msk = torch.cat((msk, torch.ones(batch, 1, dtype=torch.bool)), 1)
+            if t == new_tokens - 1:
+                break
+            r = m(input_ids=nxt[:, None], attention_mask=msk, past_key_values=past, use_cache=True, return_dict=True)
+            past = r.past_key_values
+            step_logits.append(r.logits[:, -1].float())
+        sl = torch.stack(step_logits, 1)
+        out["greedy_ids"] = torch.stack(gen, 1).numpy()           # EOS not special-cased: compare with suppress... see test
+        out["greedy_step_logits_sub"] = sl[:, :, cols].numpy()
+        out["greedy_step_top2gap"] = (sl.topk(2, -1).values[..., 0] - sl.topk(2, -1).values[..., 1]).numpy()
+    np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
+    print(f"{name}.npz: loss={out['loss']:.6f} size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
+
+
 if __name__ == "__main__":
+    import sys
     os.makedirs(GOLD, exist_ok=True)
+    torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "variants":
+        golden_variant("traj_vlm_tiny_unfrozen_lm", unfreeze_lm=True)
+        golden_variant("traj_vlm_tiny_base_encoder", point_cfg_name="PointTransformer_base_8192point", point="base")
+        sys.exit(0)
     torch.set_num_threads(os.cpu_count())
     golden_tokenizer()
     golden_model()

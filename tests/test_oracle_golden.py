@@ -176,3 +176,55 @@ def test_sampling_filter_matches_hf_processors():
             kept_min = ref[b][torch.isfinite(ref[b])].min()
             pre = hf_filter(scores, ids, temp, k, 1.0, pen)[b]          # before top-p
             assert bool((pre[~same[b]] == kept_min).all())
+
+
+# ------------------------------------------------------------------ other recipes (fixtures: make_golden.py variants)
+def _variant_check(name, point_cfg, vlm_cfg, unfreeze_lm, min_grads):
+    gv = np.load(os.path.join(GOLDEN, name + ".npz"))
+    torch.manual_seed(0)
+    m = TrajVLMOracle(LlmCfg.tiny(), point_cfg)
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    m.configure_trainable(unfreeze_language_model=unfreeze_lm)
+    m.eval()
+    bt = synth.make_batch(vlm_cfg, 2, seed=1)
+    P = int(gv["prompt_len"])
+    start = torch.from_numpy(gv["fps_start"])
+    logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=start, training=True)
+    loss = train_loss(logits, bt["tokens"], P, 0)
+    loss.backward()
+    sub = logits.detach()[:, gv["logit_rows"]][:, :, gv["logit_cols"]].numpy()
+    np.testing.assert_allclose(sub, gv["logits_sub"], atol=3e-4, rtol=1e-4)
+    assert abs(loss.item() - float(gv["loss"])) < 1e-4
+    n = 0
+    for k, p in m.named_parameters():
+        if f"gradnorm/{k}" not in gv.files:
+            continue
+        g = p.grad.flatten()
+        ref = gv[f"gradval/{k}"]
+        got = g[torch.from_numpy(gv[f"gradidx/{k}"])].numpy()
+        np.testing.assert_allclose(got, ref, atol=1e-6 + 2e-3 * np.abs(ref).max(), rtol=2e-3, err_msg=k)
+        n += 1
+    assert n >= min_grads
+    with torch.no_grad():
+        pf = m.model.point_backbone(bt["pcrgbs"], start)
+    np.testing.assert_allclose(pf[:, ::16, ::8].numpy(), gv["point_feats_sub"], atol=2e-4, rtol=1e-4)
+    T = gv["greedy_ids"].shape[1]
+    ids = greedy_decode(m, bt["prompts"], bt["prompt_masks"], bt["pcrgbs"], T, fps_start=start)
+    gen = ids[:, P:].numpy()
+    gap = gv["greedy_step_top2gap"]
+    k = min(gen.shape[1], gap.shape[1])
+    agree = gen[:, :k] == gv["greedy_ids"][:, :k]
+    first_eos = [(list(r).index(2) if 2 in r else k) for r in gv["greedy_ids"][:, :k]]
+    for b in range(2):                                        # the fixture loop does not special-case EOS rows
+        upto = min(k, first_eos[b] + 1)
+        assert agree[b, :upto][gap[b, :upto] > 1e-3].all()
+
+
+def test_oracle_unfrozen_language_model_matches_reference():
+    """--unfreeze_language_model (model_arch.py:40-45): gradients of every LLM-layer tensor."""
+    _variant_check("traj_vlm_tiny_unfrozen_lm", PointCfg(), TrajVLMConfig.tiny(), True, 9 + 2 * 9)
+
+
+def test_oracle_base_encoder_matches_reference():
+    """PointTransformer_base_8192point (trans 1152, 12 x 96, k=48, enc 512, Linear projector)."""
+    _variant_check("traj_vlm_tiny_base_encoder", PointCfg.base(), TrajVLMConfig.tiny_base(), False, 5)

@@ -1,0 +1,125 @@
+"""GPU: the other training recipes of SURVEY 8d against fixtures generated from the REAL reference
+(oracle/make_golden.py variants): --unfreeze_language_model (model_arch.py:40-45) and config E, the base PointBERT
+encoder (PointTransformer_base_8192point.yaml: trans 1152, 12 heads x 96, k=48, enc 512, single-Linear projector).
+Tolerances as tests/test_model_gpu.py: bf16 compute vs the fp32 reference fixture."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from egoscaler_b200 import synth
+from egoscaler_b200.config import TrajVLMConfig
+from egoscaler_b200.model import TrajPointLLMForCausalLM
+from egoscaler_b200 import decode  # noqa: F401
+from egoscaler_b200.trainer import Trainer
+from conftest import GOLDEN
+
+
+def _model(cfg, **kw):
+    m = TrajPointLLMForCausalLM(cfg, "cuda", **kw)
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    return m
+
+
+def _cmp_grad(name, g, gv, cos_min=0.999, rel_max=3e-2):
+    ref = gv[f"gradval/{name}"]
+    got = g.flatten().cpu()[torch.from_numpy(gv[f"gradidx/{name}"])].numpy()
+    cos = float((got * ref).sum() / (np.linalg.norm(got) * np.linalg.norm(ref) + 1e-30))
+    rel = float(np.linalg.norm(got - ref) / (np.linalg.norm(ref) + 1e-30))
+    assert cos >= cos_min and rel <= rel_max, (name, cos, rel)
+
+
+def test_unfrozen_language_model_gradients_and_step():
+    gv = np.load(os.path.join(GOLDEN, "traj_vlm_tiny_unfrozen_lm.npz"))
+    cfg = TrajVLMConfig.tiny()
+    m = _model(cfg, unfreeze_language_model=True)
+    m.train()
+    bt = synth.make_batch(cfg, 2, seed=1)
+    tr = Trainer(m, lr=1e-3)
+    tr.zero_grad()
+    loss = tr.forward_backward(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], int(gv["prompt_len"]),
+                               torch.from_numpy(gv["fps_start"]))
+    assert abs(float(loss) - float(gv["loss"])) <= 2e-2 * float(gv["loss"])
+    d, f = cfg.hidden_size, cfg.intermediate_size
+    n = 0
+    for li in range(cfg.num_hidden_layers):
+        pre = f"model.layers.{li}."
+        parts = {
+            pre + "self_attn.q_proj.weight": tr.wgrad["wqkv"][li][:d], pre + "self_attn.k_proj.weight": tr.wgrad["wqkv"][li][d:2 * d],
+            pre + "self_attn.v_proj.weight": tr.wgrad["wqkv"][li][2 * d:], pre + "self_attn.o_proj.weight": tr.wgrad["wo"][li],
+            pre + "mlp.gate_proj.weight": tr.wgrad["wgu"][li][:f], pre + "mlp.up_proj.weight": tr.wgrad["wgu"][li][f:],
+            pre + "mlp.down_proj.weight": tr.wgrad["wdown"][li], pre + "input_layernorm.weight": tr.wgrad["ln1"][li],
+            pre + "post_attention_layernorm.weight": tr.wgrad["ln2"][li]}
+        for name, g in parts.items():
+            assert f"gradnorm/{name}" in gv.files, name
+            _cmp_grad(name, g.contiguous(), gv, cos_min=0.998, rel_max=6e-2 if "layernorm" in name else 4e-2)
+            n += 1
+    for k in tr.names:
+        _cmp_grad(k, tr.grad[k], gv)
+        n += 1
+    assert n >= 27
+    # one AdamW step moves the LLM weights by ~lr (sign-like first step) and refreshes the derived operand copies
+    w0 = m.trunk.layers[0].wo.clone()
+    wT0 = m.trunk.layers[0].woT.clone()
+    tr.optimizer_step()
+    w1 = m.trunk.layers[0].wo
+    delta = (w1.float() - w0.float()).abs()
+    assert 2e-4 < float(delta.mean()) < 3e-3
+    assert torch.equal(m.trunk.layers[0].woT, w1.t().contiguous()) and not torch.equal(wT0, m.trunk.layers[0].woT)
+    sd = m.state_dict()
+    assert torch.equal(sd["model.layers.0.self_attn.o_proj.weight"], w1)
+    # loss goes down over a few steps on the same batch
+    losses = []
+    for _ in range(4):
+        losses.append(float(tr.train_step({**bt, "prompts": bt["prompts"]}, torch.from_numpy(gv["fps_start"]))))
+    assert losses[-1] < losses[0] < float(gv["loss"]) * 1.02
+
+
+def test_base_encoder_forward_grads_and_decode():
+    gv = np.load(os.path.join(GOLDEN, "traj_vlm_tiny_base_encoder.npz"))
+    cfg = TrajVLMConfig.tiny_base()
+    m = _model(cfg)
+    bt = synth.make_batch(cfg, 2, seed=1)
+    start = torch.from_numpy(gv["fps_start"])
+    with torch.no_grad():
+        feats = m.point_features(bt["pcrgbs"], start)
+    got = feats[:, ::16, ::8].float().cpu().numpy()
+    ref = gv["point_proj_sub"]
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 3e-2
+    out = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], return_dict=True, fps_start=start)
+    L = out.logits.float().cpu()
+    sub = L[:, gv["logit_rows"]][:, :, gv["logit_cols"]].numpy()
+    assert np.abs(sub - gv["logits_sub"]).max() <= 2e-2 * np.abs(gv["logits_sub"]).max()
+    m.train()
+    tr = Trainer(m, lr=2e-5)
+    tr.zero_grad()
+    loss = tr.forward_backward(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], int(gv["prompt_len"]), start)
+    assert abs(float(loss) - float(gv["loss"])) <= 2e-2 * float(gv["loss"])
+    assert set(tr.names) >= {"model.point_proj.weight", "model.point_proj.bias", "lm_head.weight", "model.embed_tokens.weight"}
+    for k in tr.names:
+        _cmp_grad(k, tr.grad[k], gv)
+    # greedy decode vs the reference's manual cached loop (fixture loop does not special-case EOS: suppress nothing,
+    # compare up to the first divergence / EOS, divergence only where the reference's top-2 margin is bf16 noise)
+    T = gv["greedy_ids"].shape[1]
+    g = m.generate(input_ids=bt["prompts"], attention_mask=bt["prompt_masks"], point_clouds=bt["pcrgbs"], max_length=T,
+                   do_sample=False, fps_start=start)
+    P = bt["prompts"].shape[1]
+    gen = g.sequences[:, P:].cpu().numpy()
+    refids = gv["greedy_ids"]
+    sl = torch.stack(g.scores, 1).cpu()[:, :, gv["logit_cols"]].numpy()
+    ref_sub = gv["greedy_step_logits_sub"]
+    for b in range(2):
+        n = min(gen.shape[1], refids.shape[1], sl.shape[1])
+        eos = np.nonzero(refids[b, :n] == 2)[0]
+        n = n if eos.size == 0 else int(eos[0]) + 1
+        agree = gen[b, :n] == refids[b, :n]
+        first_div = n if agree.all() else int(np.argmin(agree))
+        if first_div < n:                                      # a divergence is legitimate only inside bf16 logit noise
+            assert gv["greedy_step_top2gap"][b, first_div] < 5e-2, (b, first_div)
+        # the step logits are comparable while the generated prefixes agree (incl. the step that diverges)
+        k = min(first_div + 1, n)
+        mx = np.abs(ref_sub[b, :k]).max()
+        assert np.abs(sl[b, :k] - ref_sub[b, :k]).max() <= 3e-2 * mx, (b, k)
