@@ -19,6 +19,7 @@ import torch
 from . import ops
 from .encoder import projector_backward
 from .model import TrajPointLLMForCausalLM
+from .parallel import GradExchange
 
 
 def linear_warmup_lr(base_lr: float, step: int, warmup: int, total: int) -> float:
@@ -45,10 +46,8 @@ class Trainer:
         # LLM-layer tensors are optimised as the PACKED kernel operands (q|k|v and gate|up share one buffer each; AdamW is
         # element-wise, so this equals stepping the reference's separate parameters); everything else by parameter name.
         self.names: List[str] = [n for n in model.trainable_names() if not n.startswith("model.layers.")]
-        self.rank = 0
-        if world_size > 1:
-            import torch.distributed as dist
-            self.rank = dist.get_rank(process_group)
+        self.dp = GradExchange(world_size, process_group)
+        self.rank = self.dp.rank
         self.trunk_units = []               # (kind, layer, bf16 tensor); --unfreeze_language_model (model_arch.py:40-45)
         self.wgrad = None
         if model.unfreeze_language_model:
@@ -62,7 +61,7 @@ class Trainer:
             # ZeRO-1 (train.py:99-103): optimizer states of unit u live on rank u % world only
             self.t_master, self.t_m, self.t_v = {}, {}, {}
             for u, (k, li, t) in enumerate(self.trunk_units):
-                if u % self.world_size_safe(world_size) == self.rank:
+                if self.dp.owns(u):
                     self.t_master[u] = t.detach().float().clone()
                     self.t_m[u] = torch.zeros_like(self.t_master[u])
                     self.t_v[u] = torch.zeros_like(self.t_master[u])
@@ -73,10 +72,6 @@ class Trainer:
         self.v = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.last_loss: Optional[torch.Tensor] = None
-
-    @staticmethod
-    def world_size_safe(w: int) -> int:
-        return max(1, int(w))
 
     def zero_grad(self):
         for g in self.grad.values():
@@ -131,31 +126,19 @@ class Trainer:
         self.last_loss = loss
         return loss
 
-    # ------------------------------------------------------------------ data parallel
+    # ------------------------------------------------------------------ data parallel (parallel.GradExchange)
     def _reduce_async(self, names: List[str]):
-        if self.world <= 1:
-            return
-        import torch.distributed as dist
-        if not hasattr(self, "_pending"):
-            self._pending = []
-        for n in names:
-            self._pending.append(dist.all_reduce(self.grad[n], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+        self.dp.allreduce_async(self.grad[n] for n in names)
 
     def _reduce_layer_async(self, li: int):
         """ZeRO-1 gradient exchange of one LLM layer, started as soon as its backward has been queued: every unit is
-        sum-reduced to its owner rank only (the reduce-scatter half of an all-reduce), overlapping the remaining layers."""
-        import torch.distributed as dist
-        if not hasattr(self, "_pending"):
-            self._pending = []
+        sum-reduced to its owner rank only, overlapping the backward of the remaining layers."""
         for u, (k, l2, _) in enumerate(self.trunk_units):
             if l2 == li:
-                self._pending.append(dist.reduce(self.wgrad[k][li], dst=dist.get_global_rank(self.pg, u % self.world) if self.pg is not None
-                                                 else u % self.world, op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+                self.dp.reduce_to_owner_async(u, self.wgrad[k][li])
 
     def _wait_reduce(self):
-        for w in getattr(self, "_pending", []):
-            w.wait()
-        self._pending = []
+        self.dp.wait()
 
     # ------------------------------------------------------------------ optimizer
     def optimizer_step(self):
@@ -186,15 +169,7 @@ class Trainer:
                            self.step_count, scale)
                 if not t.is_contiguous():
                     t.copy_(self.t_master[u])
-        if self.world > 1:
-            import torch.distributed as dist
-            hs = []
-            for u, (k, li, t) in enumerate(self.trunk_units):
-                src = u % self.world
-                hs.append(dist.broadcast(t, src=dist.get_global_rank(self.pg, src) if self.pg is not None else src,
-                                         group=self.pg, async_op=True))
-            for h in hs:
-                h.wait()
+        self.dp.broadcast_from_owners([(u, t) for u, (k, li, t) in enumerate(self.trunk_units)])
         for lw in self.model.trunk.layers:
             lw.refresh_derived()
 
