@@ -114,4 +114,31 @@ int esb_knn_group(const float* pts, const float* centers, int B, int N, int C, i
     return knn_group(pts, centers, B, N, C, G, K, out_ld, nb_out, idx_out, ST(stream));
 }
 
+/* ---- trainable point encoder (--unfreeze_pc_encoder) */
+int esb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                      int64_t rows, int d, float eps, void* stream) {
+    return layernorm_bwd(dy, x, gamma, dres, dx, dgamma, dbeta, rows, d, eps, ST(stream));
+}
+int esb_colsum2_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, int64_t M, int N, float* out0, float* out1, void* stream) {
+    return colsum2_bf16(a, lda, b, ldb, M, N, out0, out1, ST(stream));
+}
+int esb_bn_coeffs(int mode, const float* sum0, const float* sum1, int64_t R, int C, const float* gamma, const float* beta, float eps,
+                  float momentum, float* mean_io, float* rstd_io, float* running_mean, float* running_var, float* A, float* B,
+                  float* Cc, float* dgamma, float* dbeta, void* stream) {
+    return bn_coeffs(mode, sum0, sum1, R, C, gamma, beta, eps, momentum, mean_io, rstd_io, running_mean, running_var, A, B, Cc, dgamma,
+                     dbeta, ST(stream));
+}
+int esb_affine_cols(const void* x, const void* y, const float* A, const float* B, const float* Cc, void* out, int64_t rows, int C,
+                    int relu, void* stream) {
+    return affine_cols(x, y, A, B, Cc, out, rows, C, relu, ST(stream));
+}
+int esb_relu_mask(const void* dy, const void* y, void* out, int64_t n, void* stream) { return relu_mask(dy, y, out, n, ST(stream)); }
+int esb_group_maxpool_bwd(const void* f, const void* dpool, const void* dcat, void* df, int64_t groups, int n, int C, void* stream) {
+    return group_maxpool_bwd(f, dpool, dcat, df, groups, n, C, ST(stream));
+}
+int esb_scale_rows_add(const void* x, const void* y, const float* scale, void* out, int64_t rows, int d, int64_t rows_per_batch,
+                       void* stream) {
+    return scale_rows_add(x, y, scale, out, rows, d, rows_per_batch, ST(stream));
+}
+
 }  // extern "C"

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dot_kernel(const AttnBwdParams p
 template <int HD>
 __global__ void __launch_bounds__(BWD_THREADS) attn_bwd_dkdv_kernel(const AttnBwdParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int TILE = 64 * HD * 2;
+    constexpr int TILE = 64 * tile_row_bytes<HD>();
     uint8_t* sK = smem;
     uint8_t* sV = smem + TILE;
     uint8_t* sQ = smem + 2 * TILE;          // 2 stages

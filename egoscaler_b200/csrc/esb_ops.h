@@ -73,6 +73,21 @@ int attn_decode(const void* q, long long q_bs, const void* k, const void* v, lon
                 long long o_bs, const uint8_t* kmask, long long kmask_ld, const int* len_ptr, int len_static, int B, int H,
                 int hd, float scale, cudaStream_t s);
 
+// encoder_train.cu (--unfreeze_pc_encoder)
+int layernorm_bwd(const void* dy, const void* x, const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                  long long rows, int d, float eps, cudaStream_t s);
+int colsum2_bf16(const void* a, long long lda, const void* b, long long ldb, long long M, int N, float* out0, float* out1,
+                 cudaStream_t s);
+int bn_coeffs(int mode, const float* sum0, const float* sum1, long long R, int C, const float* gamma, const float* beta, float eps,
+              float momentum, float* mean_io, float* rstd_io, float* running_mean, float* running_var, float* A, float* B, float* Cc,
+              float* dgamma, float* dbeta, cudaStream_t s);
+int affine_cols(const void* x, const void* y, const float* A, const float* B, const float* Cc, void* out, long long rows, int C,
+                int relu, cudaStream_t s);
+int relu_mask(const void* dy, const void* y, void* out, long long n, cudaStream_t s);
+int group_maxpool_bwd(const void* f, const void* dpool, const void* dcat, void* df, long long groups, int n, int C, cudaStream_t s);
+int scale_rows_add(const void* x, const void* y, const float* scale, void* out, long long rows, int d, long long rows_per_batch,
+                   cudaStream_t s);
+
 // pointcloud.cu
 int fps(const float* pts, int B, int N, int C, int G, const long long* start, float* centers, int* center_idx, void* centers_pad,
         int pad_ld, cudaStream_t s);

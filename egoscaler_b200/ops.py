@@ -481,3 +481,74 @@ def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: t
             _p(kmask), 0 if kmask is None else kmask.stride(0), B, H, L, L, hd, 1 if causal else 0, 0,
             float(scale if scale is not None else hd ** -0.5), _stream())
     return dqkv
+
+
+# ------------------------------------------------------------------------------------------------ trainable point encoder
+def layernorm_bwd(dy, x, gamma, dgamma=None, dbeta=None, dres=None, eps: float = 1e-5):
+    """nn.LayerNorm backward; ``x`` is the LayerNorm input.  Returns dx (+ dres); dgamma / dbeta fp32 are accumulated."""
+    _chk(dy, torch.bfloat16, "layernorm_bwd.dy"); _chk(x, torch.bfloat16, "layernorm_bwd.x"); _chk(gamma, torch.float32, "layernorm_bwd.gamma")
+    assert dy.is_contiguous() and x.is_contiguous()
+    rows, d = x.shape
+    dx = torch.empty_like(x)
+    _l.call("esb_layernorm_bwd", dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), _p(dres), dx.data_ptr(), _p(dgamma), _p(dbeta),
+            rows, d, float(eps), _stream())
+    return dx
+
+
+def colsum2(a, b, out0, out1):
+    """out0[c] += sum_r a[r,c]; out1[c] += sum_r a[r,c] * b[r,c] (b None: a*a)."""
+    _chk(a, torch.bfloat16, "colsum2.a")
+    M, N = a.shape
+    _l.call("esb_colsum2_bf16", a.data_ptr(), a.stride(0), _p(b), 0 if b is None else b.stride(0), M, N, out0.data_ptr(), _p(out1),
+            _stream())
+
+
+def bn_coeffs(mode: int, sum0, sum1, R: int, gamma, beta, mean, rstd, A, B, C, running_mean=None, running_var=None,
+              dgamma=None, dbeta=None, eps: float = 1e-5, momentum: float = 0.1):
+    _l.call("esb_bn_coeffs", mode, sum0.data_ptr(), sum1.data_ptr(), R, gamma.numel(), gamma.data_ptr(), _p(beta), float(eps),
+            float(momentum), mean.data_ptr(), rstd.data_ptr(), _p(running_mean), _p(running_var), A.data_ptr(), _p(B), C.data_ptr(),
+            _p(dgamma), _p(dbeta), _stream())
+
+
+def affine_cols(x, A, C, y=None, B=None, relu: bool = False, out=None):
+    """out[r,c] = act(A[c]*x[r,c] + B[c]*y[r,c] + C[c])."""
+    _chk(x, torch.bfloat16, "affine_cols.x")
+    assert x.is_contiguous() and (y is None or y.is_contiguous())
+    rows, Cn = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _l.call("esb_affine_cols", x.data_ptr(), _p(y), A.data_ptr(), _p(B), C.data_ptr(), out.data_ptr(), rows, Cn, 1 if relu else 0,
+            _stream())
+    return out
+
+
+def relu_mask(dy, y):
+    _chk(dy, torch.bfloat16, "relu_mask.dy"); _chk(y, torch.bfloat16, "relu_mask.y")
+    assert dy.is_contiguous() and y.is_contiguous() and dy.shape == y.shape
+    out = torch.empty_like(dy)
+    _l.call("esb_relu_mask", dy.data_ptr(), y.data_ptr(), out.data_ptr(), dy.numel(), _stream())
+    return out
+
+
+def group_maxpool_bwd(f, n: int, dpool=None, dcat=None):
+    """Backward of ops.group_maxpool: f [G*n, C]; dpool [G, C] (plain) or dcat [G*n, 2C] (concat form) -> df [G*n, C]."""
+    _chk(f, torch.bfloat16, "group_maxpool_bwd.f")
+    assert f.is_contiguous()
+    R, C = f.shape
+    df = torch.empty_like(f)
+    for t in (dpool, dcat):
+        if t is not None:
+            _chk(t, torch.bfloat16, "group_maxpool_bwd.d")
+            assert t.is_contiguous()
+    _l.call("esb_group_maxpool_bwd", f.data_ptr(), _p(dpool), _p(dcat), df.data_ptr(), R // n, n, C, _stream())
+    return df
+
+
+def scale_rows_add(y, scale, rows_per_batch: int, x=None):
+    """DropPath: x + scale[row // rows_per_batch] * y (x None: scale * y)."""
+    _chk(y, torch.bfloat16, "scale_rows_add.y"); _chk(scale, torch.float32, "scale_rows_add.scale")
+    assert y.is_contiguous() and (x is None or x.is_contiguous())
+    rows, d = y.shape
+    out = torch.empty_like(y)
+    _l.call("esb_scale_rows_add", _p(x), y.data_ptr(), scale.data_ptr(), out.data_ptr(), rows, d, rows_per_batch, _stream())
+    return out

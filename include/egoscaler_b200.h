@@ -216,6 +216,31 @@ int esb_fps(const float* pts, int B, int N, int C, int G, const int64_t* start, 
 int esb_knn_group(const float* pts, const float* centers, int B, int N, int C, int G, int K, int out_ld, void* nb_out,
                   int32_t* idx_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------ trainable point encoder
+ * Only used with --unfreeze_pc_encoder (model_arch.py:36-38,121-122): PointBERT then runs in train mode.
+ * nn.LayerNorm backward (point_encoder.py:58,64,142): x = LayerNorm input [rows,d] bf16; dx = dLN + dres (dres or NULL);
+ * dgamma/dbeta fp32 [d] are ACCUMULATED (or NULL). */
+int esb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                      int64_t rows, int d, float eps, void* stream);
+/* out0[c] += sum_r a[r,c]; out1[c] += sum_r a[r,c]*b[r,c] (b NULL: a*a).  BatchNorm1d batch statistics, dvae.py:196,202. */
+int esb_colsum2_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, int64_t M, int N, float* out0, float* out1, void* stream);
+/* Per-channel BatchNorm coefficients from those sums.  mode 0 (forward): y = A*z + C, saves mean/rstd, updates the running
+ * statistics (momentum, unbiased variance).  mode 1 (backward): dz = A*dy + B*z + C, dgamma/dbeta accumulated. */
+int esb_bn_coeffs(int mode, const float* sum0, const float* sum1, int64_t R, int C, const float* gamma, const float* beta, float eps,
+                  float momentum, float* mean_io, float* rstd_io, float* running_mean, float* running_var, float* A, float* B,
+                  float* Cc, float* dgamma, float* dbeta, void* stream);
+/* out[r,c] = act(A[c]*x[r,c] + B[c]*y[r,c] + C[c]); y/B may be NULL; relu=1 applies nn.ReLU.  bf16 [rows,C] contiguous. */
+int esb_affine_cols(const void* x, const void* y, const float* A, const float* B, const float* Cc, void* out, int64_t rows, int C,
+                    int relu, void* stream);
+/* nn.ReLU backward: out = y > 0 ? dy : 0 (y = ReLU output). */
+int esb_relu_mask(const void* dy, const void* y, void* out, int64_t n, void* stream);
+/* torch.max(dim) backward of the mini-PointNet pools (dvae.py:217-220), first arg-max receives the gradient.
+ * f [groups*n, C]; dpool [groups, C] (plain) XOR dcat [groups*n, 2C] (gradient of cat(global.expand, f)). */
+int esb_group_maxpool_bwd(const void* f, const void* dpool, const void* dcat, void* df, int64_t groups, int n, int C, void* stream);
+/* DropPath (timm, point_encoder.py:62,74-75): out = x + scale[row / rows_per_batch] * y; x NULL: out = scale * y (backward). */
+int esb_scale_rows_add(const void* x, const void* y, const float* scale, void* out, int64_t rows, int d, int64_t rows_per_batch,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

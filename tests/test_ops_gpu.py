@@ -106,7 +106,8 @@ def _attn_ref(q, k, v, causal, kmask, q_pos0=0):
     return torch.einsum("bhij,bjhe->bihe", p, v.float()).reshape(B, Lq, H * hd), torch.logsumexp(s, -1)
 
 
-@pytest.mark.parametrize("hd,H,L,causal", [(64, 4, 696, True), (128, 2, 200, True), (64, 6, 513, False), (128, 3, 64, True), (64, 2, 77, True)])
+@pytest.mark.parametrize("hd,H,L,causal", [(64, 4, 696, True), (128, 2, 200, True), (64, 6, 513, False), (128, 3, 64, True), (64, 2, 77, True),
+                                              (96, 12, 513, False), (96, 2, 130, True)])
 def test_attention_fwd_bwd(hd, H, L, causal):
     B, d = 2, H * hd
     qkv = rnd(B, L, 3, H, hd, seed=7)
@@ -228,3 +229,76 @@ def test_pool_transpose_colsum_copy():
     dst = torch.zeros(3, 5, 64, device="cuda", dtype=torch.bfloat16)
     ops.copy_rows(src[:, 7:12, :], dst)
     assert torch.equal(dst, src[:, 7:12])
+
+
+# ------------------------------------------------------------------ trainable point encoder kernels (encoder_train.cu)
+def test_layernorm_bwd():
+    rows, d = 1026, 384
+    x, dy, dres = rnd(rows, d, seed=1), rnd(rows, d, seed=2), rnd(rows, d, seed=3)
+    gamma = (torch.randn(d, device="cuda") * 0.3 + 1).float()
+    beta = torch.randn(d, device="cuda")
+    xf, gf, bf = x.float().requires_grad_(True), gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    y = F.layer_norm(xf, (d,), gf, bf, 1e-5)
+    y.backward(dy.float())
+    dg, db = torch.zeros(d, device="cuda"), torch.zeros(d, device="cuda")
+    dx = ops.layernorm_bwd(dy, x, gamma, dgamma=dg, dbeta=db, dres=dres)
+    close(dx, xf.grad + dres.float(), 1.5e-2)
+    close(dg, gf.grad, 5e-3)
+    close(db, bf.grad, 5e-3)
+
+
+def test_batchnorm_train_forward_backward():
+    """colsum2 + bn_coeffs + affine_cols + relu_mask == nn.BatchNorm1d(train) + ReLU and their autograd."""
+    R, C = 4096, 128
+    z = rnd(R, C, seed=4, scale=2.0)
+    dy = rnd(R, C, seed=5)
+    bn = torch.nn.BatchNorm1d(C).cuda().train()
+    with torch.no_grad():
+        bn.weight.copy_(torch.randn(C) * 0.2 + 1); bn.bias.copy_(torch.randn(C) * 0.1)
+    gamma, beta = bn.weight.detach().clone(), bn.bias.detach().clone()
+    rm, rv = bn.running_mean.clone(), bn.running_var.clone()
+    zf = z.float().requires_grad_(True)
+    yref = torch.relu(bn(zf))
+    yref.backward(dy.float())
+    f = lambda: torch.zeros(C, device="cuda")
+    s0, s1, mean, rstd, A, B, Cc = f(), f(), f(), f(), f(), f(), f()
+    ops.colsum2(z, None, s0, s1)
+    ops.bn_coeffs(0, s0, s1, R, gamma, beta, mean, rstd, A, None, Cc, running_mean=rm, running_var=rv)
+    y = ops.affine_cols(z, A, Cc, relu=True)
+    close(y, yref, 1e-2)
+    close(rm, bn.running_mean, 1e-3)
+    close(rv, bn.running_var, 1e-3)
+    dym = ops.relu_mask(dy, y)
+    t0, t1, dg, db = f(), f(), f(), f()
+    ops.colsum2(dym, z, t0, t1)
+    ops.bn_coeffs(1, t0, t1, R, gamma, None, mean, rstd, A, B, Cc, dgamma=dg, dbeta=db)
+    dz = ops.affine_cols(dym, A, Cc, y=z, B=B)
+    close(dz, zf.grad, 2e-2)
+    close(dg, bn.weight.grad, 1e-2)
+    close(db, bn.bias.grad, 1e-2)
+
+
+def test_group_maxpool_bwd_and_droppath():
+    G, n, C = 40, 32, 256
+    f = rnd(G * n, C, seed=6)
+    ff = f.float().view(G, n, C).requires_grad_(True)
+    # plain: max over n
+    dpool = rnd(G, C, seed=7)
+    ff.max(1)[0].backward(dpool.float())
+    df = ops.group_maxpool_bwd(f, n, dpool=dpool)
+    assert torch.equal(df.float().view(G, n, C), ff.grad)
+    # concat: cat(global.expand, f)
+    ff.grad = None
+    dcat = rnd(G * n, 2 * C, seed=8)
+    cat = torch.cat([ff.max(1, keepdim=True)[0].expand(-1, n, -1), ff], -1)
+    cat.backward(dcat.float().view(G, n, 2 * C))
+    df2 = ops.group_maxpool_bwd(f, n, dcat=dcat)
+    close(df2.view(G, n, C), ff.grad, 1e-2)
+    # DropPath scale: x + s[b] * y
+    B, L, d = 3, 513, 384
+    x, y = rnd(B * L, d, seed=9), rnd(B * L, d, seed=10)
+    sc = torch.tensor([0.0, 1.0 / 0.9, 1.0 / 0.9], device="cuda")
+    out = ops.scale_rows_add(y, sc, L, x=x)
+    ref = x.float().view(B, L, d) + sc[:, None, None] * y.float().view(B, L, d)
+    close(out.view(B, L, d), ref, 1e-2)
+    close(ops.scale_rows_add(y, sc, L).view(B, L, d), sc[:, None, None] * y.float().view(B, L, d), 1e-2)
