@@ -227,7 +227,7 @@ def golden_model(name="traj_vlm_tiny", batch=2, new_tokens=152):
 
 
 def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unfreeze_lm=False, batch=2, new_tokens=24,
-                   point="v12"):
+                   point="v12", unfreeze_pc=False):
     """Smaller fixtures for the other recipes of SURVEY 8d: (a) ``--unfreeze_language_model`` (model_arch.py:40-45):
     gradients of every LLM-layer tensor; (b) config E: the base PointBERT encoder yaml (trans 1152, 12 heads x 96,
     k=48, enc 512, single-Linear projector) with the default freezing: logits / loss / trainable grads / greedy ids."""
@@ -236,19 +236,31 @@ def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unf
     sd = synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True)
     m.load_state_dict(sd, strict=True)
     for p in m.model.point_backbone.parameters():
-        p.requires_grad = False
+        p.requires_grad = bool(unfreeze_pc)
     for p in m.model.layers.parameters():
         p.requires_grad = bool(unfreeze_lm)
     m.train()
     if not unfreeze_lm:
         m.model.layers.eval()
-    m.model.point_backbone.eval()
+    if not unfreeze_pc:
+        m.model.point_backbone.eval()                      # model_arch.py:121-122
     cfg = TrajVLMConfig.tiny() if point == "v12" else TrajVLMConfig.tiny_base()
     bt = synth.make_batch(cfg, batch, seed=1)
     ids, mask, pc = bt["tokens"], bt["attention_masks"], bt["pcrgbs"]
     P = bt["prompts"].shape[1]
     out = dict(fps_seed=np.int64(FPS_SEED), fps_start=_fps_start(pc.shape[1], batch).numpy(), prompt_len=np.int64(P),
                torch_version=np.array(torch.__version__), transformers_version=np.array(__import__("transformers").__version__))
+    if unfreeze_pc:
+        # the CPU-generator draws the train-mode encoder makes after torch.manual_seed(FPS_SEED): the FPS start
+        # (misc.py:52) and then one torch.rand((B,1,1)) per DropPath with rate > 0 (blocks 1..11, attention then MLP)
+        torch.manual_seed(FPS_SEED)
+        torch.randint(0, pc.shape[1], (batch,), dtype=torch.long)
+        depth = len(m.model.point_backbone.blocks.blocks)
+        du = torch.zeros(depth, 2, batch)
+        for j in range(1, depth):
+            for br in range(2):
+                du[j, br] = torch.rand((batch, 1, 1)).flatten()
+        out["drop_u"] = du.numpy()
     res = _ref_forward(m, ids, mask, pc)
     logits = res.logits
     lg = logits[:, P - 1:-1, :]
@@ -268,6 +280,14 @@ def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unf
         sel = torch.from_numpy(rng.choice(flat.numel(), min(2048, flat.numel()), replace=False)).long()
         out[f"gradidx/{k}"] = sel.numpy()
         out[f"gradval/{k}"] = flat[sel].numpy()
+    if unfreeze_pc:
+        enc = m.model.point_backbone.encoder
+        for nm, bn in (("first_conv.1", enc.first_conv[1]), ("second_conv.1", enc.second_conv[1])):
+            out[f"running_mean/{nm}"] = bn.running_mean.numpy().copy()       # after ONE train-mode forward (momentum 0.1)
+            out[f"running_var/{nm}"] = bn.running_var.numpy().copy()
+        np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
+        print(f"{name}.npz: loss={out['loss']:.6f} size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
+        return
     with torch.no_grad():
         torch.manual_seed(FPS_SEED)
         pf = m.model.point_backbone(pc)
@@ -301,6 +321,11 @@ if __name__ == "__main__":
     import sys
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "unfrozen_pc":
+        golden_variant("traj_vlm_tiny_unfrozen_pc", unfreeze_pc=True)
+        golden_variant("traj_vlm_tiny_base_unfrozen_pc", point_cfg_name="PointTransformer_base_8192point", point="base",
+                       unfreeze_pc=True)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "variants":
         golden_variant("traj_vlm_tiny_unfrozen_lm", unfreeze_lm=True)
         golden_variant("traj_vlm_tiny_base_encoder", point_cfg_name="PointTransformer_base_8192point", point="base")

@@ -39,6 +39,7 @@ class PointCfg:
     point_dims: int = 6
     proj_hidden: Tuple[int, ...] = (1024, 2048)
     use_max_pool: bool = False
+    drop_path_rate: float = 0.1         # both yaml files; active only when the encoder trains (--unfreeze_pc_encoder)
 
     @staticmethod
     def base() -> "PointCfg":
@@ -165,30 +166,41 @@ class _Mlp(nn.Module):
 
 
 class _Block(nn.Module):
-    """pointbert/point_encoder.py:58-76 (pre-LN; DropPath is identity in eval)."""
+    """pointbert/point_encoder.py:58-76 (pre-LN).  DropPath = timm 0.4.12 ``drop_path``: identity in eval or at rate 0
+    (nn.Identity, :62); in train mode ``x / keep * floor(keep + U[0,1))`` with one draw per sample.  ``u`` injects the
+    two uniform draws [2, B] of this block (attention branch, MLP branch); None draws them like timm does."""
 
-    def __init__(self, dim: int, heads: int):
+    def __init__(self, dim: int, heads: int, drop_path: float = 0.0):
         super().__init__()
         self.norm1 = nn.LayerNorm(dim)
         self.norm2 = nn.LayerNorm(dim)
         self.mlp = _Mlp(dim, int(dim * 4.0))
         self.attn = _Attn(dim, heads)
+        self.drop_path = float(drop_path)
 
-    def forward(self, x):
-        x = x + self.attn(self.norm1(x))
-        return x + self.mlp(self.norm2(x))
+    def _dp(self, y, u):
+        if self.drop_path == 0.0 or not self.training:
+            return y
+        keep = 1.0 - self.drop_path
+        r = torch.rand((y.shape[0], 1, 1), dtype=y.dtype) if u is None else u.reshape(-1, 1, 1).to(y.dtype)
+        return y.div(keep) * (keep + r).floor()
+
+    def forward(self, x, u=None):
+        x = x + self._dp(self.attn(self.norm1(x)), None if u is None else u[0])
+        return x + self._dp(self.mlp(self.norm2(x)), None if u is None else u[1])
 
 
 class _Blocks(nn.Module):
     """pointbert/point_encoder.py:79-98: ``x = block(x + pos)`` at every depth."""
 
-    def __init__(self, dim: int, depth: int, heads: int):
+    def __init__(self, dim: int, depth: int, heads: int, drop_path_rate: float = 0.0):
         super().__init__()
-        self.blocks = nn.ModuleList([_Block(dim, heads) for _ in range(depth)])
+        dpr = [v.item() for v in torch.linspace(0, drop_path_rate, depth)]            # point_encoder.py:134
+        self.blocks = nn.ModuleList([_Block(dim, heads, dpr[i]) for i in range(depth)])
 
-    def forward(self, x, pos):
-        for b in self.blocks:
-            x = b(x + pos)
+    def forward(self, x, pos, drop_u=None):
+        for i, b in enumerate(self.blocks):
+            x = b(x + pos, None if drop_u is None else drop_u[i])
         return x
 
 
@@ -203,7 +215,8 @@ class PointTransformer(nn.Module):
         self.cls_token = nn.Parameter(torch.zeros(1, 1, cfg.trans_dim))
         self.cls_pos = nn.Parameter(torch.randn(1, 1, cfg.trans_dim))
         self.pos_embed = nn.Sequential(nn.Linear(3, 128), nn.GELU(), nn.Linear(128, cfg.trans_dim))
-        self.blocks = _Blocks(cfg.trans_dim, cfg.depth, cfg.num_heads)
+        self.blocks = _Blocks(cfg.trans_dim, cfg.depth, cfg.num_heads, cfg.drop_path_rate)
+        self.drop_u: Optional[torch.Tensor] = None      # [depth, 2, B] injected DropPath uniforms (tests)
         self.norm = nn.LayerNorm(cfg.trans_dim)
 
     def forward(self, pts: torch.Tensor, fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -213,7 +226,7 @@ class PointTransformer(nn.Module):
         B = tok.size(0)
         x = torch.cat((self.cls_token.expand(B, -1, -1), tok), dim=1)               # :181
         pos = torch.cat((self.cls_pos.expand(B, -1, -1), self.pos_embed(center)), dim=1)
-        x = self.norm(self.blocks(x, pos))                                          # :184-185
+        x = self.norm(self.blocks(x, pos, self.drop_u))                             # :184-185
         if not self.cfg.use_max_pool:
             return x
         return torch.cat([x[:, 0], x[:, 1:].max(1)[0]], dim=-1).unsqueeze(1)        # :188

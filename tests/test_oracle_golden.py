@@ -228,3 +228,38 @@ def test_oracle_unfrozen_language_model_matches_reference():
 def test_oracle_base_encoder_matches_reference():
     """PointTransformer_base_8192point (trans 1152, 12 x 96, k=48, enc 512, Linear projector)."""
     _variant_check("traj_vlm_tiny_base_encoder", PointCfg.base(), TrajVLMConfig.tiny_base(), False, 5)
+
+
+@pytest.mark.parametrize("name,base", [("traj_vlm_tiny_unfrozen_pc", False), ("traj_vlm_tiny_base_unfrozen_pc", True)])
+def test_oracle_unfrozen_point_encoder_matches_reference(name, base):
+    """--unfreeze_pc_encoder (model_arch.py:36-38,121-122): encoder in TRAIN mode = BatchNorm batch statistics
+    (dvae.py:196,202) + DropPath (point_encoder.py:62,74-75,134); the fixture stores the reference's DropPath draws."""
+    gv = np.load(os.path.join(GOLDEN, name + ".npz"))
+    torch.manual_seed(0)
+    m = TrajVLMOracle(LlmCfg.tiny(), PointCfg.base() if base else PointCfg())
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    m.configure_trainable(unfreeze_pc_encoder=True)
+    m.eval()
+    m.model.point_backbone.train()
+    m.model.point_backbone.drop_u = torch.from_numpy(gv["drop_u"])
+    bt = synth.make_batch(TrajVLMConfig.tiny_base() if base else TrajVLMConfig.tiny(), 2, seed=1)
+    P = int(gv["prompt_len"])
+    logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=torch.from_numpy(gv["fps_start"]), training=True)
+    loss = train_loss(logits, bt["tokens"], P, 0)
+    loss.backward()
+    sub = logits.detach()[:, gv["logit_rows"]][:, :, gv["logit_cols"]].numpy()
+    np.testing.assert_allclose(sub, gv["logits_sub"], atol=3e-4, rtol=1e-4)
+    assert abs(loss.item() - float(gv["loss"])) < 1e-4
+    n = 0
+    for k, p in m.named_parameters():
+        if f"gradnorm/{k}" not in gv.files:
+            continue
+        ref = gv[f"gradval/{k}"]
+        got = p.grad.flatten()[torch.from_numpy(gv[f"gradidx/{k}"])].numpy()
+        np.testing.assert_allclose(got, ref, atol=1e-6 + 3e-3 * np.abs(ref).max(), rtol=3e-3, err_msg=k)
+        n += 1
+    assert n > 150                                            # all encoder tensors + the default trainable set
+    enc = m.model.point_backbone.encoder
+    for nm, bn in (("first_conv.1", enc.first_conv[1]), ("second_conv.1", enc.second_conv[1])):
+        np.testing.assert_allclose(bn.running_mean.numpy(), gv[f"running_mean/{nm}"], atol=1e-5, rtol=1e-4)
+        np.testing.assert_allclose(bn.running_var.numpy(), gv[f"running_var/{nm}"], atol=1e-5, rtol=1e-4)
