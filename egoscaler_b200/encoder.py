@@ -141,8 +141,9 @@ def projector_forward(pp: PackedProjector, feats: torch.Tensor, save: Optional[l
 
 
 def projector_backward(pp: PackedProjector, saved: list, dout: torch.Tensor, grads_w: List[torch.Tensor],
-                       grads_b: List[torch.Tensor]) -> None:
-    """dout [R, d] bf16.  Accumulates fp32 dW / db into ``grads_w`` / ``grads_b`` (encoder is frozen: no dfeats)."""
+                       grads_b: List[torch.Tensor], need_input_grad: bool = False) -> Optional[torch.Tensor]:
+    """dout [R, d] bf16.  Accumulates fp32 dW / db into ``grads_w`` / ``grads_b``.  The gradient w.r.t. the encoder
+    output is only computed (and returned) when the encoder trains (--unfreeze_pc_encoder)."""
     wT = pp.transposed()
     n = len(pp.w)
     dz = dout
@@ -153,5 +154,6 @@ def projector_backward(pp: PackedProjector, saved: list, dout: torch.Tensor, gra
         ops.colsum(dz, grads_b[i])
         # dW[N,K] = dz^T [N,R] . x [R,K]  ->  A = dz^T (rows N, contraction R), B = x^T (rows K, contraction R)
         ops.gemm(ops.transpose(dz), ops.transpose(x), out=grads_w[i], accumulate=True)
-        if i > 0:
+        if i > 0 or need_input_grad:
             dz = ops.gemm(dz, wT[i])          # dx[R,K] = dz[R,N] . W[N,K] ; wT is [K,N] (contraction-major)
+    return dz if need_input_grad else None

@@ -88,16 +88,19 @@ class TrajPointLLMForCausalLM(ParamTree):
 
     def train(self, mode: bool = True):
         """model_arch.py:110-124: frozen sub-modules stay in eval.  The CUDA path has no dropout and uses BatchNorm
-        running statistics only, which is exactly the reference behaviour while the encoder is frozen."""
+        running statistics only, which is exactly the reference behaviour while the encoder is frozen.  With
+        --unfreeze_pc_encoder the trainer routes the encoder through encoder_train.py (batch statistics + DropPath)."""
         super().train(mode)
-        if mode and self.unfreeze_pc_encoder:
-            raise NotImplementedError("training the point encoder (--unfreeze_pc_encoder) is not built yet")
         return self
 
     def trainable_names(self) -> List[str]:
         return [n for n, q in self.named_parameters() if q.requires_grad]
 
     # ------------------------------------------------------------------ operand packing
+    def repack_encoder(self):
+        """Rebuild only the point-encoder operands (after an optimizer step on its parameters)."""
+        self._packed_encoder = PackedPointEncoder(self.cfg, self.named())
+
     def repack(self):
         """(Re)build kernel operands from the parameters: call after load_state_dict / optimizer steps on the
         projector / lm_head.  Trunk weights are the parameters themselves (views), nothing is copied."""
@@ -141,7 +144,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         return torch.randint(0, n_points, (batch,), dtype=torch.long)
 
     def point_features(self, point_clouds: torch.Tensor, fps_start: Optional[torch.Tensor] = None,
-                       save: Optional[list] = None) -> torch.Tensor:
+                       save: Optional[list] = None, enc_train=None) -> torch.Tensor:
         """pointllm.py:124-129: point_backbone -> point_proj.  [B,N,C] fp32 -> [B, Np, d] bf16."""
         if self._packed_encoder is None:
             self.repack()
@@ -150,7 +153,11 @@ class TrajPointLLMForCausalLM(ParamTree):
             fps_start = self.draw_fps_start(N, B)
         fps_start = fps_start.to(self.dev)
         pts = point_clouds.to(self.dev, torch.float32)
-        tok = point_encoder_forward(self._packed_encoder, pts, fps_start)
+        if enc_train is not None:          # --unfreeze_pc_encoder: train-mode encoder, activations kept for its backward
+            from .encoder_train import train_forward
+            tok, enc_train["saved"] = train_forward(enc_train["pk"], pts, fps_start, enc_train.get("drop_u"))
+        else:
+            tok = point_encoder_forward(self._packed_encoder, pts, fps_start)
         Np, T = tok.shape[1], tok.shape[2]
         out = projector_forward(self._packed_proj, tok.view(B * Np, T), save)
         return out.view(B, Np, self.cfg.hidden_size)
@@ -190,7 +197,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         return attention_mask.to(dev).to(torch.uint8).contiguous()
 
     def hidden_states(self, input_ids, attention_mask=None, point_clouds=None, fps_start=None, cache: Optional[KVCache] = None,
-                      saved=None, proj_saved=None, splice_pos=None, pos_dev=None):
+                      saved=None, proj_saved=None, splice_pos=None, pos_dev=None, enc_train=None):
         """Everything up to (not including) the final norm.  Returns (hidden [B*L, d], splice_pos)."""
         input_ids = input_ids.to(self.dev)
         B, L = input_ids.shape
@@ -199,7 +206,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         if (L != 1 or self.training) and point_clouds is not None:       # pointllm.py:112
             if splice_pos is None:                                       # host-side checks first: the (async)
                 splice_pos = self.splice_positions(input_ids)            # encoder launches then queue without a sync
-            feats = self.point_features(point_clouds, fps_start, proj_saved)
+            feats = self.point_features(point_clouds, fps_start, proj_saved, enc_train)
         x = ops.embed_splice(input_ids, self.model.embed_tokens.weight.detach(), feats, splice_pos if feats is not None else None,
                              self.point_backbone_config["point_token_len"])
         h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved, pos_dev)

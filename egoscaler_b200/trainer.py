@@ -35,9 +35,11 @@ class Trainer:
     def __init__(self, model: TrajPointLLMForCausalLM, lr: float = 2e-5, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.01, warmup_steps: int = 0, total_steps: int = 0, process_group=None,
                  world_size: int = 1):
-        if model.unfreeze_pc_encoder:
-            raise NotImplementedError("--unfreeze_pc_encoder (BatchNorm batch statistics + DropPath in the encoder backward) is not built")
         self.model = model
+        self.enc_train = None               # --unfreeze_pc_encoder (model_arch.py:36-38,121-122): encoder_train.py
+        if model.unfreeze_pc_encoder:
+            from .encoder_train import TrainPointEncoder
+            self.enc_train = {"pk": TrainPointEncoder(model.cfg, model.named())}
         self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
         self.warmup, self.total = warmup_steps, total_steps
         self.pg, self.world = process_group, world_size
@@ -83,7 +85,7 @@ class Trainer:
 
     # ------------------------------------------------------------------ forward + backward
     def forward_backward(self, tokens: torch.Tensor, attention_masks: torch.Tensor, pcrgbs: torch.Tensor, prompt_len: int,
-                         fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
+                         fps_start: Optional[torch.Tensor] = None, drop_u: Optional[torch.Tensor] = None) -> torch.Tensor:
         m, cfg = self.model, self.model.cfg
         dev = m.dev
         tokens = tokens.to(dev)
@@ -93,7 +95,10 @@ class Trainer:
         n_point = m.point_backbone_config["point_token_len"]
         kmask = m._kmask(attention_masks, dev)
         saved, proj_saved = [], []
-        h, splice_pos = m.hidden_states(tokens, attention_masks, pcrgbs, fps_start, None, saved, proj_saved)
+        if self.enc_train is not None:
+            self.enc_train["drop_u"] = drop_u               # injected DropPath uniforms [depth, 2, B] (None: drawn on device)
+        h, splice_pos = m.hidden_states(tokens, attention_masks, pcrgbs, fps_start, None, saved, proj_saved,
+                                        enc_train=self.enc_train)
         # ---- head: rows P-1 .. L-2 only (train.py:174)
         hs = torch.empty(B, Tn, d, device=dev, dtype=torch.bfloat16)
         ops.copy_rows(h.view(B, L, d)[:, P - 1:L - 1, :], hs)
@@ -120,9 +125,13 @@ class Trainer:
         ops.embed_splice_bwd(tokens, dx, splice_pos, n_point, self.grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id)
         pw = [w for w, _ in m.projector_params()]
         pb = [b for _, b in m.projector_params()]
-        projector_backward(m._packed_proj, proj_saved, dfeats.view(B * n_point, d), [self.grad[n] for n in pw],
-                           [self.grad[n] for n in pb])
+        dtok = projector_backward(m._packed_proj, proj_saved, dfeats.view(B * n_point, d), [self.grad[n] for n in pw],
+                                  [self.grad[n] for n in pb], need_input_grad=self.enc_train is not None)
         self._reduce_async(["model.embed_tokens.weight"] + pw + pb)
+        if self.enc_train is not None:
+            from .encoder_train import train_backward
+            train_backward(self.enc_train["pk"], self.enc_train.pop("saved"), dtok, self.grad)
+            self._reduce_async([n for n in self.names if n.startswith("model.point_backbone.")])
         self.last_loss = loss
         return loss
 
@@ -158,6 +167,9 @@ class Trainer:
         self.model._lm_head_T = None
         self.model._lm_head_tiled = None
         self.model._packed_proj.refresh()
+        if self.enc_train is not None:
+            self.enc_train["pk"].refresh()
+            self.model.repack_encoder()
 
     def _trunk_step(self, lr: float, scale: float):
         """AdamW on the LLM-layer units this rank owns, then (N > 1) broadcast of the updated bf16 weights from their
@@ -173,10 +185,10 @@ class Trainer:
         for lw in self.model.trunk.layers:
             lw.refresh_derived()
 
-    def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None, drop_u: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration of train.py:157-184 on a collate_fn-shaped batch (dataset.py:184-194)."""
         self.zero_grad()
         loss = self.forward_backward(batch["tokens"], batch["attention_masks"], batch["pcrgbs"], batch["prompts"].shape[1],
-                                     fps_start)
+                                     fps_start, drop_u)
         self.optimizer_step()
         return loss

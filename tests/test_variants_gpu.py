@@ -123,3 +123,53 @@ def test_base_encoder_forward_grads_and_decode():
         k = min(first_div + 1, n)
         mx = np.abs(ref_sub[b, :k]).max()
         assert np.abs(sl[b, :k] - ref_sub[b, :k]).max() <= 3e-2 * mx, (b, k)
+
+
+@pytest.mark.parametrize("name,base", [("traj_vlm_tiny_unfrozen_pc", False), ("traj_vlm_tiny_base_unfrozen_pc", True)])
+def test_unfrozen_point_encoder_gradients_and_step(name, base):
+    """--unfreeze_pc_encoder: train-mode encoder (BatchNorm batch statistics, DropPath with the reference's own draws
+    injected) forward + hand-written backward vs the gradients of the real reference."""
+    gv = np.load(os.path.join(GOLDEN, name + ".npz"))
+    cfg = TrajVLMConfig.tiny_base() if base else TrajVLMConfig.tiny()
+    m = _model(cfg, unfreeze_pc_encoder=True)
+    m.train()
+    bt = synth.make_batch(cfg, 2, seed=1)
+    tr = Trainer(m, lr=1e-4)
+    tr.zero_grad()
+    start, du = torch.from_numpy(gv["fps_start"]), torch.from_numpy(gv["drop_u"])
+    loss = tr.forward_backward(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], int(gv["prompt_len"]), start, drop_u=du)
+    assert abs(float(loss) - float(gv["loss"])) <= 2e-2 * float(gv["loss"])
+    worst = {}
+    n_enc = 0
+    for k in tr.names:
+        assert f"gradnorm/{k}" in gv.files, k
+        ref = gv[f"gradval/{k}"]
+        got = tr.grad[k].flatten().cpu()[torch.from_numpy(gv[f"gradidx/{k}"])].numpy()
+        n_enc += k.startswith("model.point_backbone.")
+        if float(gv[f"gradnorm/{k}"]) < 1e-6:
+            # biases in front of a BatchNorm on batch statistics have a structurally ZERO gradient (the reference holds
+            # 1e-7 round-off there): ours must be zero up to bf16 round-off of the column sums
+            wn = float(gv["gradnorm/" + k.replace(".bias", ".weight")])
+            assert float(tr.grad[k].norm()) <= 5e-3 * wn, (k, float(tr.grad[k].norm()), wn)
+            continue
+        cos = float((got * ref).sum() / (np.linalg.norm(got) * np.linalg.norm(ref) + 1e-30))
+        rel = float(np.linalg.norm(got - ref) / (np.linalg.norm(ref) + 1e-30))
+        worst[k] = (cos, rel)
+    bad = {k: v for k, v in worst.items() if v[0] < 0.99 or v[1] > 0.12}
+    assert not bad, bad
+    # the bulk must be tight: bf16 activations through 12 blocks + batch-norm statistics
+    cosv = np.array([v[0] for v in worst.values()])
+    assert np.median(cosv) > 0.999 and n_enc > 150
+    # BatchNorm running statistics after one train-mode forward (momentum 0.1, unbiased variance)
+    sd = m.state_dict()
+    for nm in ("first_conv.1", "second_conv.1"):
+        for st in ("running_mean", "running_var"):
+            ref = gv[f"{st}/{nm}"]
+            got = sd[f"model.point_backbone.encoder.{nm}.{st}"].float().cpu().numpy()
+            assert np.abs(got - ref).max() <= 2e-2 * np.abs(ref).max() + 1e-4, (nm, st)
+    # optimizer step updates encoder parameters and the eval-mode packed operands; loss decreases on the same batch
+    w0 = sd["model.point_backbone.blocks.blocks.3.mlp.fc1.weight"].clone()
+    tr.optimizer_step()
+    assert not torch.equal(m.state_dict()["model.point_backbone.blocks.blocks.3.mlp.fc1.weight"], w0)
+    losses = [float(tr.train_step(bt, start, drop_u=du)) for _ in range(4)]
+    assert losses[-1] < losses[0]
