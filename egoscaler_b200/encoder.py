@@ -93,8 +93,6 @@ def point_encoder_forward(pk: PackedPointEncoder, pts: torch.Tensor, fps_start: 
     ops.copy_rows(pk.cls_pos.expand(B, 1, T), pos[:, :1, :])
     x2 = x.view(B * Np, T)
     pos2 = pos.view(B * Np, T)
-    if cfg.use_max_pool:
-        raise NotImplementedError("use_max_pool variant (point_encoder.py:186-189) is not built yet")
     for blk in pk.blocks:                                                             # point_encoder.py:95-98, 58-76
         y = ops.layernorm(x2, blk["n1_g"], blk["n1_b"], add=pos2, sum_out=x2)         # x <- x + pos ; y = LN1(x)
         qkv = ops.gemm(y, blk["qkv_w"]).view(B, Np, 3, H, hd)
@@ -103,8 +101,17 @@ def point_encoder_forward(pk: PackedPointEncoder, pts: torch.Tensor, fps_start: 
         y = ops.layernorm(x1, blk["n2_g"], blk["n2_b"])
         hmid = ops.gemm(y, blk["fc1_w"], bias=blk["fc1_b"], act=ops.ACT_GELU)
         x2 = ops.gemm(hmid, blk["fc2_w"], bias=blk["fc2_b"], residual=x1)
-    out = ops.layernorm(x2, pk.norm_g, pk.norm_b)
-    return out.view(B, Np, T)
+    out = ops.layernorm(x2, pk.norm_g, pk.norm_b).view(B, Np, T)
+    if not cfg.use_max_pool:
+        return out
+    # point_encoder.py:186-189: one token per cloud = cat(cls feature, max over the G group tokens)  [B, 1, 2T]
+    rest = torch.empty(B, G, T, device=pts.device, dtype=torch.bfloat16)
+    ops.copy_rows(out[:, 1:, :], rest)
+    mx = ops.group_maxpool(rest.view(B * G, T), G, concat=False)
+    res = torch.empty(B, 1, 2 * T, device=pts.device, dtype=torch.bfloat16)
+    ops.copy_rows(out[:, :1, :], res[:, :, :T])
+    ops.copy_rows(mx.view(B, 1, T), res[:, :, T:])
+    return res
 
 
 class PackedProjector:

@@ -173,3 +173,42 @@ def test_unfrozen_point_encoder_gradients_and_step(name, base):
     assert not torch.equal(m.state_dict()["model.point_backbone.blocks.blocks.3.mlp.fc1.weight"], w0)
     losses = [float(tr.train_step(bt, start, drop_u=du)) for _ in range(4)]
     assert losses[-1] < losses[0]
+
+
+def test_use_max_pool_branch_matches_oracle():
+    """point_encoder.py:186-189 (``use_max_pool``: one point token of 2*trans_dim = cat(cls, max over groups)); no shipped
+    yaml enables it, so this is a functional check against the oracle restatement on the same weights."""
+    import dataclasses
+    from oracle.traj_vlm import LlmCfg, PointCfg, TrajVLMOracle, train_loss
+    pc = dataclasses.replace(TrajVLMConfig.tiny().point, use_max_pool=True)
+    cfg = dataclasses.replace(TrajVLMConfig.tiny(), point=pc)
+    assert cfg.point.point_token_len == 1
+    m = _model(cfg)
+    torch.manual_seed(0)
+    om = TrajVLMOracle(LlmCfg.tiny(), PointCfg(use_max_pool=True))
+    sd = synth.det_state_dict(om.state_dict(), seed=0, round_bf16=True)
+    om.load_state_dict(sd, strict=True)
+    m.load_state_dict(sd, strict=True)
+    om.configure_trainable()
+    om.eval()
+    bt = synth.make_batch(cfg, 2, seed=1)
+    assert int((bt["tokens"][0] == 32000).sum()) == 1
+    start = torch.zeros(2, dtype=torch.long)
+    P = bt["prompts"].shape[1]
+    ref = om(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=start, training=True)
+    ref_loss = train_loss(ref, bt["tokens"], P, 0)
+    ref_loss.backward()
+    out = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], return_dict=True, fps_start=start)
+    L = out.logits.float().cpu()
+    assert L.shape == ref.shape
+    assert float((L - ref.detach()).abs().max()) <= 2e-2 * float(ref.detach().abs().max())
+    m.train()
+    tr = Trainer(m, lr=2e-5)
+    tr.zero_grad()
+    loss = tr.forward_backward(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], P, start)
+    assert abs(float(loss) - float(ref_loss)) <= 2e-2 * float(ref_loss)
+    named = dict(om.named_parameters())
+    for k in tr.names:
+        g, r = tr.grad[k].flatten().cpu().numpy(), named[k].grad.flatten().numpy()
+        cos = float((g * r).sum() / (np.linalg.norm(g) * np.linalg.norm(r) + 1e-30))
+        assert cos >= 0.999, (k, cos)
