@@ -39,16 +39,23 @@ def parse():
     ap.add_argument("--decode-only", action="store_true", help="profiling aid: build the model and run only the decode measurement")
     ap.add_argument("--decode-batch", type=int, default=32, help="sequences per GPU (BASELINE configs[3]: 256 / 8 GPUs)")
     ap.add_argument("--cpu-budget-s", type=float, default=200.0)
+    ap.add_argument("--encoder", default="v12", choices=["v12", "base"],
+                    help="point encoder yaml: v12 = PointTransformer_8192point_2layer (default), base = PointTransformer_base_8192point "
+                         "(BASELINE configs[4], SURVEY 8d config E)")
+    ap.add_argument("--recipe", default="default", choices=["default", "unfreeze_lm", "unfreeze_pc"],
+                    help="freezing recipe of model_arch.py:33-51: default, --unfreeze_language_model, --unfreeze_pc_encoder")
     return ap.parse_args()
 
 
-def workload_name(cfgname, B):
+def workload_name(cfgname, B, encoder="v12", recipe="default"):
     if cfgname == "full":
-        return f"full-size traj-VLM bf16 training step (LLaMA-7B dims, PointBERT v1.2, B={B}/GPU, L=696, P=544, default freezing)"
+        enc = "PointBERT v1.2" if encoder == "v12" else "PointBERT base (1152-d, k=48)"
+        rec = {"default": "default freezing", "unfreeze_lm": "--unfreeze_language_model", "unfreeze_pc": "--unfreeze_pc_encoder"}[recipe]
+        return f"full-size traj-VLM bf16 training step (LLaMA-7B dims, {enc}, B={B}/GPU, L=696, P=544, {rec})"
     return f"tiny traj-VLM training step (d=256, 2 layers, B={B}/GPU, L=696)"
 
 
-def flops_per_sample_train(cfg, L=696, T=152):
+def flops_per_sample_train(cfg, L=696, T=152, recipe="default"):
     """forward + data-gradients through the trunk/attention, head on T rows fwd+dgrad+wgrad, projector
     fwd+dgrad+wgrad, encoder forward only."""
     d, f, n, V = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers, cfg.vocab_size
@@ -61,6 +68,10 @@ def flops_per_sample_train(cfg, L=696, T=152):
     proj = sum(2 * Np * a * b for a, b in zip(dims[:-1], dims[1:]))
     enc = 2 * Np * p.depth * 12 * p.trans_dim ** 2 + 4 * Np * Np * p.trans_dim * p.depth \
         + 2 * p.num_group * p.group_size * (p.point_dims * 128 + 128 * 256 + 512 * 512 + 512 * p.encoder_dims)
+    if recipe == "unfreeze_lm":                   # + weight gradients of the trunk (attention backward counted 2x forward)
+        return 3 * (lin + att) + 3 * (head + proj) + enc
+    if recipe == "unfreeze_pc":                   # + data and weight gradients of the encoder
+        return 2 * (lin + att) + 3 * (head + proj) + 3 * enc
     return 2 * (lin + att) + 3 * (head + proj) + enc
 
 
@@ -136,12 +147,12 @@ class GemmTimer:
 
 
 # ------------------------------------------------------------------------------------------------ our arm
-def build_model(torch, cfg, device):
+def build_model(torch, cfg, device, **model_kw):
     """Random-init weights of the named architecture (no checkpoint is available offline): N(0, 0.02) for the LLM /
     embeddings / head (HF initializer_range), fan-in scaled for the point encoder and projector, identity norms."""
     from egoscaler_b200.model import TrajPointLLMForCausalLM
     from egoscaler_b200 import decode  # noqa: F401
-    m = TrajPointLLMForCausalLM(cfg, device)
+    m = TrajPointLLMForCausalLM(cfg, device, **model_kw)
     g = torch.Generator(device=device).manual_seed(0)
     with torch.no_grad():
         for name, p in list(m.named_parameters()) + list(m.named_buffers()):
@@ -183,9 +194,13 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    cfg = TrajVLMConfig.full() if args.config == "full" else TrajVLMConfig.tiny()
+    if args.config == "full":
+        cfg = TrajVLMConfig.full() if args.encoder == "v12" else TrajVLMConfig.full_base()
+    else:
+        cfg = TrajVLMConfig.tiny() if args.encoder == "v12" else TrajVLMConfig.tiny_base()
     B = args.batch
-    model = build_model(torch, cfg, dev)
+    model = build_model(torch, cfg, dev, unfreeze_language_model=args.recipe == "unfreeze_lm",
+                        unfreeze_pc_encoder=args.recipe == "unfreeze_pc")
     if args.decode_only:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         d = decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks)
@@ -270,7 +285,7 @@ def run_b200(args):
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": round(ms_res / args.steps, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic (collate_fn-shaped batches, random-init weights)",
-        "config": {"workload": workload_name(args.config, B), "per_gpu_batch": B, "global_batch": B * world, "seq_len": L,
+        "config": {"workload": workload_name(args.config, B, args.encoder, args.recipe), "per_gpu_batch": B, "global_batch": B * world, "seq_len": L,
                    "prompt_len": P, "parallelism": f"dp{world}", "l2": "working set (13.5 GB of weights per pass) >> 126 MB L2"},
         "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                 "ms_per_step": round(ms_e2e / args.steps, 3)},
@@ -280,7 +295,7 @@ def run_b200(args):
                      "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": gemm_traffic(), "peak_source": peak_src,
                      "launches_per_step": timer.n // args.steps, "gemm_ms_per_step": round(gemm_ms / args.steps, 3),
                      "gemm_share_of_step": round(gemm_ms / ms_res, 4),
-                     "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
+                     "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P, args.recipe) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
         "loss": round(float(loss_res), 4),
     }
     if not args.no_decode:
