@@ -47,38 +47,54 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const __nv_bfl
     const __nv_bfloat16* vb = v + b * kv_bs + static_cast<long long>(h) * HD + sub * EPL;
     const uint8_t* km = kmask ? kmask + b * kmask_ld : nullptr;
 
-    for (int j0 = 0; j0 < Lk; j0 += DEC_GROUPS) {        // uniform trip count: the shuffles below need every lane
-        const bool in_range = (j0 + grp) < Lk;
-        const int j = in_range ? (j0 + grp) : (Lk - 1);
-        const bool ok = in_range && (km ? (km[j] != 0) : true);   // uniform over the 8 lanes of a group
-        float dot = 0.0f;
-        uint4 vv[VPL];
+    // DEC_UNROLL keys per group per trip: all K/V vectors of the trip are requested before the first one is consumed, which
+    // doubles the bytes in flight per thread (the kernel is a pure HBM stream: 2 * Lk * d * 2 B per sequence per layer).
+    constexpr int DEC_UNROLL = 2;
+    for (int j0 = 0; j0 < Lk; j0 += DEC_GROUPS * DEC_UNROLL) {   // uniform trip count: the shuffles below need every lane
+        uint4 ku[DEC_UNROLL][VPL], vu[DEC_UNROLL][VPL];
+        bool okv[DEC_UNROLL];
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-            const uint4 u = __ldg(reinterpret_cast<const uint4*>(kb + static_cast<long long>(j) * kv_rs + i * 8));
-            vv[i] = __ldg(reinterpret_cast<const uint4*>(vb + static_cast<long long>(j) * kv_rs + i * 8));
-            const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-            dot += qv[i * 8 + 0] * a.x + qv[i * 8 + 1] * a.y + qv[i * 8 + 2] * bb.x + qv[i * 8 + 3] * bb.y +
-                   qv[i * 8 + 4] * c.x + qv[i * 8 + 5] * c.y + qv[i * 8 + 6] * d.x + qv[i * 8 + 7] * d.y;
+        for (int u = 0; u < DEC_UNROLL; ++u) {
+            const int jj = j0 + u * DEC_GROUPS + grp;
+            const bool in_range = jj < Lk;
+            const int j = in_range ? jj : (Lk - 1);
+            okv[u] = in_range && (km ? (km[j] != 0) : true);       // uniform over the 8 lanes of a group
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+                ku[u][i] = __ldg(reinterpret_cast<const uint4*>(kb + static_cast<long long>(j) * kv_rs + i * 8));
+                vu[u][i] = __ldg(reinterpret_cast<const uint4*>(vb + static_cast<long long>(j) * kv_rs + i * 8));
+            }
         }
-        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
-        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
-        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
-        if (!ok) continue;
-        const float sc = dot * scale;
-        const float mn = fmaxf(m, sc);
-        const float corr = __expf(m - mn);            // m = -inf -> 0
-        const float pr = __expf(sc - mn);
-        // the reference rounds P to bf16 before P@V (softmax(...).to(q.dtype) @ V); normalisation happens after here
-        l = l * corr + pr;
-        m = mn;
 #pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-            const float2 a = unpack_bf16x2(vv[i].x), bb = unpack_bf16x2(vv[i].y), c = unpack_bf16x2(vv[i].z), d = unpack_bf16x2(vv[i].w);
-            acc[i * 8 + 0] = acc[i * 8 + 0] * corr + pr * a.x; acc[i * 8 + 1] = acc[i * 8 + 1] * corr + pr * a.y;
-            acc[i * 8 + 2] = acc[i * 8 + 2] * corr + pr * bb.x; acc[i * 8 + 3] = acc[i * 8 + 3] * corr + pr * bb.y;
-            acc[i * 8 + 4] = acc[i * 8 + 4] * corr + pr * c.x; acc[i * 8 + 5] = acc[i * 8 + 5] * corr + pr * c.y;
-            acc[i * 8 + 6] = acc[i * 8 + 6] * corr + pr * d.x; acc[i * 8 + 7] = acc[i * 8 + 7] * corr + pr * d.y;
+        for (int u = 0; u < DEC_UNROLL; ++u) {
+            float dot = 0.0f;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+                const uint4 w = ku[u][i];
+                const float2 a = unpack_bf16x2(w.x), bb = unpack_bf16x2(w.y), c = unpack_bf16x2(w.z), d = unpack_bf16x2(w.w);
+                dot += qv[i * 8 + 0] * a.x + qv[i * 8 + 1] * a.y + qv[i * 8 + 2] * bb.x + qv[i * 8 + 3] * bb.y +
+                       qv[i * 8 + 4] * c.x + qv[i * 8 + 5] * c.y + qv[i * 8 + 6] * d.x + qv[i * 8 + 7] * d.y;
+            }
+            dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+            dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+            dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+            if (!okv[u]) continue;
+            const float sc = dot * scale;
+            const float mn = fmaxf(m, sc);
+            const float corr = __expf(m - mn);            // m = -inf -> 0
+            const float pr = __expf(sc - mn);
+            // the reference rounds P to bf16 before P@V (softmax(...).to(q.dtype) @ V); normalisation happens after here
+            l = l * corr + pr;
+            m = mn;
+#pragma unroll
+            for (int i = 0; i < VPL; ++i) {
+                const uint4 w = vu[u][i];
+                const float2 a = unpack_bf16x2(w.x), bb = unpack_bf16x2(w.y), c = unpack_bf16x2(w.z), d = unpack_bf16x2(w.w);
+                acc[i * 8 + 0] = acc[i * 8 + 0] * corr + pr * a.x; acc[i * 8 + 1] = acc[i * 8 + 1] * corr + pr * a.y;
+                acc[i * 8 + 2] = acc[i * 8 + 2] * corr + pr * bb.x; acc[i * 8 + 3] = acc[i * 8 + 3] * corr + pr * bb.y;
+                acc[i * 8 + 4] = acc[i * 8 + 4] * corr + pr * c.x; acc[i * 8 + 5] = acc[i * 8 + 5] * corr + pr * c.y;
+                acc[i * 8 + 6] = acc[i * 8 + 6] * corr + pr * d.x; acc[i * 8 + 7] = acc[i * 8 + 7] * corr + pr * d.y;
+            }
         }
     }
     if (sub == 0) { s_m[grp] = m; s_l[grp] = l; }
