@@ -141,4 +141,9 @@ int esb_scale_rows_add(const void* x, const void* y, const float* scale, void* o
     return scale_rows_add(x, y, scale, out, rows, d, rows_per_batch, ST(stream));
 }
 
+int esb_traj_metrics(const float* gen, const float* gt, const int32_t* gen_len, const int32_t* gt_len, int B, int Tg, int Tt, int D,
+                     int c0, int c1, int r0, double* out, void* stream) {
+    return traj_metrics(gen, gt, gen_len, gt_len, B, Tg, Tt, D, c0, c1, r0, out, ST(stream));
+}
+
 }  // extern "C"

@@ -18,7 +18,7 @@ _CTYPE = {
     "void*": ctypes.c_void_p, "const void*": ctypes.c_void_p, "float*": ctypes.c_void_p,
     "const float*": ctypes.c_void_p, "int64_t*": ctypes.c_void_p, "const int64_t*": ctypes.c_void_p,
     "int32_t*": ctypes.c_void_p, "const int32_t*": ctypes.c_void_p, "const uint8_t*": ctypes.c_void_p,
-    "uint8_t*": ctypes.c_void_p, "const char*": ctypes.c_char_p,
+    "uint8_t*": ctypes.c_void_p, "double*": ctypes.c_void_p, "const double*": ctypes.c_void_p, "const char*": ctypes.c_char_p,
     "int": ctypes.c_int, "int64_t": ctypes.c_int64, "float": ctypes.c_float, "double": ctypes.c_double,
     "uint64_t": ctypes.c_uint64,
 }

@@ -552,3 +552,20 @@ def scale_rows_add(y, scale, rows_per_batch: int, x=None):
     out = torch.empty_like(y)
     _l.call("esb_scale_rows_add", _p(x), y.data_ptr(), scale.data_ptr(), out.data_ptr(), rows, d, rows_per_batch, _stream())
     return out
+
+
+# ------------------------------------------------------------------------------------------------ metrics
+def traj_metrics(gen: torch.Tensor, gt: torch.Tensor, gen_len: Optional[torch.Tensor] = None, gt_len: Optional[torch.Tensor] = None,
+                 cols=(0, 6), rot_col: int = 3) -> torch.Tensor:
+    """models/utils/metrics.py per sample: gen [B,Tg,D], gt [B,Tt,D] fp32 -> [B,4] fp64 (ADE, FDE, IDE, angular distance)."""
+    _chk(gen, torch.float32, "traj_metrics.gen"); _chk(gt, torch.float32, "traj_metrics.gt")
+    gen, gt = gen.contiguous(), gt.contiguous()
+    B, Tg, D = gen.shape
+    Tt = gt.shape[1]
+    for t in (gen_len, gt_len):
+        if t is not None:
+            _chk(t, torch.int32, "traj_metrics.len")
+    out = torch.empty(B, 4, device=gen.device, dtype=torch.float64)
+    _l.call("esb_traj_metrics", gen.data_ptr(), gt.data_ptr(), _p(gen_len), _p(gt_len), B, Tg, Tt, D, int(cols[0]), int(cols[1]),
+            int(rot_col), out.data_ptr(), _stream())
+    return out

@@ -241,6 +241,15 @@ int esb_group_maxpool_bwd(const void* f, const void* dpool, const void* dcat, vo
 int esb_scale_rows_add(const void* x, const void* y, const float* scale, void* out, int64_t rows, int d, int64_t rows_per_batch,
                        void* stream);
 
+/* ------------------------------------------------------------------------------------------------ metrics
+ * egoscaler/models/utils/metrics.py: average_displacement_error :37-54, final_displacement_error :7-26,
+ * initial_displacement_error :28-35, anglar_distance :60-88, per sample (train.py:258-260, evaluate.py:145-147).
+ * gen [B,Tg,D], gt [B,Tt,D] fp32; gen_len / gt_len [B] valid steps (NULL = all); a shorter gen repeats its last pose, a
+ * longer one is truncated.  out [B,4] fp64 = (ADE, FDE, IDE, angular distance); displacement over columns [c0,c1),
+ * rotation vector in columns [r0,r0+3) (r0 < 0: no angular distance).  gen_len <= 0 -> NaN row (sample skipped). */
+int esb_traj_metrics(const float* gen, const float* gt, const int32_t* gen_len, const int32_t* gt_len, int B, int Tg, int Tt, int D,
+                     int c0, int c1, int r0, double* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

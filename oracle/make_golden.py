@@ -317,10 +317,53 @@ def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unf
     print(f"{name}.npz: loss={out['loss']:.6f} size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
 
 
+def golden_metrics():
+    """Outputs of the REAL egoscaler/models/utils/metrics.py (fastdtw stubbed: not installed, DTW is not on the path) on
+    seeded [T, 6] trajectory pairs of unequal lengths, incl. tiny rotation angles and identical rotations."""
+    import importlib.util
+    import types
+    sys_mod = __import__("sys")
+    if "fastdtw" not in sys_mod.modules:
+        st = types.ModuleType("fastdtw"); st.fastdtw = lambda *a, **k: (0.0, [])
+        sys_mod.modules["fastdtw"] = st
+    spec = importlib.util.spec_from_file_location("ref_metrics", os.path.join(ref_shim.REF_ROOT, "egoscaler/models/utils/metrics.py"))
+    rm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(rm)
+    rng = np.random.default_rng(11)
+    B, TG, TT = 24, 20, 20
+    gen = rng.uniform(-1, 1, (B, TG, 6)).astype(np.float32)
+    gt = rng.uniform(-1, 1, (B, TT, 6)).astype(np.float32)
+    gen[:, :, 3:] *= np.float32(np.pi)
+    gt[:, :, 3:] *= np.float32(np.pi)
+    gen[0, :, 3:] = gt[0, :, 3:]                        # identical rotations -> dot = 1 (clip / arccos edge)
+    gen[1, :, 3:] *= np.float32(1e-4); gt[1, :, 3:] *= np.float32(1e-4)      # small-angle branch of from_rotvec
+    gen[2, :, 3:] = 0; gt[2, :, 3:] = 0
+    gen_len = rng.integers(1, TG + 1, B).astype(np.int32)
+    gt_len = rng.integers(1, TT + 1, B).astype(np.int32)
+    gen_len[:4] = [TG, 5, 20, 1]; gt_len[:4] = [TT, 20, 7, 20]
+    out = dict(gen=gen, gt=gt, gen_len=gen_len, gt_len=gt_len)
+    res = np.zeros((B, 4), np.float64)
+    for b in range(B):
+        g, t = gen[b, :gen_len[b]], gt[b, :gt_len[b]]
+        res[b] = [rm.average_displacement_error(g, t), rm.final_displacement_error(g, t), rm.initial_displacement_error(g, t),
+                  rm.anglar_distance(g[:, 3:], t[:, 3:])]
+    out["ade_fde_ide_gd_all6"] = res
+    res3 = np.zeros((B, 3), np.float64)
+    for b in range(B):
+        g, t = gen[b, :gen_len[b], :3], gt[b, :gt_len[b], :3]
+        res3[b] = [rm.average_displacement_error(g, t), rm.final_displacement_error(g, t), rm.initial_displacement_error(g, t)]
+    out["ade_fde_ide_xyz"] = res3
+    np.savez_compressed(os.path.join(GOLD, "traj_metrics.npz"), **out)
+    print("traj_metrics.npz", res[:3])
+
+
 if __name__ == "__main__":
     import sys
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "metrics":
+        golden_metrics()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "unfrozen_pc":
         golden_variant("traj_vlm_tiny_unfrozen_pc", unfreeze_pc=True)
         golden_variant("traj_vlm_tiny_base_unfrozen_pc", point_cfg_name="PointTransformer_base_8192point", point="base",

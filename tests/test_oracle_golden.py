@@ -263,3 +263,15 @@ def test_oracle_unfrozen_point_encoder_matches_reference(name, base):
     for nm, bn in (("first_conv.1", enc.first_conv[1]), ("second_conv.1", enc.second_conv[1])):
         np.testing.assert_allclose(bn.running_mean.numpy(), gv[f"running_mean/{nm}"], atol=1e-5, rtol=1e-4)
         np.testing.assert_allclose(bn.running_var.numpy(), gv[f"running_var/{nm}"], atol=1e-5, rtol=1e-4)
+
+
+def test_metrics_oracle_matches_reference():
+    """oracle/metrics.py vs outputs of the real egoscaler/models/utils/metrics.py (tests/golden/traj_metrics.npz)."""
+    from oracle import metrics as om
+    g = np.load(os.path.join(GOLDEN, "traj_metrics.npz"))
+    for b in range(g["gen"].shape[0]):
+        gen, gt = g["gen"][b, :g["gen_len"][b]], g["gt"][b, :g["gt_len"][b]]
+        got = [om.ade(gen, gt), om.fde(gen, gt), om.ide(gen, gt), om.angular_distance(gen[:, 3:], gt[:, 3:])]
+        np.testing.assert_allclose(got, g["ade_fde_ide_gd_all6"][b], rtol=1e-6, atol=1e-7)
+        got3 = [om.ade(gen[:, :3], gt[:, :3]), om.fde(gen[:, :3], gt[:, :3]), om.ide(gen[:, :3], gt[:, :3])]
+        np.testing.assert_allclose(got3, g["ade_fde_ide_xyz"][b], rtol=1e-6, atol=1e-7)
