@@ -85,6 +85,11 @@ ESB_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
 }
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// griddepcontrol.wait: returns once the grid this one programmatically depends on has completed and flushed its
+// memory (no-op for a kernel launched without cudaLaunchAttributeProgrammaticStreamSerialization).
+ESB_DEVICE void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- TMA
 ESB_DEVICE void tma_prefetch_desc(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

@@ -95,14 +95,28 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
 
     if (warp == 0) {
         if (lane == 0) {
-            // ===================== TMA producer: runs ahead across unit boundaries
+            // ===================== TMA producer: runs ahead across unit boundaries.
+            // Programmatic dependent launch: the weights do not depend on the previous kernel of the stream, so the first
+            // ring of WEIGHT stages is requested before griddepcontrol.wait; the X tiles of those stages (written by the
+            // previous kernel) follow after it.  Launch latency, prologue and the first DRAM round trip of the weight
+            // stream thereby overlap the tail of the preceding small kernel (rmsnorm / rope+attention / silu).
             int stage = 0;
             uint32_t phase = 0;
+            int n_pend = 0;
+            int pend_kb[SK_STAGES];
+            bool dep_ready = false;
             for (int u = blockIdx.x; u < units; u += gridDim.x) {
                 const int tile = u / p.splits, s = u - tile * p.splits;
                 const int kb0 = s * p.kb_per;
                 const int kb1 = min(p.num_kb, kb0 + p.kb_per);
                 for (int kb = kb0; kb < kb1; ++kb) {
+                    if (!dep_ready && n_pend == SK_STAGES) {
+                        griddep_wait();
+                        for (int i = 0; i < n_pend; ++i)
+                            tma_load_2d_hint(smem + i * S::STAGE_BYTES + S::W_BYTES, &tma_x, &full_bar[i], pend_kb[i] * SK_BK, 0, kEvictLast);
+                        n_pend = 0;
+                        dep_ready = true;
+                    }
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     uint8_t* sw = smem + stage * S::STAGE_BYTES;
                     mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
@@ -111,13 +125,20 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                                           &full_bar[stage], kEvictFirst);
                     else
                         tma_load_2d_hint(sw, &tma_w, &full_bar[stage], kb * SK_BK, tile * SK_ROWS, kEvictFirst);
-                    tma_load_2d_hint(sw + S::W_BYTES, &tma_x, &full_bar[stage], kb * SK_BK, 0, kEvictLast);
+                    if (dep_ready) tma_load_2d_hint(sw + S::W_BYTES, &tma_x, &full_bar[stage], kb * SK_BK, 0, kEvictLast);
+                    else pend_kb[n_pend++] = kb;             // first ring pass: stage index == n_pend
                     if (++stage == SK_STAGES) { stage = 0; phase ^= 1u; }
                 }
+            }
+            if (!dep_ready) {
+                griddep_wait();
+                for (int i = 0; i < n_pend; ++i)
+                    tma_load_2d_hint(smem + i * S::STAGE_BYTES + S::W_BYTES, &tma_x, &full_bar[i], pend_kb[i] * SK_BK, 0, kEvictLast);
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
+            griddep_wait();
             // ===================== MMA issuer: D[128 weight rows, BT tokens] += W_tile * X_tile^T
             constexpr uint32_t idesc = umma_idesc_bf16(SK_ROWS, BT);
             int stage = 0;
@@ -151,6 +172,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
         }
     } else {
         // ===================== epilogue (4 warps): thread <-> one weight row n, registers <-> tokens
+        griddep_wait();                                   // residual / workspace / counters belong to earlier kernels
         const int q = warp & 3;
         const int nl = q * 32 + lane;
         int acc = 0;
@@ -258,7 +280,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
 }
 
 template <int BT, int SK_STAGES>
-int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyParams& p, int grid, cudaStream_t stream) {
+int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyParams& p, int grid, bool pdl, cudaStream_t stream) {
     using S = SkinnySmem<BT, SK_STAGES>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -269,7 +291,21 @@ int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyPara
         }
         attr_set = true;
     }
-    gemm_skinny_tcgen05_kernel<BT, SK_STAGES><<<grid, SK_THREADS, S::TOTAL, stream>>>(tw, tx, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(SK_THREADS);
+    cfg.dynamicSmemBytes = S::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_skinny_tcgen05_kernel<BT, SK_STAGES>, tw, tx, p);
+    if (e != cudaSuccess) {
+        set_last_error("gemm_skinny launch: %s", cudaGetErrorString(e));
+        return ESB_ERR_CUDA;
+    }
     return check_launch("gemm_skinny_tcgen05");
 }
 
@@ -378,7 +414,7 @@ int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw,
         return best_s > max_splits_ws ? ESB_ERR_WORKSPACE : ESB_ERR_INVALID_ARG;
     }
     CUtensorMap tw, tx;
-    int rc = w_tiled ? make_tma_2d_bf16(&tw, W, static_cast<long long>(n_tiles) * num_kb * SK_ROWS, SK_BK, SK_BK, SK_ROWS)
+    int rc = (w_tiled & 1) ? make_tma_2d_bf16(&tw, W, static_cast<long long>(n_tiles) * num_kb * SK_ROWS, SK_BK, SK_BK, SK_ROWS)
                      : make_tma_2d_bf16(&tw, W, N, K, ldw, SK_ROWS);
     if (rc) return rc;
     rc = make_tma_2d_bf16(&tx, X, M, K, ldx, bt);
@@ -387,13 +423,14 @@ int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw,
     p.M = M; p.N = N; p.K = K;
     p.C = reinterpret_cast<__nv_bfloat16*>(C); p.ldc = ldc;
     p.res = reinterpret_cast<const __nv_bfloat16*>(residual); p.ldr = ldr;
-    p.n_tiles = n_tiles; p.splits = best_s; p.kb_per = kb_per; p.num_kb = num_kb; p.w_tiled = w_tiled ? 1 : 0;
+    p.n_tiles = n_tiles; p.splits = best_s; p.kb_per = kb_per; p.num_kb = num_kb; p.w_tiled = (w_tiled & 1) ? 1 : 0;
     p.counters = reinterpret_cast<int*>(workspace);
     p.partial = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_COUNTER_BYTES) : nullptr;
     p.w_tiles = reinterpret_cast<const uint8_t*>(W);
     const long long units = static_cast<long long>(n_tiles) * best_s;
     const int grid = static_cast<int>(units < slots ? units : slots);
-    return bt == 32 ? launch_skinny<32, 4>(tw, tx, p, grid, stream) : launch_skinny<64, 4>(tw, tx, p, grid, stream);
+    const bool pdl = (w_tiled & 2) != 0;          // caller promises W is not written by the kernel launched just before
+    return bt == 32 ? launch_skinny<32, 4>(tw, tx, p, grid, pdl, stream) : launch_skinny<64, 4>(tw, tx, p, grid, pdl, stream);
 }
 
 }  // namespace esb

@@ -125,14 +125,16 @@ class LlamaTrunk:
         decode = attn_decode and B <= ops.SKINNY_MAX_M      # weight-streaming GEMMs on the tiled copies
         if pos_dev is not None:          # graph-replayed decode step: the position lives in a device counter
             assert attn_decode and pos0 == 0
+        if decode:
+            for w in self.layers:          # decode-layout copies exist before the first kernel of the step is queued, so no
+                w.ensure_tiled()           # skinny GEMM is ever launched right behind the kernel that wrote its weights
         for li, w in enumerate(self.layers):
             if saved is not None:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
             else:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps), None
             if decode:
-                w.ensure_tiled()
-                qkv = ops.gemm_skinny(xn, w.tqkv)
+                qkv = ops.gemm_skinny(xn, w.tqkv, weights_const=True)
             else:
                 qkv = ops.gemm(xn, w.wqkv)                                        # [T, 3d]
             if cache is not None:
@@ -153,14 +155,14 @@ class LlamaTrunk:
                 r = ops.attention(q4[:, :, 0], k4, v4, causal=True, kmask=kmask, q_pos0=pos0, want_lse=saved is not None)
                 o, lse = r if saved is not None else (r, None)
                 o = o.view(B * L, d)
-            h = ops.gemm_skinny(o, w.to, residual=x) if decode else ops.gemm(o, w.wo, residual=x)
+            h = ops.gemm_skinny(o, w.to, residual=x, weights_const=True) if decode else ops.gemm(o, w.wo, residual=x)
             if saved is not None:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps, want_rstd=True)
             else:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps), None
-            gu = ops.gemm_skinny(hn, w.tgu) if decode else ops.gemm(hn, w.wgu)
+            gu = ops.gemm_skinny(hn, w.tgu, weights_const=True) if decode else ops.gemm(hn, w.wgu)
             a = ops.silu_mul(gu)
-            out = ops.gemm_skinny(a, w.tdown, residual=h) if decode else ops.gemm(a, w.wdown, residual=h)
+            out = ops.gemm_skinny(a, w.tdown, residual=h, weights_const=True) if decode else ops.gemm(a, w.wdown, residual=h)
             if saved is not None:
                 saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu))
             x = out

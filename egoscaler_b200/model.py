@@ -216,13 +216,14 @@ class TrajPointLLMForCausalLM(ParamTree):
 
     def logits_from_hidden(self, h: torch.Tensor, decode: bool = False) -> torch.Tensor:
         """final RMSNorm + lm_head (pointllm.py:227-228) -> [rows, V] view of a [rows, v_pad] bf16 buffer."""
+        skinny = decode and h.shape[0] <= ops.SKINNY_MAX_M       # cached single-token step: stream the tiled copy
+        if skinny and self._lm_head_tiled is None:
+            self._lm_head_tiled = ops.retile_weight(self.lm_head.weight.detach())
         hn = ops.rmsnorm(h, self.model.norm.weight.detach(), self.cfg.rms_norm_eps)
         buf = torch.empty(h.shape[0], self.v_pad, device=h.device, dtype=torch.bfloat16)
         out = buf[:, :self.cfg.vocab_size]
-        if decode and h.shape[0] <= ops.SKINNY_MAX_M:       # cached single-token step: stream the tiled copy
-            if self._lm_head_tiled is None:
-                self._lm_head_tiled = ops.retile_weight(self.lm_head.weight.detach())
-            ops.gemm_skinny(hn, self._lm_head_tiled, out=out)
+        if skinny:
+            ops.gemm_skinny(hn, self._lm_head_tiled, out=out, weights_const=True)
         else:
             ops.gemm(hn, self.lm_head.weight.detach(), out=out)
         return out

@@ -34,6 +34,7 @@ def _chk(t: torch.Tensor, dtype, name: str):
 
 # ------------------------------------------------------------------------------------------------ GEMM
 SKINNY_MAX_M = 64
+pdl_enabled = True        # programmatic dependent launch of the decode-step GEMMs (tools/decode_variants.py toggles it)
 skinny_enabled = True
 _SKINNY_WS_BYTES = 96 << 20        # counters (16 KiB, zero) + fp32 split-K partials; lm_head at 9 splits needs ~37 MB
 _skinny_ws = {}
@@ -69,9 +70,10 @@ def retile_weight(w: torch.Tensor) -> TiledWeight:
 
 
 def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
-                out: Optional[torch.Tensor] = None, force_splits: int = 0) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, force_splits: int = 0, weights_const: bool = False) -> torch.Tensor:
     """``a @ w.T + residual`` for M <= 64 rows through the split-K weight-streaming kernel; ``w`` is a [N,K] bf16
-    tensor or a :class:`TiledWeight`."""
+    tensor or a :class:`TiledWeight`.  ``weights_const``: promise that ``w`` is not written by the kernel launched just
+    before on this stream -> programmatic dependent launch with early weight prefetch (the decode step)."""
     _chk(a, torch.bfloat16, "gemm_skinny.a")
     M, K = a.shape
     if isinstance(w, TiledWeight):
@@ -87,7 +89,7 @@ def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
         gemm_timer.before(M, N, K)
     _l.call("esb_gemm_skinny_bf16", a.data_ptr(), a.stride(0), wp, ldw, out.data_ptr(), out.stride(0),
             M, N, K, _p(residual), 0 if residual is None else residual.stride(0), ws.data_ptr(), ws.numel(), force_splits,
-            tiled, _stream())
+            tiled | (2 if (weights_const and pdl_enabled) else 0), _stream())
     if gemm_timer is not None:
         gemm_timer.after()
     return out

@@ -65,7 +65,10 @@ int esb_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* 
  * zero); it may be shared by all launches on one stream.  force_splits: 0 = auto.
  * w_tiled = 0: W is the state_dict layout [N,K] (ldw).  w_tiled = 1: W was re-laid out once by
  * esb_retile_weight_bf16 into [ceil(N/128)][ceil(K/64)][128][64] (zero padded) so that every pipeline stage is one
- * contiguous 16 KiB read - the HBM-friendly layout for streaming each weight exactly once (ldw ignored). */
+ * contiguous 16 KiB read - the HBM-friendly layout for streaming each weight exactly once (ldw ignored).
+ * w_tiled bit 1 (value 2): the caller promises that W is NOT written by the kernel launched immediately before on this
+ * stream; the launch then uses programmatic dependent launch and prefetches its first weight stages while that kernel
+ * drains (X, residual and workspace are only touched after griddepcontrol.wait). */
 int64_t esb_gemm_skinny_workspace_bytes(int M, int N, int K);
 int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                          const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,

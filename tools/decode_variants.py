@@ -32,10 +32,12 @@ def run(t_new, graph):
     return e0.elapsed_time(e1)
 
 
-for skinny in (True, False):
+for skinny, pdl in ((True, True), (True, False), (True, True), (True, False), (False, False)):
     ops.SKINNY_MAX_M = 64 if skinny else 0
     ops.skinny_enabled = skinny
-    for graph in (True, False):
+    ops.pdl_enabled = pdl
+    print("pdl", pdl, end=" ")
+    for graph in (True,):
         run(4, graph)
         t1 = min(run(1, graph) for _ in range(2))
         tT = min(run(T, graph) for _ in range(2))
