@@ -88,4 +88,11 @@ int esb_traj_ids_to_poses(const int64_t* ids, int B, int T, int num_bins, int64_
                              scale_mode, d_max, d_min, max_steps, pad_repeat, out, count, ST(stream));
 }
 
+int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T, int num_bins, int64_t base_id, int64_t ts_id,
+                          int64_t tsep_id, int64_t te_id, int64_t eos_id, int64_t pad_id, int norm, const double* range6, int out_ld,
+                          int64_t* out, int32_t* out_len, void* stream) {
+    return traj_poses_to_ids(poses, lens, B, T, num_bins, base_id, ts_id, tsep_id, te_id, eos_id, pad_id, norm, range6, out_ld,
+                             reinterpret_cast<long long*>(out), out_len, ST(stream));
+}
+
 }  // extern "C"

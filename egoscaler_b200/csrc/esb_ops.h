@@ -18,6 +18,9 @@ int traj_ids_to_poses(const long long* ids, int B, int T, int num_bins, long lon
 // metrics.cu
 int traj_metrics(const float* gen, const float* gt, const int* gen_len, const int* gt_len, int B, int Tg, int Tt, int D, int c0,
                  int c1, int r0, double* out, cudaStream_t s);
+int traj_poses_to_ids(const float* poses, const int* lens, int B, int T, int num_bins, long long base, long long ts, long long tsep,
+                      long long te, long long eos, long long pad, int norm, const double* range6, int out_ld, long long* out,
+                      int* out_len, cudaStream_t s);
 
 // norms.cu
 int rmsnorm_fwd(const void* x, long long ldx, const void* w, void* y, long long ldy, float* rstd, long long rows, int d,

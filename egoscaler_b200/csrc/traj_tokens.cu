@@ -233,4 +233,59 @@ int traj_ids_to_poses(const long long* ids, int B, int T, int num_bins, long lon
     return check_launch("traj_ids_to_poses");
 }
 
+// ------------------------------------------------------------------------------------------------ poses -> ids
+// Data-side tokenisation, the inverse of traj_ids_to_poses: normalised poses in [-1, 1] are discretised
+// with utils/utils.py:13-16 discretize_action (bit-exact np.digitize) and laid out as the token sequence the parser
+// utils/utils.py:47-104 / constant.py expects:  <ts> (6 x <p*> <tsep>) x len  <te> eos pad...   One warp per sequence.
+// norm = 1 first applies the inverse of dataset.py:139-146 denorm(do_norm=True): xyz affine [min,max] -> [-1,1], rot / pi
+// (the forward normaliser itself is not shipped by the reference).
+__global__ void __launch_bounds__(128) traj_poses_to_ids_kernel(const float* __restrict__ poses, const int* __restrict__ lens, int B,
+                                                                int T, int num_bins, long long base, long long ts, long long tsep,
+                                                                long long te, long long eos, long long pad, int norm,
+                                                                const double* __restrict__ range6, int out_ld,
+                                                                long long* __restrict__ out, int* __restrict__ out_len) {
+    __shared__ double edges[kMaxBins];
+    build_edges(edges, num_bins);
+    const int b = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= B) return;
+    int n = lens ? lens[b] : T;
+    n = n < 0 ? 0 : (n > T ? T : n);
+    const int need = 1 + 7 * n + 2;
+    long long* o = out + static_cast<long long>(b) * out_ld;
+    for (int i = lane; i < out_ld; i += 32) {
+        long long tok = pad;
+        if (i == 0) tok = ts;
+        else if (i < 1 + 7 * n) {
+            const int step = (i - 1) / 7, j = (i - 1) % 7;
+            if (j == 6) tok = tsep;
+            else {
+                double v = static_cast<double>(poses[(static_cast<long long>(b) * T + step) * 6 + j]);
+                if (norm) {
+                    if (j < 3) v = 2.0 * (v - range6[2 * j]) / (range6[2 * j + 1] - range6[2 * j]) - 1.0;
+                    else v = v / 3.141592653589793;
+                    v = static_cast<double>(static_cast<float>(v));          // the stored normalised pose is float32
+                }
+                tok = base + digitize_m1(v, edges, num_bins);
+            }
+        } else if (i == 1 + 7 * n) tok = te;
+        else if (i == 2 + 7 * n) tok = eos;
+        o[i] = tok;
+    }
+    if (lane == 0 && out_len) out_len[b] = need <= out_ld ? need : out_ld;
+}
+
+int traj_poses_to_ids(const float* poses, const int* lens, int B, int T, int num_bins, long long base, long long ts, long long tsep,
+                      long long te, long long eos, long long pad, int norm, const double* range6, int out_ld, long long* out,
+                      int* out_len, cudaStream_t s) {
+    if (B <= 0) return ESB_OK;
+    if (!poses || !out || num_bins < 2 || num_bins > kMaxBins || T < 1 || out_ld < 3 + 7 * T || (norm && !range6)) {
+        set_last_error("traj_poses_to_ids: bad arguments (T=%d out_ld=%d needs >= %d)", T, out_ld, 3 + 7 * T);
+        return ESB_ERR_INVALID_ARG;
+    }
+    traj_poses_to_ids_kernel<<<(B + 3) / 4, 128, 0, s>>>(poses, lens, B, T, num_bins, base, ts, tsep, te, eos, pad, norm, range6, out_ld,
+                                                         out, out_len);
+    return check_launch("traj_poses_to_ids");
+}
+
 }  // namespace esb

@@ -571,3 +571,23 @@ def traj_metrics(gen: torch.Tensor, gt: torch.Tensor, gen_len: Optional[torch.Te
     _l.call("esb_traj_metrics", gen.data_ptr(), gt.data_ptr(), _p(gen_len), _p(gt_len), B, Tg, Tt, D, int(cols[0]), int(cols[1]),
             int(rot_col), out.data_ptr(), _stream())
     return out
+
+
+def traj_poses_to_ids(poses: torch.Tensor, lens: Optional[torch.Tensor] = None, num_bins: int = 256, base_id: int = 32006,
+                      ts_id: int = 32003, tsep_id: int = 32004, te_id: int = 32005, eos_id: int = 2, pad_id: int = 0,
+                      ranges: Optional[torch.Tensor] = None, out_len_total: Optional[int] = None):
+    """Normalised (or, with ``ranges`` fp64 [6] = min/max of x,y,z, physical) poses [B,T,6] -> (ids [B,Lout] int64, len [B])."""
+    _chk(poses, torch.float32, "traj_poses_to_ids.poses")
+    poses = poses.contiguous()
+    B, T, six = poses.shape
+    assert six == 6
+    Lout = out_len_total if out_len_total is not None else 3 + 7 * T
+    out = torch.empty(B, Lout, device=poses.device, dtype=torch.int64)
+    olen = torch.empty(B, device=poses.device, dtype=torch.int32)
+    if lens is not None:
+        _chk(lens, torch.int32, "traj_poses_to_ids.lens")
+    if ranges is not None:
+        _chk(ranges, torch.float64, "traj_poses_to_ids.ranges")
+    _l.call("esb_traj_poses_to_ids", poses.data_ptr(), _p(lens), B, T, num_bins, base_id, ts_id, tsep_id, te_id, eos_id, pad_id,
+            0 if ranges is None else 1, _p(ranges), Lout, out.data_ptr(), olen.data_ptr(), _stream())
+    return out, olen

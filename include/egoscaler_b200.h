@@ -244,6 +244,15 @@ int esb_group_maxpool_bwd(const void* f, const void* dpool, const void* dcat, vo
 int esb_scale_rows_add(const void* x, const void* y, const float* scale, void* out, int64_t rows, int d, int64_t rows_per_batch,
                        void* stream);
 
+/* Data-side tokenisation (inverse of esb_traj_ids_to_poses): poses [B,T,6] f32, lens [B] (NULL: T) ->
+ * ids [B,out_ld] int64 = <ts> (6 bins <tsep>) x len <te> eos pad..., out_len [B] (or NULL); bins by utils/utils.py:13-16
+ * discretize_action, token layout as parsed by utils/utils.py:47-104 (constant.py templates).  norm=1 first maps physical
+ * poses to [-1,1] with the inverse of dataset.py:139-146 (range6 = device {min_x,max_x,min_y,max_y,min_z,max_z}, rot/pi).
+ * out_ld >= 3 + 7*T. */
+int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T, int num_bins, int64_t base_id, int64_t ts_id,
+                          int64_t tsep_id, int64_t te_id, int64_t eos_id, int64_t pad_id, int norm, const double* range6, int out_ld,
+                          int64_t* out, int32_t* out_len, void* stream);
+
 /* ------------------------------------------------------------------------------------------------ metrics
  * egoscaler/models/utils/metrics.py: average_displacement_error :37-54, final_displacement_error :7-26,
  * initial_displacement_error :28-35, anglar_distance :60-88, per sample (train.py:258-260, evaluate.py:145-147).

@@ -146,3 +146,23 @@ def pad_repeat_last(gen: np.ndarray, T: int) -> np.ndarray:
     if gen.shape[0] < T:
         gen = np.concatenate([gen, np.repeat(gen[-1][None, :], T - gen.shape[0], axis=0)], axis=0)
     return gen
+
+
+def poses_to_ids(poses: np.ndarray, num_bins: int = 256, base: int = TRAJ_TOKEN_BASE, eos: int = 2) -> list:
+    """Forward tokenisation (not shipped by the reference): the sequence whose decode by
+    ``str_to_float``/``ids_to_poses`` (utils/utils.py:47-104) gives back ``token_to_action(discretize_action(poses))``:
+    ``<ts> (<pA> <pB> <pC> <pD> <pE> <pF> <tsep>) x T <te> eos`` with bins from ``discretize_action`` (:13-16)."""
+    ids = [TS_TOKEN]
+    for row in np.asarray(poses, np.float32):
+        ids += (discretize_action(row, num_bins) + base).tolist() + [TSEP_TOKEN]
+    return ids + [TE_TOKEN, eos]
+
+
+def norm_poses(traj: np.ndarray) -> np.ndarray:
+    """Inverse of ``denorm(do_norm=True)`` (dataset.py:139-146): physical [.., 6] -> [-1, 1], float32."""
+    t = np.array(traj, np.float64, copy=True)
+    r = DATASET_RANGE
+    for j, ax in enumerate("xyz"):
+        t[..., j] = 2.0 * (t[..., j] - r["min_" + ax]) / (r["max_" + ax] - r["min_" + ax]) - 1.0
+    t[..., 3:] = t[..., 3:] / np.pi
+    return t.astype(np.float32)

@@ -121,3 +121,65 @@ def test_ids_to_poses_random_vs_oracle():
         assert cnt[b] == n
         assert np.array_equal(poses[b, :n], ref[:n])
         assert np.array_equal(poses[b], tt.pad_repeat_last(ref[:n], 40))
+
+
+def test_poses_to_ids_roundtrip_and_oracle():
+    """Data-side tokenisation: ids == oracle layout built from the pinned discretize_action; decoding them with
+    the (reference-pinned) parser gives token_to_action(discretize_action(poses)) -- the quantiser round trip -- bit-exactly;
+    ragged lengths, exact bin edges, out-of-range values and the physical -> normalised mapping (inverse of denorm)."""
+    import numpy as np
+    import torch
+    from egoscaler_b200 import ops
+    from oracle import traj_tokenizer as tt
+    rng = np.random.default_rng(4)
+    B, T = 37, 20
+    poses = rng.uniform(-1.02, 1.02, (B, T, 6)).astype(np.float32)
+    poses[0, 0] = np.linspace(-1, 1, 256)[[0, 1, 127, 128, 254, 255]].astype(np.float32)     # exact edges
+    poses[1, 0] = [np.nan, np.inf, -np.inf, -1.0, 1.0, 0.0]
+    lens = rng.integers(0, T + 1, B).astype(np.int32)
+    lens[:3] = [T, T, 0]
+    ids, olen = ops.traj_poses_to_ids(torch.from_numpy(poses).cuda(), torch.from_numpy(lens).cuda())
+    ids, olen = ids.cpu().numpy(), olen.cpu().numpy()
+    assert ids.shape == (B, 3 + 7 * T)
+    for b in range(B):
+        ref = tt.poses_to_ids(poses[b, :lens[b]])
+        assert olen[b] == len(ref)
+        assert np.array_equal(ids[b, :len(ref)], np.array(ref)) and (ids[b, len(ref):] == 0).all()
+    # round trip through the parser kernel and through the oracle parser
+    back, cnt = ops.traj_ids_to_poses(torch.from_numpy(ids).cuda(), max_steps=T, pad_repeat=False)
+    back, cnt = back.cpu().numpy(), cnt.cpu().numpy()
+    for b in range(B):
+        if b == 1:
+            continue                                               # NaN / inf row: bins -1 / 255 are checked above via the oracle ids
+        n = int(lens[b])
+        # the reference parser splits on <tsep>: the trailing "<te>" segment has no pose and repeats the previous one
+        # (utils/utils.py:91-93), so a well-formed sequence of n poses parses to n + 1 (capped by max_steps)
+        ref_parse = tt.ids_to_poses(ids[b].tolist())
+        in_range = n > 0 and bool((tt.discretize_action(poses[b, :n]) >= 0).all())
+        if in_range:
+            assert cnt[b] == min(n + 1, T)
+        if ref_parse is None:                                  # x < -1 quantises to bin -1 = id of <te>: such a pose does not parse
+            assert cnt[b] == 0
+        else:
+            assert cnt[b] == min(len(ref_parse), T) and np.array_equal(back[b, :cnt[b]], ref_parse[:cnt[b]])
+        q = tt.token_to_action(tt.discretize_action(poses[b, :n]), 256).astype(np.float32)
+        ok = (tt.discretize_action(poses[b, :n]) >= 0).all(axis=1) if n else np.zeros(0, bool)
+        if n and ok.all():
+            assert np.array_equal(back[b, :n], q)
+    # physical units -> normalised -> ids  ==  oracle normaliser + tokeniser
+    phys = np.stack([rng.uniform(-2, 2, (B, T)), rng.uniform(-2, 2, (B, T)), rng.uniform(0, 2.5, (B, T)),
+                     rng.uniform(-3.1, 3.1, (B, T)), rng.uniform(-3.1, 3.1, (B, T)), rng.uniform(-3.1, 3.1, (B, T))], -1).astype(np.float32)
+    r = tt.DATASET_RANGE
+    ranges = torch.tensor([r["min_x"], r["max_x"], r["min_y"], r["max_y"], r["min_z"], r["max_z"]], dtype=torch.float64).cuda()
+    ids2, _ = ops.traj_poses_to_ids(torch.from_numpy(phys).cuda(), None, ranges=ranges)
+    ids2 = ids2.cpu().numpy()
+    nrm = tt.norm_poses(phys)
+    mism = 0
+    for b in range(B):
+        ref = np.array(tt.poses_to_ids(nrm[b]))
+        mism += int((ids2[b, :len(ref)] != ref).sum())
+    assert mism == 0
+    # and denorm(dequantised) lands within one bin of the physical input
+    back2, _ = ops.traj_ids_to_poses(torch.from_numpy(ids2).cuda(), max_steps=T, scale=ops.SCALE_DENORM, pad_repeat=False)
+    err = np.abs(back2.cpu().numpy() - phys)
+    assert err[..., :2].max() <= 4.0 / 255 + 1e-5 and err[..., 2].max() <= 2.5 / 255 + 1e-5 and err[..., 3:].max() <= 2 * np.pi / 255 + 1e-5
