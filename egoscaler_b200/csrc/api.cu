@@ -95,4 +95,18 @@ int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T,
                              reinterpret_cast<long long*>(out), out_len, ST(stream));
 }
 
+int64_t esb_rgbd_workspace_bytes(int H, int W) { return rgbd_workspace_bytes(H, W); }
+
+int esb_rgbd_to_points(const float* rgbd, int H, int W, const int32_t* boxes, int n_boxes, double principal_point, double focal_x,
+                       double focal_y, int has_d_thres, double d_thres, float* out, int64_t cap, int64_t* out_count,
+                       void* workspace, int64_t workspace_bytes, void* stream) {
+    return rgbd_to_points(rgbd, H, W, boxes, n_boxes, principal_point, focal_x, focal_y, has_d_thres, d_thres, out, cap,
+                          reinterpret_cast<long long*>(out_count), workspace, workspace_bytes, ST(stream));
+}
+
+int esb_pc_sample_norm(const float* points, int64_t cloud_stride, int64_t n, const int64_t* idx, int B, int S, float* out,
+                       void* stream) {
+    return pc_sample_norm(points, cloud_stride, n, reinterpret_cast<const long long*>(idx), B, S, out, ST(stream));
+}
+
 }  // extern "C"

@@ -22,6 +22,14 @@ int traj_poses_to_ids(const float* poses, const int* lens, int B, int T, int num
                       long long te, long long eos, long long pad, int norm, const double* range6, int out_ld, long long* out,
                       int* out_len, cudaStream_t s);
 
+// rgbd_frontend.cu
+long long rgbd_workspace_bytes(int H, int W);
+int rgbd_to_points(const float* rgbd, int H, int W, const int* boxes, int n_boxes, double principal, double fx, double fy,
+                   int has_thres, double d_thres, float* out, long long cap, long long* out_count, void* workspace,
+                   long long workspace_bytes, cudaStream_t s);
+int pc_sample_norm(const float* pts, long long cloud_stride, long long n, const long long* idx, int B, int S, float* out,
+                   cudaStream_t s);
+
 // norms.cu
 int rmsnorm_fwd(const void* x, long long ldx, const void* w, void* y, long long ldy, float* rstd, long long rows, int d,
                 float eps, cudaStream_t s);

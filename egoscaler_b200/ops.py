@@ -591,3 +591,50 @@ def traj_poses_to_ids(poses: torch.Tensor, lens: Optional[torch.Tensor] = None, 
     _l.call("esb_traj_poses_to_ids", poses.data_ptr(), _p(lens), B, T, num_bins, base_id, ts_id, tsep_id, te_id, eos_id, pad_id,
             0 if ranges is None else 1, _p(ranges), Lout, out.data_ptr(), olen.data_ptr(), _stream())
     return out, olen
+
+
+def rgbd_to_points(rgbd: torch.Tensor, boxes: Optional[torch.Tensor], principal_point: float, focal_x: float, focal_y: float,
+                   d_thres: Optional[float] = None, cap: Optional[int] = None):
+    """pcm_tools.py:68-96 get_points_colors on device: rgbd [H,W,4] fp32, boxes [nb,4] int32 {xmin,ymin,xmax,ymax} or None
+    -> (pts [cap,6] fp32 = xyz ++ rgb/255 in row-major pixel order, count int64 [1] device)."""
+    _chk(rgbd, torch.float32, "rgbd_to_points.rgbd")
+    rgbd = rgbd.contiguous()
+    H, W, four = rgbd.shape
+    assert four == 4
+    nb = 0
+    if boxes is not None and boxes.numel():
+        _chk(boxes, torch.int32, "rgbd_to_points.boxes")
+        boxes = boxes.contiguous()
+        assert boxes.shape[1] == 4
+        nb = boxes.shape[0]
+    cap = H * W if cap is None else int(cap)
+    out = torch.empty(cap, 6, device=rgbd.device, dtype=torch.float32)
+    count = torch.empty(1, device=rgbd.device, dtype=torch.int64)
+    wsb = int(_l.lib().raw("esb_rgbd_workspace_bytes")(H, W))
+    ws = torch.empty(wsb, device=rgbd.device, dtype=torch.uint8)
+    _l.call("esb_rgbd_to_points", rgbd.data_ptr(), H, W, _p(boxes) if nb else None, nb, float(principal_point), float(focal_x),
+            float(focal_y), 0 if d_thres is None else 1, 0.0 if d_thres is None else float(d_thres), out.data_ptr(), cap,
+            count.data_ptr(), ws.data_ptr(), wsb, _stream())
+    return out, count
+
+
+def pc_sample_norm(points: torch.Tensor, idx: Optional[torch.Tensor] = None, n: Optional[int] = None,
+                   num_samples: Optional[int] = None) -> torch.Tensor:
+    """pointllm/data/utils.py:146-157 pc_norm of the rows ``idx`` [B,S] (None: the first ``num_samples`` rows) of points
+    [B,N,6] fp32 (only the first ``n`` rows of each cloud are valid) -> [B,S,6] fp32, ready for the point encoder."""
+    _chk(points, torch.float32, "pc_sample_norm.points")
+    if points.dim() == 2:
+        points = points.unsqueeze(0)
+    points = points.contiguous()
+    B, N, six = points.shape
+    assert six == 6
+    n = N if n is None else int(n)
+    if idx is not None:
+        _chk(idx, torch.int64, "pc_sample_norm.idx")
+        idx = idx.contiguous().view(B, -1)
+        S = idx.shape[1]
+    else:
+        S = n if num_samples is None else int(num_samples)
+    out = torch.empty(B, S, 6, device=points.device, dtype=torch.float32)
+    _l.call("esb_pc_sample_norm", points.data_ptr(), N * 6, n, _p(idx), B, S, out.data_ptr(), _stream())
+    return out

@@ -253,6 +253,22 @@ int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T,
                           int64_t tsep_id, int64_t te_id, int64_t eos_id, int64_t pad_id, int norm, const double* range6, int out_ld,
                           int64_t* out, int32_t* out_len, void* stream);
 
+/* ------------------------------------------------------------------------------------------------ RGB-D front-end
+ * Producer of `pcrgbs`.  esb_rgbd_to_points replaces egoscaler/data/tools/pcm_tools.py:68-96 get_points_colors
+ * (call sites data/train/7_get_object_trajectory.py:191-200,244-253; unprojection also depth.py:55-60): rgbd [H,W,4] fp32
+ * (r,g,b in 0..255, metric depth), boxes [n_boxes,4] int32 {xmin,ymin,xmax,ymax} (non-negative; pixels inside are dropped),
+ * pinhole (principal_point, focal_x, focal_y; configs/camera.py:6-9), optional z < d_thres.  out [cap,6] fp32 =
+ * (x,y,z,r/255,g/255,b/255) of the surviving pixels in row-major order, *out_count = number of survivors (may exceed cap;
+ * rows >= cap are not written).  workspace >= esb_rgbd_workspace_bytes(H,W) device bytes. */
+int64_t esb_rgbd_workspace_bytes(int H, int W);
+int esb_rgbd_to_points(const float* rgbd, int H, int W, const int32_t* boxes, int n_boxes, double principal_point, double focal_x,
+                       double focal_y, int has_d_thres, double d_thres, float* out, int64_t cap, int64_t* out_count,
+                       void* workspace, int64_t workspace_bytes, void* stream);
+/* pointllm/data/utils.py:146-157 pc_norm over a caller-chosen subset: points [B][n,6] fp32 (cloud_stride elements apart),
+ * idx [B,S] int64 row indices (NULL: the first S rows) -> out [B,S,6]: xyz - mean, / max L2 norm (fp64 arithmetic), rgb copied. */
+int esb_pc_sample_norm(const float* points, int64_t cloud_stride, int64_t n, const int64_t* idx, int B, int S, float* out,
+                       void* stream);
+
 /* ------------------------------------------------------------------------------------------------ metrics
  * egoscaler/models/utils/metrics.py: average_displacement_error :37-54, final_displacement_error :7-26,
  * initial_displacement_error :28-35, anglar_distance :60-88, per sample (train.py:258-260, evaluate.py:145-147).

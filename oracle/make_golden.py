@@ -357,12 +357,61 @@ def golden_metrics():
     print("traj_metrics.npz", res[:3])
 
 
+def _ref_function(relpath, name, **ns):
+    """Compile ONE function of a reference file in isolation (its module imports open3d / transformers at file scope, which
+    are absent or irrelevant here): the function body that runs is the reference's own, read from REF_ROOT at run time."""
+    import ast
+    path = os.path.join(ref_shim.REF_ROOT, relpath)
+    tree = ast.parse(open(path).read(), path)
+    fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == name]
+    assert len(fn) == 1, (relpath, name)
+    g = dict(np=np, **ns)
+    exec(compile(ast.Module(body=fn, type_ignores=[]), path, "exec"), g)
+    return g[name]
+
+
+def golden_rgbd_frontend():
+    """Outputs of the REAL get_points_colors (data/tools/pcm_tools.py:68-96) and pc_norm (pointllm/data/utils.py:146-157) on
+    seeded RGB-D frames: with / without bboxes and depth threshold, a non-square frame, an all-invalid frame."""
+    from oracle.rgbd_frontend import synth_rgbd
+    gpc = _ref_function("egoscaler/data/tools/pcm_tools.py", "get_points_colors")
+    pcn = _ref_function("egoscaler/models/pointllm/pointllm/data/utils.py", "pc_norm")
+    cases = [  # name, H, W, boxes, c, fx, fy, d_thres
+        ("plain", 40, 40, None, 19.5, 30.25, 30.25, None),
+        ("boxes_thres", 64, 48, [(5, 7, 20, 30), (30, 0, 48, 10), (10, 50, 12, 64)], 23.5, 41.0, 39.5, 4.0),
+        ("aria_crop", 33, 57, [(0, 0, 57, 3)], 703.5, 605.343, 605.343, 3.0),
+        ("all_boxed", 16, 16, [(0, 0, 16, 16)], 7.5, 10.0, 10.0, None),
+    ]
+    out = {}
+    rng = np.random.default_rng(3)
+    for k, (name, H, W, boxes, c, fx, fy, thr) in enumerate(cases):
+        rgbd = synth_rgbd(H, W, seed=100 + k)
+        bb = None if boxes is None else [{"box": dict(xmin=b[0], ymin=b[1], xmax=b[2], ymax=b[3])} for b in boxes]
+        pts, cols = gpc(rgbd=rgbd, bbox=bb, width=W, height=H, principal_p=c, focal_len_x=fx, focal_len_y=fy, d_thres=thr)
+        out[f"{name}/rgbd"] = rgbd
+        out[f"{name}/boxes"] = np.zeros((0, 4), np.int32) if boxes is None else np.asarray(boxes, np.int32)
+        out[f"{name}/cam"] = np.asarray([c, fx, fy, np.nan if thr is None else thr], np.float64)
+        out[f"{name}/points"] = pts
+        out[f"{name}/colors"] = cols
+        assert pts.dtype == np.float64 and cols.dtype == np.float32, (pts.dtype, cols.dtype)
+        if len(pts) >= 64:
+            idx = rng.choice(len(pts), size=min(512, len(pts)), replace=False)
+            pc = np.concatenate([pts[idx], cols[idx].astype(np.float64)], axis=1)
+            out[f"{name}/sample_idx"] = idx.astype(np.int64)
+            out[f"{name}/pc_norm"] = pcn(pc)
+        print(name, rgbd.dtype, pts.shape, cols.shape)
+    np.savez_compressed(os.path.join(GOLD, "rgbd_frontend.npz"), **out)
+
+
 if __name__ == "__main__":
     import sys
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
     if len(sys.argv) > 1 and sys.argv[1] == "metrics":
         golden_metrics()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "rgbd":
+        golden_rgbd_frontend()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "unfrozen_pc":
         golden_variant("traj_vlm_tiny_unfrozen_pc", unfreeze_pc=True)

@@ -275,3 +275,23 @@ def test_metrics_oracle_matches_reference():
         np.testing.assert_allclose(got, g["ade_fde_ide_gd_all6"][b], rtol=1e-6, atol=1e-7)
         got3 = [om.ade(gen[:, :3], gt[:, :3]), om.fde(gen[:, :3], gt[:, :3]), om.ide(gen[:, :3], gt[:, :3])]
         np.testing.assert_allclose(got3, g["ade_fde_ide_xyz"][b], rtol=1e-6, atol=1e-7)
+
+
+RGBD_CASES = ["plain", "boxes_thres", "aria_crop", "all_boxed"]
+
+
+def test_rgbd_frontend_oracle_matches_reference():
+    """oracle/rgbd_frontend.py vs outputs of the real get_points_colors (pcm_tools.py:68-96) and pc_norm
+    (pointllm/data/utils.py:146-157) stored in tests/golden/rgbd_frontend.npz: bit-exact."""
+    from oracle import rgbd_frontend as rf
+    g = np.load(os.path.join(GOLDEN, "rgbd_frontend.npz"))
+    for name in RGBD_CASES:
+        c, fx, fy, thr = g[f"{name}/cam"]
+        pts, cols = rf.get_points_colors(g[f"{name}/rgbd"], g[f"{name}/boxes"].tolist(), c, fx, fy, None if np.isnan(thr) else thr)
+        assert pts.dtype == np.float64 and cols.dtype == np.float32
+        assert np.array_equal(pts, g[f"{name}/points"]) and np.array_equal(cols, g[f"{name}/colors"]), name
+        if f"{name}/pc_norm" in g.files:
+            idx = g[f"{name}/sample_idx"]
+            pc = np.concatenate([pts[idx], cols[idx].astype(np.float64)], axis=1)
+            assert np.array_equal(rf.pc_norm(pc), g[f"{name}/pc_norm"]), name
+    assert g["all_boxed/points"].shape == (0, 3)
