@@ -95,6 +95,11 @@ int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T,
                              reinterpret_cast<long long*>(out), out_len, ST(stream));
 }
 
+int esb_traj_preprocess(const float* traj, const int32_t* lens, int B, int T, int D, int num_steps, int smooth, float* out,
+                        int32_t* mask, void* stream) {
+    return traj_preprocess(traj, lens, B, T, D, num_steps, smooth, out, mask, ST(stream));
+}
+
 int64_t esb_rgbd_workspace_bytes(int H, int W) { return rgbd_workspace_bytes(H, W); }
 
 int esb_rgbd_to_points(const float* rgbd, int H, int W, const int32_t* boxes, int n_boxes, double principal_point, double focal_x,

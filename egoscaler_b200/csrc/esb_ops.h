@@ -22,6 +22,9 @@ int traj_poses_to_ids(const float* poses, const int* lens, int B, int T, int num
                       long long te, long long eos, long long pad, int norm, const double* range6, int out_ld, long long* out,
                       int* out_len, cudaStream_t s);
 
+int traj_preprocess(const float* traj, const int* lens, int B, int T, int D, int num_steps, int smooth, float* out, int* mask,
+                    cudaStream_t s);
+
 // rgbd_frontend.cu
 long long rgbd_workspace_bytes(int H, int W);
 int rgbd_to_points(const float* rgbd, int H, int W, const int* boxes, int n_boxes, double principal, double fx, double fy,

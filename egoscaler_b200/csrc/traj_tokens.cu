@@ -288,4 +288,65 @@ int traj_poses_to_ids(const float* poses, const int* lens, int B, int T, int num
     return check_launch("traj_poses_to_ids");
 }
 
+// ------------------------------------------------------------------------------------------------ pre-processing
+// egoscaler/models/utils/traj_utils.py: smoothing_traj :42-96 (moving average over the position columns with the reference's
+// edge rules, fp32 left-to-right like numpy on float32 rows, no FMA contraction) followed by preprocess_traj :3-40
+// (np.linspace(0, T-1, num_steps).astype(int) gather when T >= num_steps, else pad with the last point; mask 1 = real).
+ESB_DEVICE float smoothed_pos(const float* __restrict__ src, int D, int n, int j, int d) {
+    auto P = [&](int t) { return src[static_cast<long long>(t) * D + d]; };
+    auto add = [](float a, float b) { return __fadd_rn(a, b); };
+    if (j == 0) {
+        if (n >= 3) return __fdiv_rn(add(add(__fmul_rn(3.0f, P(0)), P(1)), P(2)), 5.0f);
+        if (n == 2) return __fdiv_rn(add(__fmul_rn(3.0f, P(0)), P(1)), 4.0f);
+        return P(0);
+    }
+    if (j == 1) {
+        if (n >= 4) return __fdiv_rn(add(add(add(__fmul_rn(2.0f, P(0)), P(1)), P(2)), P(3)), 5.0f);
+        if (n == 3) return __fdiv_rn(add(add(__fmul_rn(2.0f, P(0)), P(1)), P(2)), 4.0f);
+        return P(1);
+    }
+    if (j == n - 2) {                                   // n >= 4 here (j >= 2)
+        return __fdiv_rn(add(add(add(P(j - 2), P(j - 1)), P(j)), P(j + 1)), 4.0f);
+    }
+    if (j == n - 1) {                                   // n >= 3 here
+        return __fdiv_rn(add(add(P(j - 2), P(j - 1)), P(j)), 3.0f);
+    }
+    return __fdiv_rn(add(add(add(add(P(j - 2), P(j - 1)), P(j)), P(j + 1)), P(j + 2)), 5.0f);
+}
+
+__global__ void __launch_bounds__(128) traj_preprocess_kernel(const float* __restrict__ traj, const int* __restrict__ lens, int T,
+                                                              int D, int num_steps, int smooth, float* __restrict__ out,
+                                                              int* __restrict__ mask) {
+    const int b = blockIdx.x;
+    int n = lens ? lens[b] : T;
+    n = n < 1 ? 1 : (n > T ? T : n);
+    const float* src = traj + static_cast<long long>(b) * T * D;
+    float* dst = out + static_cast<long long>(b) * num_steps * D;
+    const double step = num_steps > 1 ? static_cast<double>(n - 1) / static_cast<double>(num_steps - 1) : 0.0;
+    for (int e = threadIdx.x; e < num_steps * D; e += blockDim.x) {
+        const int s = e / D, d = e - s * D;
+        int j;
+        bool real = true;
+        if (n >= num_steps) {
+            j = (num_steps > 1 && s == num_steps - 1) ? n - 1 : static_cast<int>(__dmul_rn(static_cast<double>(s), step));
+        } else {
+            real = s < n;
+            j = real ? s : n - 1;
+        }
+        dst[e] = (smooth && d < 3) ? smoothed_pos(src, D, n, j, d) : src[static_cast<long long>(j) * D + d];
+        if (mask && d == 0) mask[static_cast<long long>(b) * num_steps + s] = real ? 1 : 0;
+    }
+}
+
+int traj_preprocess(const float* traj, const int* lens, int B, int T, int D, int num_steps, int smooth, float* out, int* mask,
+                    cudaStream_t s) {
+    if (B <= 0) return ESB_OK;
+    if (!traj || !out || T < 1 || D < 1 || num_steps < 1 || (smooth && D < 3)) {
+        set_last_error("traj_preprocess: bad arguments (T=%d D=%d num_steps=%d)", T, D, num_steps);
+        return ESB_ERR_INVALID_ARG;
+    }
+    traj_preprocess_kernel<<<B, 128, 0, s>>>(traj, lens, T, D, num_steps, smooth, out, mask);
+    return check_launch("traj_preprocess");
+}
+
 }  // namespace esb

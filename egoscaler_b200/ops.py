@@ -593,6 +593,21 @@ def traj_poses_to_ids(poses: torch.Tensor, lens: Optional[torch.Tensor] = None, 
     return out, olen
 
 
+def traj_preprocess(traj: torch.Tensor, lens: Optional[torch.Tensor], num_steps: int, smooth: bool = False):
+    """traj_utils.py smoothing_traj (optional) then preprocess_traj, batched: traj [B,T,D] fp32, lens [B] int32 or None
+    -> (out [B,num_steps,D] fp32, padding mask [B,num_steps] int32)."""
+    _chk(traj, torch.float32, "traj_preprocess.traj")
+    traj = traj.contiguous()
+    B, T, D = traj.shape
+    if lens is not None:
+        _chk(lens, torch.int32, "traj_preprocess.lens")
+    out = torch.empty(B, num_steps, D, device=traj.device, dtype=torch.float32)
+    mask = torch.empty(B, num_steps, device=traj.device, dtype=torch.int32)
+    _l.call("esb_traj_preprocess", traj.data_ptr(), _p(lens), B, T, D, int(num_steps), 1 if smooth else 0, out.data_ptr(),
+            mask.data_ptr(), _stream())
+    return out, mask
+
+
 def rgbd_to_points(rgbd: torch.Tensor, boxes: Optional[torch.Tensor], principal_point: float, focal_x: float, focal_y: float,
                    d_thres: Optional[float] = None, cap: Optional[int] = None):
     """pcm_tools.py:68-96 get_points_colors on device: rgbd [H,W,4] fp32, boxes [nb,4] int32 {xmin,ymin,xmax,ymax} or None

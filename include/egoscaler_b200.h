@@ -253,6 +253,12 @@ int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T,
                           int64_t tsep_id, int64_t te_id, int64_t eos_id, int64_t pad_id, int norm, const double* range6, int out_ld,
                           int64_t* out, int32_t* out_len, void* stream);
 
+/* egoscaler/models/utils/traj_utils.py: smoothing_traj :42-96 (smooth != 0; position columns 0..2, the reference's edge rules,
+ * fp32) then preprocess_traj :3-40 to num_steps (linspace-index gather when len >= num_steps, else pad with the last point).
+ * traj [B,T,D] fp32, lens [B] (NULL: T) -> out [B,num_steps,D], mask [B,num_steps] int32 (1 = real step, 0 = padding; or NULL). */
+int esb_traj_preprocess(const float* traj, const int32_t* lens, int B, int T, int D, int num_steps, int smooth, float* out,
+                        int32_t* mask, void* stream);
+
 /* ------------------------------------------------------------------------------------------------ RGB-D front-end
  * Producer of `pcrgbs`.  esb_rgbd_to_points replaces egoscaler/data/tools/pcm_tools.py:68-96 get_points_colors
  * (call sites data/train/7_get_object_trajectory.py:191-200,244-253; unprojection also depth.py:55-60): rgbd [H,W,4] fp32

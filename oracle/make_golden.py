@@ -403,12 +403,44 @@ def golden_rgbd_frontend():
     np.savez_compressed(os.path.join(GOLD, "rgbd_frontend.npz"), **out)
 
 
+def golden_traj_preprocess():
+    """Outputs of the REAL egoscaler/models/utils/traj_utils.py (pure numpy) on seeded float32 trajectories of every edge
+    length (1..6) and longer ones, for num_steps 20 (the reference's) and 7."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_traj_utils", os.path.join(ref_shim.REF_ROOT, "egoscaler/models/utils/traj_utils.py"))
+    tu = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tu)
+    rng = np.random.default_rng(21)
+    lens = np.asarray([1, 2, 3, 4, 5, 6, 7, 19, 20, 21, 33, 80, 81, 64], np.int32)
+    T = int(lens.max())
+    traj = rng.uniform(-2, 2, (len(lens), T, 6)).astype(np.float32)
+    out = dict(traj=traj, lens=lens)
+    for ns in (20, 7):
+        for smooth in (0, 1):
+            res = np.zeros((len(lens), ns, 6), np.float32)
+            msk = np.zeros((len(lens), ns), np.int32)
+            for b, n in enumerate(lens):
+                t = traj[b, :n]
+                if smooth:
+                    t = tu.smoothing_traj(t)
+                    assert t.dtype == np.float32
+                r, m = tu.preprocess_traj(t, ns, return_padding_mask=True)
+                res[b], msk[b] = r, m
+            out[f"out/{ns}/{smooth}"] = res
+            out[f"mask/{ns}/{smooth}"] = msk
+    np.savez_compressed(os.path.join(GOLD, "traj_preprocess.npz"), **out)
+    print("traj_preprocess.npz", {k: v.shape for k, v in out.items()})
+
+
 if __name__ == "__main__":
     import sys
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
     if len(sys.argv) > 1 and sys.argv[1] == "metrics":
         golden_metrics()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "traj_preprocess":
+        golden_traj_preprocess()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "rgbd":
         golden_rgbd_frontend()

@@ -166,3 +166,39 @@ def norm_poses(traj: np.ndarray) -> np.ndarray:
         t[..., j] = 2.0 * (t[..., j] - r["min_" + ax]) / (r["max_" + ax] - r["min_" + ax]) - 1.0
     t[..., 3:] = t[..., 3:] / np.pi
     return t.astype(np.float32)
+
+
+# ---------------------------------------------------------------------------------------------- pre-processing (N3)
+def smoothing_traj(traj):
+    """egoscaler/models/utils/traj_utils.py:42-96 restated with slices: moving average over columns 0..2 with the reference's
+    edge rules (branch order j==0, j==1, j==T-2, j==T-1, general); summation left to right in the input dtype."""
+    traj = np.asarray(traj)
+    p = traj[:, :3]
+    n = p.shape[0]
+    q = p.copy()
+    if n >= 5:
+        q[2:n - 2] = (p[0:n - 4] + p[1:n - 3] + p[2:n - 2] + p[3:n - 1] + p[4:n]) / 5
+    if n >= 3:
+        q[0] = (3 * p[0] + p[1] + p[2]) / 5
+    elif n == 2:
+        q[0] = (3 * p[0] + p[1]) / 4
+    if n >= 4:
+        q[1] = (2 * p[0] + p[1] + p[2] + p[3]) / 5
+    elif n == 3:
+        q[1] = (2 * p[0] + p[1] + p[2]) / 4
+    if n >= 4:                                      # j == n-2 (and j >= 2)
+        q[n - 2] = (p[n - 4] + p[n - 3] + p[n - 2] + p[n - 1]) / 4
+    if n >= 3:                                      # j == n-1 (and j >= 2)
+        q[n - 1] = (p[n - 3] + p[n - 2] + p[n - 1]) / 3
+    return np.concatenate([q, traj[:, 3:]], axis=-1)
+
+
+def preprocess_traj(traj, num_steps):
+    """traj_utils.py:3-40: -> (resampled [num_steps, D], padding mask [num_steps] int)."""
+    traj = np.asarray(traj)
+    T = traj.shape[0]
+    if T >= num_steps:
+        idx = np.linspace(0, T - 1, num_steps).astype(int)
+        return traj[idx], np.ones(num_steps, dtype=int)
+    pad = num_steps - T
+    return np.vstack([traj, np.repeat(traj[-1:], pad, axis=0)]), np.concatenate([np.ones(T, dtype=int), np.zeros(pad, dtype=int)])

@@ -295,3 +295,18 @@ def test_rgbd_frontend_oracle_matches_reference():
             pc = np.concatenate([pts[idx], cols[idx].astype(np.float64)], axis=1)
             assert np.array_equal(rf.pc_norm(pc), g[f"{name}/pc_norm"]), name
     assert g["all_boxed/points"].shape == (0, 3)
+
+
+def test_traj_preprocess_oracle_matches_reference():
+    """oracle smoothing_traj / preprocess_traj vs outputs of the real traj_utils.py (tests/golden/traj_preprocess.npz)."""
+    from oracle import traj_tokenizer as ot
+    g = np.load(os.path.join(GOLDEN, "traj_preprocess.npz"))
+    for ns in (20, 7):
+        for smooth in (0, 1):
+            for b, n in enumerate(g["lens"]):
+                t = g["traj"][b, :n]
+                if smooth:
+                    t = ot.smoothing_traj(t)
+                r, m = ot.preprocess_traj(t, ns)
+                assert np.array_equal(r, g[f"out/{ns}/{smooth}"][b]), (ns, smooth, n)
+                assert np.array_equal(m, g[f"mask/{ns}/{smooth}"][b])

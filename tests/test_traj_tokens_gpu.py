@@ -183,3 +183,24 @@ def test_poses_to_ids_roundtrip_and_oracle():
     back2, _ = ops.traj_ids_to_poses(torch.from_numpy(ids2).cuda(), max_steps=T, scale=ops.SCALE_DENORM, pad_repeat=False)
     err = np.abs(back2.cpu().numpy() - phys)
     assert err[..., :2].max() <= 4.0 / 255 + 1e-5 and err[..., 2].max() <= 2.5 / 255 + 1e-5 and err[..., 3:].max() <= 2 * np.pi / 255 + 1e-5
+
+
+def test_traj_preprocess_matches_reference_golden():
+    """csrc/traj_tokens.cu traj_preprocess vs outputs of the real traj_utils.py (smoothing_traj then preprocess_traj) for
+    every edge length: bit-exact, incl. the padding mask."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "traj_preprocess.npz"))
+    traj = torch.from_numpy(g["traj"]).cuda()
+    lens = torch.from_numpy(g["lens"]).cuda()
+    for ns in (20, 7):
+        for smooth in (0, 1):
+            out, mask = ops.traj_preprocess(traj, lens, ns, smooth=bool(smooth))
+            assert np.array_equal(out.cpu().numpy(), g[f"out/{ns}/{smooth}"]), (ns, smooth)
+            assert np.array_equal(mask.cpu().numpy(), g[f"mask/{ns}/{smooth}"])
+    # lens=None: every row uses all T steps
+    out, mask = ops.traj_preprocess(traj[:3], None, 20, smooth=True)
+    from oracle import traj_tokenizer as ot
+    for b in range(3):
+        r, m = ot.preprocess_traj(ot.smoothing_traj(g["traj"][b]), 20)
+        assert np.array_equal(out[b].cpu().numpy(), r) and np.array_equal(mask[b].cpu().numpy(), m)
