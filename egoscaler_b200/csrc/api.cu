@@ -9,6 +9,7 @@
 namespace esb {
 
 static thread_local char g_err[512] = "";
+int g_pdl_chain = 0;
 
 void set_last_error(const char* fmt, ...) {
     va_list ap;
@@ -98,6 +99,11 @@ int esb_traj_poses_to_ids(const float* poses, const int32_t* lens, int B, int T,
 int esb_traj_preprocess(const float* traj, const int32_t* lens, int B, int T, int D, int num_steps, int smooth, float* out,
                         int32_t* mask, void* stream) {
     return traj_preprocess(traj, lens, B, T, D, num_steps, smooth, out, mask, ST(stream));
+}
+
+int esb_set_pdl_chain(int on) {
+    g_pdl_chain = on ? 1 : 0;
+    return ESB_OK;
 }
 
 int64_t esb_rgbd_workspace_bytes(int H, int W) { return rgbd_workspace_bytes(H, W); }

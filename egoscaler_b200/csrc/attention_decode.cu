@@ -24,6 +24,8 @@ __global__ void __launch_bounds__(DEC_THREADS) attn_decode_kernel(const __nv_bfl
     constexpr int VPL = EPL / 8;                 // 16-byte vectors per lane
     __shared__ float s_acc[DEC_GROUPS][HD];
     __shared__ float s_m[DEC_GROUPS], s_l[DEC_GROUPS];
+    griddep_launch();
+    griddep_wait();
     const int h = blockIdx.x, b = blockIdx.y;
     const int grp = threadIdx.x >> 3, sub = threadIdx.x & 7;
     const int Lk = len_static + (len_ptr ? *len_ptr : 0);
@@ -123,8 +125,8 @@ int attn_decode(const void* q, long long q_bs, const void* k, const void* v, lon
     if ((q_bs & 7) || (kv_bs & 7) || (kv_rs & 7)) { set_last_error("attn_decode: strides must keep 16-byte alignment"); return ESB_ERR_INVALID_ARG; }
     dim3 grid(H, B);
     const __nv_bfloat16 *qq = static_cast<const __nv_bfloat16*>(q), *kk = static_cast<const __nv_bfloat16*>(k), *vv = static_cast<const __nv_bfloat16*>(v);
-    if (hd == 128) attn_decode_kernel<128><<<grid, DEC_THREADS, 0, s>>>(qq, q_bs, kk, vv, kv_bs, kv_rs, static_cast<__nv_bfloat16*>(o), o_bs, kmask, kmask_ld, len_ptr, len_static, scale);
-    else if (hd == 64) attn_decode_kernel<64><<<grid, DEC_THREADS, 0, s>>>(qq, q_bs, kk, vv, kv_bs, kv_rs, static_cast<__nv_bfloat16*>(o), o_bs, kmask, kmask_ld, len_ptr, len_static, scale);
+    if (hd == 128) launch_chain(attn_decode_kernel<128>, grid, dim3(DEC_THREADS), 0, s, qq, q_bs, kk, vv, kv_bs, kv_rs, static_cast<__nv_bfloat16*>(o), o_bs, kmask, kmask_ld, len_ptr, len_static, scale);
+    else if (hd == 64) launch_chain(attn_decode_kernel<64>, grid, dim3(DEC_THREADS), 0, s, qq, q_bs, kk, vv, kv_bs, kv_rs, static_cast<__nv_bfloat16*>(o), o_bs, kmask, kmask_ld, len_ptr, len_static, scale);
     else { set_last_error("attn_decode: head_dim %d unsupported", hd); return ESB_ERR_UNSUPPORTED; }
     return check_launch("attn_decode");
 }

@@ -89,6 +89,11 @@ ESB_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
 // griddepcontrol.wait: returns once the grid this one programmatically depends on has completed and flushed its
 // memory (no-op for a kernel launched without cudaLaunchAttributeProgrammaticStreamSerialization).
 ESB_DEVICE void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// griddepcontrol.launch_dependents: once every CTA of this grid has issued it (or exited), the CTAs of a dependent grid
+// launched with the programmatic attribute may become resident and run their prologue up to their own griddepcontrol.wait.
+// Every kernel on a programmatic chain issues griddep_wait() on all paths before touching memory another kernel owns, so
+// completion order stays transitive along the chain.
+ESB_DEVICE void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ----------------------------------------------------------------------------- TMA
 ESB_DEVICE void tma_prefetch_desc(const CUtensorMap* m) {

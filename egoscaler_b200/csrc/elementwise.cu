@@ -28,6 +28,8 @@ __global__ void __launch_bounds__(256) rope_kernel(__nv_bfloat16* __restrict__ b
                                                    int pos0, const int* __restrict__ pos_ptr, float sign, long long rows,
                                                    __nv_bfloat16* __restrict__ kcache, __nv_bfloat16* __restrict__ vcache,
                                                    int kv_head0, int kv_heads, long long v_col0, int cache_len) {
+    griddep_launch();
+    griddep_wait();
     const int half = hd >> 1;
     const int vec_per_head = half >> 3;
     if (pos_ptr) pos0 += *pos_ptr;                 // device-side position (CUDA-graph replay of the decode step)
@@ -83,10 +85,10 @@ int rope(void* buf, long long ld, long long rows, int L, int n_heads, int hd, co
     if (rows <= 0) return ESB_OK;
     if ((hd & 15) || (ld & 7)) { set_last_error("rope: head_dim must be a multiple of 16 and ld of 8"); return ESB_ERR_INVALID_ARG; }
     const long long total = rows * n_heads * (hd / 16);
-    rope_kernel<<<ew_grid(total, 256), 256, 0, s>>>(static_cast<__nv_bfloat16*>(buf), ld, L, n_heads, hd,
-                                                    static_cast<const __nv_bfloat16*>(cos_tab), static_cast<const __nv_bfloat16*>(sin_tab),
-                                                    pos0, pos_ptr, inverse ? -1.0f : 1.0f, rows, static_cast<__nv_bfloat16*>(kcache),
-                                                    static_cast<__nv_bfloat16*>(vcache), kv_head0, kv_heads, v_col0, cache_len);
+    launch_chain(rope_kernel, dim3(ew_grid(total, 256)), dim3(256), 0, s, static_cast<__nv_bfloat16*>(buf), ld, L, n_heads, hd,
+                 static_cast<const __nv_bfloat16*>(cos_tab), static_cast<const __nv_bfloat16*>(sin_tab), pos0, pos_ptr,
+                 inverse ? -1.0f : 1.0f, rows, static_cast<__nv_bfloat16*>(kcache), static_cast<__nv_bfloat16*>(vcache), kv_head0,
+                 kv_heads, v_col0, cache_len);
     return check_launch("rope");
 }
 
@@ -94,6 +96,8 @@ int rope(void* buf, long long ld, long long rows, int L, int n_heads, int hd, co
 // gu [rows, 2f] (gate | up)  ->  act [rows, f] = bf16(bf16(silu(g)) * u)
 __global__ void __launch_bounds__(256) silu_mul_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act,
                                                            long long rows, int f) {
+    griddep_launch();
+    griddep_wait();
     const int fv = f >> 3;
     const long long total = rows * fv;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -141,7 +145,8 @@ __global__ void __launch_bounds__(256) silu_mul_bwd_kernel(const __nv_bfloat16* 
 int silu_mul_fwd(const void* gu, void* act, long long rows, int f, cudaStream_t s) {
     if (rows <= 0) return ESB_OK;
     if (f & 7) { set_last_error("silu_mul: f must be a multiple of 8"); return ESB_ERR_INVALID_ARG; }
-    silu_mul_fwd_kernel<<<ew_grid(rows * (f / 8), 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(gu), static_cast<__nv_bfloat16*>(act), rows, f);
+    launch_chain(silu_mul_fwd_kernel, dim3(ew_grid(rows * (f / 8), 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(gu),
+                 static_cast<__nv_bfloat16*>(act), rows, f);
     return check_launch("silu_mul_fwd");
 }
 int silu_mul_bwd(const void* gu, const void* dact, void* dgu, long long rows, int f, cudaStream_t s) {

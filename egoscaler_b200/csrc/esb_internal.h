@@ -12,6 +12,26 @@ const char* last_error();
 int check_launch(const char* what);
 int device_sm_count();
 
+// Decode-step launch chain (esb_set_pdl_chain): when on, launch_chain() adds cudaLaunchAttributeProgrammaticStreamSerialization,
+// so the kernel's CTAs are scheduled while its predecessor drains and park in griddepcontrol.wait (launch latency and, for
+// the skinny GEMM, the weight-ring prefetch overlap the predecessor).  Only kernels that begin with griddep_wait() use it.
+extern int g_pdl_chain;
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl_chain ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
 
 // 3-D bf16 tensor {cols (contiguous), rows, batches} with row / batch strides in elements; box = {box_cols, box_rows, 1},

@@ -70,6 +70,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int units = p.n_tiles * p.splits;
+    griddep_launch();                                     // dependents park in their own griddepcontrol.wait
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_w);

@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const __nv_bfloat16* _
                                                           __nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out,
                                                           int d, long long ldx, long long ldy, float eps) {
     __shared__ float red[32];
+    griddep_launch();
+    griddep_wait();
     const long long row = blockIdx.x;
     const uint4* xp = reinterpret_cast<const uint4*>(x + row * ldx);
     const int nv = d >> 3;
@@ -177,8 +179,8 @@ int rmsnorm_fwd(const void* x, long long ldx, const void* w, void* y, long long 
     if ((d & 7) || (ldx & 7) || (ldy & 7)) { set_last_error("rmsnorm_fwd: d/ld must be multiples of 8 (d=%d)", d); return ESB_ERR_INVALID_ARG; }
     int threads = ((d / 8 + 31) / 32) * 32;
     threads = threads > 256 ? 256 : (threads < 32 ? 32 : threads);
-    rmsnorm_fwd_kernel<<<static_cast<unsigned>(rows), threads, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), static_cast<__nv_bfloat16*>(y), rstd, d, ldx, ldy, eps);
+    launch_chain(rmsnorm_fwd_kernel, dim3(static_cast<unsigned>(rows)), dim3(threads), 0, s,
+                 static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), static_cast<__nv_bfloat16*>(y), rstd, d, ldx, ldy, eps);
     return check_launch("rmsnorm_fwd");
 }
 

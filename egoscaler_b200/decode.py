@@ -78,8 +78,9 @@ def generate(model: TrajPointLLMForCausalLM, input_ids: torch.Tensor, attention_
     pos_dev = torch.full((1,), P, device=dev, dtype=torch.int32)
 
     def token_step():
-        hl_, _ = model.hidden_states(tok, mask, None, None, cache, pos_dev=pos_dev)
-        lg = model.logits_from_hidden(hl_, decode=True)
+        with ops.pdl_chain():
+            hl_, _ = model.hidden_states(tok, mask, None, None, cache, pos_dev=pos_dev)
+            lg = model.logits_from_hidden(hl_, decode=True)
         pick(lg, 1 - P, pos_dev, scores, 1, pos_dev)
         ops.greedy_update(nxt, tok.view(B), unfinished, seq, 1, mask, cfg.eos_token_id, cfg.pad_token_id, pos_ptr=pos_dev)
 

@@ -34,6 +34,7 @@ def _chk(t: torch.Tensor, dtype, name: str):
 
 # ------------------------------------------------------------------------------------------------ GEMM
 SKINNY_MAX_M = 64
+pdl_chain_enabled = False  # small kernels of the decode step on the programmatic launch chain too (esb_set_pdl_chain): measured 5.51 vs 5.29-5.45 ms/token off (tools/decode_variants.py), so off; the early launch_dependents triggers in those kernels stay (they let the PDL GEMMs prefetch)
 pdl_enabled = True        # programmatic dependent launch of the decode-step GEMMs (tools/decode_variants.py toggles it)
 skinny_enabled = True
 _SKINNY_WS_BYTES = 96 << 20        # counters (16 KiB, zero) + fp32 split-K partials; lm_head at 9 splits needs ~37 MB
@@ -653,3 +654,17 @@ def pc_sample_norm(points: torch.Tensor, idx: Optional[torch.Tensor] = None, n: 
     out = torch.empty(B, S, 6, device=points.device, dtype=torch.float32)
     _l.call("esb_pc_sample_norm", points.data_ptr(), N * 6, n, _p(idx), B, S, out.data_ptr(), _stream())
     return out
+
+
+class pdl_chain:
+    """Context manager around the single-token decode step: launches inside it use programmatic stream serialization
+    (esb_set_pdl_chain); a no-op when ``pdl_chain_enabled`` is False."""
+
+    def __enter__(self):
+        if pdl_chain_enabled:
+            _l.lib().raw("esb_set_pdl_chain")(1)
+        return self
+
+    def __exit__(self, *exc):
+        _l.lib().raw("esb_set_pdl_chain")(0)
+        return False

@@ -42,6 +42,11 @@ extern "C" {
 
 int esb_version(void);
 const char* esb_last_error(void);
+/* Launch mode of the single-token decode step (decode.py token_step; reference loop: HF generate driven by model_arch.py:94-108).
+ * on != 0: the small kernels of the step (rmsnorm, rope, silu*mul, decode attention, embedding, arg-max, bookkeeping) are
+ * launched with programmatic stream serialization, like the skinny GEMMs already are: each parks in griddepcontrol.wait
+ * until its predecessor has completed, so results are unchanged and launch latency overlaps.  Process-global; default off. */
+int esb_set_pdl_chain(int on);
 int esb_device_sm_count(void);
 
 /* ------------------------------------------------------------------------------------------------ GEMM

@@ -32,13 +32,21 @@ def run(t_new, graph):
     return e0.elapsed_time(e1)
 
 
-for skinny, pdl in ((True, True), (True, False), (True, True), (True, False), (False, False)):
+seqs = {}
+for skinny, pdl, chain in ((True, True, True), (True, True, False), (True, True, True), (True, True, False), (True, False, False),
+                           (False, False, False)):
     ops.SKINNY_MAX_M = 64 if skinny else 0
     ops.skinny_enabled = skinny
     ops.pdl_enabled = pdl
-    print("pdl", pdl, end=" ")
+    ops.pdl_chain_enabled = chain
+    print("pdl", pdl, "chain", chain, end=" ")
     for graph in (True,):
         run(4, graph)
         t1 = min(run(1, graph) for _ in range(2))
         tT = min(run(T, graph) for _ in range(2))
         print(f"skinny={skinny} graph={graph}: prefill+1 {t1:.1f} ms, {T} tokens {tT:.1f} ms -> {(tT - t1) / (T - 1):.3f} ms/token", flush=True)
+    out = model.generate(max_length=12, use_cuda_graph=True, **args)
+    seqs[(skinny, pdl, chain)] = out.sequences.cpu()
+ref = seqs[(True, False, False)]
+for k, v in seqs.items():
+    print(k, "ids equal to the no-PDL run:", bool(torch.equal(v, ref)))
