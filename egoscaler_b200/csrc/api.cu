@@ -71,6 +71,16 @@ int esb_retile_weight_bf16(const void* W, int64_t ldw, int N, int K, void* out, 
     return retile_weight_bf16(W, ldw, N, K, out, ST(stream));
 }
 
+int esb_retile_weight_scaled_bf16(const void* W, int64_t ldw, int N, int K, const void* col_scale, void* out, void* stream) {
+    return retile_weight_scaled_bf16(W, ldw, N, K, col_scale, out, ST(stream));
+}
+int esb_gemm_skinny_normed_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
+                                const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,
+                                int w_tiled, const float* scale_src, int scale_parts, float eps, float* ssq_out, void* stream) {
+    return gemm_skinny_normed_bf16(X, ldx, W, ldw, C, ldc, M, N, K, residual, ldr, workspace, workspace_bytes, force_splits, w_tiled,
+                                   scale_src, scale_parts, eps, ssq_out, ST(stream));
+}
+
 int esb_traj_quantize(const void* x, int is_f64, int64_t n, int num_bins, int64_t id_offset, int64_t* out, void* stream) {
     return traj_quantize(x, is_f64, n, num_bins, id_offset, reinterpret_cast<long long*>(out), ST(stream));
 }

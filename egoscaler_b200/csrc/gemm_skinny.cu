@@ -40,6 +40,12 @@ struct SkinnyParams {
     int w_tiled;      // 1: W is pre-tiled [n_tiles][num_kb][128][64] (esb_retile_weight_bf16), every stage one contiguous 16 KB
     float* partial;   // [n_tiles][splits][BT][128] fp32
     int* counters;    // [n_tiles], zero on entry and on exit
+    // RMSNorm folded around the GEMM (decode step): the norm weight is folded into W at retile time, the per-token 1/rms
+    // is applied to the accumulator here, and the GEMM that PRODUCES the next norm's input leaves its sum of squares behind.
+    const float* scale_src;   // NULL: none; scale_parts == 0: rstd[m] itself; else per-tile sums of squares [scale_parts][64]
+    int scale_parts;
+    float scale_inv_d, scale_eps;
+    float* ssq_out;           // NULL or [n_tiles][64]: sum over this tile's 128 columns of bf16(out[m, :])^2
 };
 
 template <int BT, int SK_STAGES>
@@ -47,7 +53,7 @@ struct SkinnySmem {
     static constexpr int W_BYTES = SK_ROWS * SK_BK * 2;
     static constexpr int X_BYTES = BT * SK_BK * 2;
     static constexpr int STAGE_BYTES = W_BYTES + X_BYTES;
-    static constexpr int TOTAL = SK_STAGES * STAGE_BYTES + 1024 + 1024;
+    static constexpr int TOTAL = SK_STAGES * STAGE_BYTES + 1024 + 1024 + 1024;     // + s_red [4][64] fp32
 };
 
 ESB_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
@@ -66,6 +72,8 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
     uint64_t* tmem_empty = bars + 2 * SK_STAGES + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * SK_STAGES + 4);
     volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
+    float* s_scale = reinterpret_cast<float*>(tmem_slot + 4);                       // [64] per-token scale of the accumulator
+    float (*s_red)[64] = reinterpret_cast<float (*)[64]>(smem + SK_STAGES * S::STAGE_BYTES + 1024);   // [4][64]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -178,6 +186,22 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
         const int nl = q * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
+        const bool scaled = p.scale_src != nullptr;
+        if (scaled) {
+            if (nl < 64) {
+                float sc = 1.0f;
+                if (nl < p.M) {
+                    if (p.scale_parts == 0) sc = __ldcg(p.scale_src + nl);
+                    else {
+                        float t = 0.0f;
+                        for (int j = 0; j < p.scale_parts; ++j) t += __ldcg(p.scale_src + j * 64 + nl);   // fixed order
+                        sc = rsqrtf(t * p.scale_inv_d + p.scale_eps);
+                    }
+                }
+                s_scale[nl] = sc;
+            }
+            epi_bar_sync();
+        }
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
             const int tile = u / p.splits, s = u - tile * p.splits;
             const int n = tile * SK_ROWS + nl;
@@ -193,15 +217,22 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                 tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
                 tmem_ld_wait();
                 if (p.splits == 1) {
-                    if (n_ok) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const int m = c * 32 + j;
-                            if (m < p.M) {
-                                float v = __uint_as_float(r[j]);
-                                if (p.res) v += __bfloat162float(p.res[static_cast<long long>(m) * p.ldr + n]);
-                                p.C[static_cast<long long>(m) * p.ldc + n] = __float2bfloat16_rn(v);
-                            }
+                    for (int j = 0; j < 32; ++j) {
+                        const int m = c * 32 + j;
+                        float sq = 0.0f;
+                        if (n_ok && m < p.M) {
+                            float v = __uint_as_float(r[j]);
+                            if (scaled) v *= s_scale[m];
+                            if (p.res) v += __bfloat162float(p.res[static_cast<long long>(m) * p.ldr + n]);
+                            const __nv_bfloat16 ob = __float2bfloat16_rn(v);
+                            p.C[static_cast<long long>(m) * p.ldc + n] = ob;
+                            const float of = __bfloat162float(ob);
+                            sq = of * of;
+                        }
+                        if (p.ssq_out) {
+                            sq = warp_sum(sq);
+                            if (lane == 0) s_red[q][m] = sq;
                         }
                     }
                 } else {
@@ -214,6 +245,11 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
             mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1u;
+            if (p.splits == 1 && p.ssq_out) {
+                epi_bar_sync();
+                if (nl < p.M) p.ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
+                epi_bar_sync();
+            }
             if (p.splits > 1) {
                 __threadfence();
                 epi_bar_sync();
@@ -226,7 +262,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                 epi_bar_sync();
                 if (*last_flag) {
                     __threadfence();
-                    if (n_ok) {
+                    {
                         // fixed summation order s = 0..S-1 per element; 16 tokens x 4 slices of loads in flight
                         const float* base = p.partial + static_cast<size_t>(tile) * p.splits * (BT * SK_ROWS) + nl;
 #pragma unroll 1
@@ -242,7 +278,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                                     for (int j = 0; j < 16; ++j)
-                                        t[i][j] = __ldcg(base + (static_cast<size_t>(s2 + i) * BT + m0 + j) * SK_ROWS);
+                                        t[i][j] = n_ok ? __ldcg(base + (static_cast<size_t>(s2 + i) * BT + m0 + j) * SK_ROWS) : 0.0f;
 #pragma unroll
                                 for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -252,20 +288,35 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                             for (; s2 < p.splits; ++s2) {
                                 float t[16];
 #pragma unroll
-                                for (int j = 0; j < 16; ++j) t[j] = __ldcg(base + (static_cast<size_t>(s2) * BT + m0 + j) * SK_ROWS);
+                                for (int j = 0; j < 16; ++j)
+                                    t[j] = n_ok ? __ldcg(base + (static_cast<size_t>(s2) * BT + m0 + j) * SK_ROWS) : 0.0f;
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) v[j] += t[j];
                             }
 #pragma unroll
                             for (int j = 0; j < 16; ++j) {
                                 const int m = m0 + j;
-                                if (m < p.M) {
+                                float sq = 0.0f;
+                                if (n_ok && m < p.M) {
                                     float o = v[j];
+                                    if (scaled) o *= s_scale[m];
                                     if (p.res) o += __bfloat162float(p.res[static_cast<long long>(m) * p.ldr + n]);
-                                    p.C[static_cast<long long>(m) * p.ldc + n] = __float2bfloat16_rn(o);
+                                    const __nv_bfloat16 ob = __float2bfloat16_rn(o);
+                                    p.C[static_cast<long long>(m) * p.ldc + n] = ob;
+                                    const float of = __bfloat162float(ob);
+                                    sq = of * of;
+                                }
+                                if (p.ssq_out) {
+                                    sq = warp_sum(sq);
+                                    if (lane == 0 && m < 64) s_red[q][m] = sq;
                                 }
                             }
                         }
+                    }
+                    if (p.ssq_out) {
+                        epi_bar_sync();
+                        if (nl < p.M) p.ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
+                        epi_bar_sync();
                     }
                 }
             }
@@ -316,7 +367,7 @@ namespace {
 // tile (tile, kb) = W[tile*128 .. +128][kb*64 .. +64] (zero beyond N / K), 16 KiB contiguous, stored as the 128-byte-swizzled
 // shared-memory image tcgen05 expects (16-byte chunk c of row r at chunk c ^ (r & 7)), so a 1-D bulk copy stages it.
 __global__ void retile_weight_kernel(const __nv_bfloat16* __restrict__ W, long long ldw, int N, int K, int num_kb,
-                                     long long total_vec, uint4* __restrict__ out) {
+                                     long long total_vec, uint4* __restrict__ out, const __nv_bfloat16* __restrict__ col_scale) {
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total_vec;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
         const int c8 = static_cast<int>(i & 7);
@@ -333,6 +384,12 @@ __global__ void retile_weight_kernel(const __nv_bfloat16* __restrict__ W, long l
             for (int j = 0; j < 8; ++j) t[j] = (k + j < K) ? W[n * ldw + k + j] : __float2bfloat16(0.0f);
             v = *reinterpret_cast<uint4*>(t);
         }
+        if (col_scale && n < N && k < K) {                               // fold a norm weight g[k] into the column: bf16(W * g)
+            __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(&v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (k + j < K) e[j] = __float2bfloat16_rn(__bfloat162float(e[j]) * __bfloat162float(col_scale[k + j]));
+        }
         out[(i & ~7ll) | static_cast<long long>(c8 ^ (r & 7))] = v;     // SWIZZLE_128B image of the smem tile
     }
 }
@@ -343,6 +400,10 @@ long long retiled_weight_elems(int N, int K) {
 }
 
 int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cudaStream_t stream) {
+    return retile_weight_scaled_bf16(W, ldw, N, K, nullptr, out, stream);
+}
+
+int retile_weight_scaled_bf16(const void* W, long long ldw, int N, int K, const void* col_scale, void* out, cudaStream_t stream) {
     if (N <= 0 || K <= 0 || !W || !out || (ldw & 7) || (reinterpret_cast<uintptr_t>(W) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) {
         set_last_error("retile_weight_bf16: bad arguments (N=%d K=%d ldw=%lld)", N, K, ldw);
         return ESB_ERR_INVALID_ARG;
@@ -351,7 +412,7 @@ int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cu
     const long long total_vec = retiled_weight_elems(N, K) / 8;
     const int grid = device_sm_count() * 8;
     retile_weight_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(W), ldw, N, K, num_kb, total_vec,
-                                                   reinterpret_cast<uint4*>(out));
+                                                   reinterpret_cast<uint4*>(out), reinterpret_cast<const __nv_bfloat16*>(col_scale));
     return check_launch("retile_weight");
 }
 
@@ -364,7 +425,18 @@ long long gemm_skinny_workspace_bytes(int M, int N, int K) {
 int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
                      const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,
                      int w_tiled, cudaStream_t stream) {
+    return gemm_skinny_normed_bf16(X, ldx, W, ldw, C, ldc, M, N, K, residual, ldr, workspace, workspace_bytes, force_splits, w_tiled,
+                                   nullptr, 0, 0.0f, nullptr, stream);
+}
+
+int gemm_skinny_normed_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                            const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,
+                            int w_tiled, const float* scale_src, int scale_parts, float eps, float* ssq_out, cudaStream_t stream) {
     if (M <= 0 || N <= 0) return ESB_OK;
+    if (scale_parts < 0 || scale_parts > 1024) {
+        set_last_error("gemm_skinny_normed_bf16: scale_parts=%d out of range", scale_parts);
+        return ESB_ERR_INVALID_ARG;
+    }
     if (M > 64 || K <= 0 || !X || !W || !C) {
         set_last_error("gemm_skinny_bf16: bad arguments (M=%d (max 64) N=%d K=%d)", M, N, K);
         return ESB_ERR_INVALID_ARG;
@@ -428,6 +500,8 @@ int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw,
     p.counters = reinterpret_cast<int*>(workspace);
     p.partial = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_COUNTER_BYTES) : nullptr;
     p.w_tiles = reinterpret_cast<const uint8_t*>(W);
+    p.scale_src = scale_src; p.scale_parts = scale_parts; p.scale_inv_d = 1.0f / static_cast<float>(K); p.scale_eps = eps;
+    p.ssq_out = ssq_out;
     const long long units = static_cast<long long>(n_tiles) * best_s;
     const int grid = static_cast<int>(units < slots ? units : slots);
     const bool pdl = (w_tiled & 2) != 0;          // caller promises W is not written by the kernel launched just before

@@ -210,6 +210,11 @@ int rgbd_to_points(const float* rgbd, int H, int W, const int* boxes, int n_boxe
         set_last_error("rgbd_to_points: bad arguments (H=%d W=%d n_boxes=%d fx=%g fy=%g)", H, W, n_boxes, fx, fy);
         return ESB_ERR_INVALID_ARG;
     }
+    if ((reinterpret_cast<uintptr_t>(rgbd) & 15) || (n_boxes > 0 && (reinterpret_cast<uintptr_t>(boxes) & 15)) ||
+        (reinterpret_cast<uintptr_t>(workspace) & 7)) {
+        set_last_error("rgbd_to_points: rgbd / boxes must be 16-byte aligned and the workspace 8-byte aligned");
+        return ESB_ERR_INVALID_ARG;
+    }
     if (!workspace || workspace_bytes < rgbd_workspace_bytes(H, W)) {
         set_last_error("rgbd_to_points: workspace %lld B < %lld B", workspace_bytes, rgbd_workspace_bytes(H, W));
         return ESB_ERR_INVALID_ARG;

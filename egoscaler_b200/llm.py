@@ -53,12 +53,15 @@ class LayerWeights:
     to: Optional["ops.TiledWeight"] = None
     tgu: Optional["ops.TiledWeight"] = None
     tdown: Optional["ops.TiledWeight"] = None
+    tiled_folded: bool = False          # tqkv / tgu carry ln1 / ln2 folded into their columns (ops.fold_norm_enabled)
 
-    def ensure_tiled(self):
-        if self.tqkv is None:
-            self.tqkv = ops.retile_weight(self.wqkv)
+    def ensure_tiled(self, folded: bool = False):
+        if self.tqkv is None or self.tiled_folded != folded:
+            self.tqkv = ops.retile_weight(self.wqkv, self.ln1 if folded else None)
+            self.tgu = ops.retile_weight(self.wgu, self.ln2 if folded else None)
+            self.tiled_folded = folded
+        if self.to is None:
             self.to = ops.retile_weight(self.wo)
-            self.tgu = ops.retile_weight(self.wgu)
             self.tdown = ops.retile_weight(self.wdown)
 
     def refresh_derived(self):
@@ -112,6 +115,7 @@ class LlamaTrunk:
         self.cfg = cfg
         self.layers = layers
         self.cos, self.sin = rope_tables(cfg.head_dim, cfg.rope_theta, cfg.max_position_embeddings, device)
+        self.decode_stat = None      # (fp32 statistics, parts) of the last decode step's output rows (_decode_step_folded)
 
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], pos0: int = 0,
@@ -125,9 +129,12 @@ class LlamaTrunk:
         decode = attn_decode and B <= ops.SKINNY_MAX_M      # weight-streaming GEMMs on the tiled copies
         if pos_dev is not None:          # graph-replayed decode step: the position lives in a device counter
             assert attn_decode and pos0 == 0
+        self.decode_stat = None
+        if decode and ops.fold_norm_enabled and saved is None:
+            return self._decode_step_folded(x, B, kmask, pos0, cache, pos_dev)
         if decode:
             for w in self.layers:          # decode-layout copies exist before the first kernel of the step is queued, so no
-                w.ensure_tiled()           # skinny GEMM is ever launched right behind the kernel that wrote its weights
+                w.ensure_tiled(False)      # skinny GEMM is ever launched right behind the kernel that wrote its weights
         for li, w in enumerate(self.layers):
             if saved is not None:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
@@ -166,6 +173,32 @@ class LlamaTrunk:
             if saved is not None:
                 saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu))
             x = out
+        return x
+
+    def _decode_step_folded(self, x: torch.Tensor, B: int, kmask, pos0: int, cache: KVCache, pos_dev) -> torch.Tensor:
+        """The cached single-token step with every RMSNorm folded around the Linear that consumes it (7 kernels per layer
+        instead of 9):  Linear(norm(x)) = rstd(x) * (x . (W * g)^T) - g lives in the decode-layout weight copy, rstd is applied
+        in the GEMM epilogue from the sums of squares the PRODUCING GEMM (o-proj / down-proj, which already hold the finished
+        row tile) left behind.  ``self.decode_stat`` hands the last layer's statistics to the final norm + lm_head."""
+        c = self.cfg
+        d, H, hd, eps = c.hidden_size, c.num_attention_heads, c.head_dim, c.rms_norm_eps
+        for w in self.layers:
+            w.ensure_tiled(True)
+        nt = (d + 127) // 128
+        _, rstd0 = ops.rmsnorm(x, self.layers[0].ln1, eps, want_rstd=True)      # statistics of the embedding rows
+        stat = (rstd0, 0)
+        ssq = torch.empty(2, nt, 64, device=x.device, dtype=torch.float32)
+        for li, w in enumerate(self.layers):
+            qkv = ops.gemm_skinny(x, w.tqkv, weights_const=True, row_scale=stat, eps=eps)
+            ops.rope_(qkv, 1, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
+                      kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len, pos_ptr=pos_dev)
+            o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_ptr=pos_dev, len_static=pos0 + 1)
+            h = ops.gemm_skinny(o, w.to, residual=x, weights_const=True, ssq_out=ssq[0])
+            gu = ops.gemm_skinny(h, w.tgu, weights_const=True, row_scale=(ssq[0], nt), eps=eps)
+            a = ops.silu_mul(gu)
+            x = ops.gemm_skinny(a, w.tdown, residual=h, weights_const=True, ssq_out=ssq[1])
+            stat = (ssq[1], nt)
+        self.decode_stat = stat
         return x
 
     # ------------------------------------------------------------------ backward (data gradients; frozen weights)

@@ -70,6 +70,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         self._trunk: Optional[LlamaTrunk] = None
         self._lm_head_T: Optional[torch.Tensor] = None
         self._lm_head_tiled = None                          # decode-layout copy of lm_head (ops.retile_weight)
+        self._lm_head_folded = False                        # ... with model.norm folded into its columns
         self.v_pad = (cfg.vocab_size + 7) // 8 * 8          # logits leading dimension (16-byte rows)
 
     # ------------------------------------------------------------------ reference API surface
@@ -217,11 +218,19 @@ class TrajPointLLMForCausalLM(ParamTree):
     def logits_from_hidden(self, h: torch.Tensor, decode: bool = False) -> torch.Tensor:
         """final RMSNorm + lm_head (pointllm.py:227-228) -> [rows, V] view of a [rows, v_pad] bf16 buffer."""
         skinny = decode and h.shape[0] <= ops.SKINNY_MAX_M       # cached single-token step: stream the tiled copy
-        if skinny and self._lm_head_tiled is None:
-            self._lm_head_tiled = ops.retile_weight(self.lm_head.weight.detach())
-        hn = ops.rmsnorm(h, self.model.norm.weight.detach(), self.cfg.rms_norm_eps)
+        stat = getattr(self.trunk, "decode_stat", None) if skinny else None     # final norm folded into lm_head (llm.py)
+        fresh = False
+        if skinny and (self._lm_head_tiled is None or self._lm_head_folded != (stat is not None)):
+            fresh = True                                    # written by the kernel just queued: no early weight prefetch this time
+            self._lm_head_folded = stat is not None
+            self._lm_head_tiled = ops.retile_weight(self.lm_head.weight.detach(),
+                                                    self.model.norm.weight.detach() if self._lm_head_folded else None)
         buf = torch.empty(h.shape[0], self.v_pad, device=h.device, dtype=torch.bfloat16)
         out = buf[:, :self.cfg.vocab_size]
+        if stat is not None:
+            ops.gemm_skinny(h, self._lm_head_tiled, out=out, weights_const=not fresh, row_scale=stat, eps=self.cfg.rms_norm_eps)
+            return out
+        hn = ops.rmsnorm(h, self.model.norm.weight.detach(), self.cfg.rms_norm_eps)
         if skinny:
             ops.gemm_skinny(hn, self._lm_head_tiled, out=out, weights_const=True)
         else:

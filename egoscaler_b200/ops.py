@@ -35,6 +35,10 @@ def _chk(t: torch.Tensor, dtype, name: str):
 # ------------------------------------------------------------------------------------------------ GEMM
 SKINNY_MAX_M = 64
 pdl_chain_enabled = False  # small kernels of the decode step on the programmatic launch chain too (esb_set_pdl_chain): measured 5.51 vs 5.29-5.45 ms/token off (tools/decode_variants.py), so off; the early launch_dependents triggers in those kernels stay (they let the PDL GEMMs prefetch)
+# decode step with RMSNorm folded around the skinny GEMMs (llm._decode_step_folded: 7 kernels per layer instead of 9).  Measured
+# round-robin against the plain step (tools/decode_variants.py, B=32, 100 tokens): 5.88 vs 5.90 ms/token - the norm kernels
+# were already hidden behind the PDL weight prefetch, so it stays off and the plain step remains the parity-pinned path.
+fold_norm_enabled = False
 pdl_enabled = True        # programmatic dependent launch of the decode-step GEMMs (tools/decode_variants.py toggles it)
 skinny_enabled = True
 _SKINNY_WS_BYTES = 96 << 20        # counters (16 KiB, zero) + fp32 split-K partials; lm_head at 9 splits needs ~37 MB
@@ -60,21 +64,31 @@ class TiledWeight:
         self.data, self.N, self.K = data, N, K
 
 
-def retile_weight(w: torch.Tensor) -> TiledWeight:
+def retile_weight(w: torch.Tensor, col_scale: Optional[torch.Tensor] = None) -> TiledWeight:
+    """``col_scale`` [K] bf16: the weight of the RMSNorm in front of this Linear, folded into its columns."""
     _chk(w, torch.bfloat16, "retile_weight.w")
     assert w.dim() == 2 and w.stride(1) == 1
     N, K = w.shape
     n = int(_l.lib().raw("esb_retiled_weight_elems")(N, K))
     out = torch.empty(n, device=w.device, dtype=torch.bfloat16)
-    _l.call("esb_retile_weight_bf16", w.data_ptr(), w.stride(0), N, K, out.data_ptr(), _stream())
+    if col_scale is None:
+        _l.call("esb_retile_weight_bf16", w.data_ptr(), w.stride(0), N, K, out.data_ptr(), _stream())
+    else:
+        _chk(col_scale, torch.bfloat16, "retile_weight.col_scale")
+        assert col_scale.numel() == K and col_scale.is_contiguous()
+        _l.call("esb_retile_weight_scaled_bf16", w.data_ptr(), w.stride(0), N, K, col_scale.data_ptr(), out.data_ptr(), _stream())
     return TiledWeight(out, N, K)
 
 
 def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
-                out: Optional[torch.Tensor] = None, force_splits: int = 0, weights_const: bool = False) -> torch.Tensor:
+                out: Optional[torch.Tensor] = None, force_splits: int = 0, weights_const: bool = False,
+                row_scale=None, eps: float = 0.0, ssq_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``a @ w.T + residual`` for M <= 64 rows through the split-K weight-streaming kernel; ``w`` is a [N,K] bf16
     tensor or a :class:`TiledWeight`.  ``weights_const``: promise that ``w`` is not written by the kernel launched just
-    before on this stream -> programmatic dependent launch with early weight prefetch (the decode step)."""
+    before on this stream -> programmatic dependent launch with early weight prefetch (the decode step).
+    ``row_scale`` = (fp32 tensor, parts): parts == 0 -> the tensor is rstd [M]; parts > 0 -> [parts, 64] partial sums of squares
+    of ``a``'s rows (the ``ssq_out`` of the GEMM that produced ``a``), rstd = rsqrt(sum / K + eps).  ``ssq_out`` [ceil(N/128), 64]
+    fp32 receives this GEMM's per-tile sums of squares of the bf16 output rows."""
     _chk(a, torch.bfloat16, "gemm_skinny.a")
     M, K = a.shape
     if isinstance(w, TiledWeight):
@@ -88,9 +102,22 @@ def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
     ws = _skinny_workspace(a.device)
     if gemm_timer is not None:
         gemm_timer.before(M, N, K)
-    _l.call("esb_gemm_skinny_bf16", a.data_ptr(), a.stride(0), wp, ldw, out.data_ptr(), out.stride(0),
-            M, N, K, _p(residual), 0 if residual is None else residual.stride(0), ws.data_ptr(), ws.numel(), force_splits,
-            tiled | (2 if (weights_const and pdl_enabled) else 0), _stream())
+    flags = tiled | (2 if (weights_const and pdl_enabled) else 0)
+    if row_scale is None and ssq_out is None:
+        _l.call("esb_gemm_skinny_bf16", a.data_ptr(), a.stride(0), wp, ldw, out.data_ptr(), out.stride(0),
+                M, N, K, _p(residual), 0 if residual is None else residual.stride(0), ws.data_ptr(), ws.numel(), force_splits,
+                flags, _stream())
+    else:
+        sc, parts = (None, 0) if row_scale is None else row_scale
+        if sc is not None:
+            _chk(sc, torch.float32, "gemm_skinny.row_scale")
+            assert sc.is_contiguous() and sc.numel() >= (M if parts == 0 else parts * 64)
+        if ssq_out is not None:
+            _chk(ssq_out, torch.float32, "gemm_skinny.ssq_out")
+            assert ssq_out.is_contiguous() and ssq_out.numel() >= (N + 127) // 128 * 64
+        _l.call("esb_gemm_skinny_normed_bf16", a.data_ptr(), a.stride(0), wp, ldw, out.data_ptr(), out.stride(0),
+                M, N, K, _p(residual), 0 if residual is None else residual.stride(0), ws.data_ptr(), ws.numel(), force_splits,
+                flags, _p(sc), int(parts), float(eps), _p(ssq_out), _stream())
     if gemm_timer is not None:
         gemm_timer.after()
     return out

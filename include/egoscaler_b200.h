@@ -80,6 +80,19 @@ int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw,
                          int w_tiled, void* stream);
 int64_t esb_retiled_weight_elems(int N, int K);
 int esb_retile_weight_bf16(const void* W, int64_t ldw, int N, int K, void* out, void* stream);
+/* The decode step with LlamaRMSNorm (HF modeling_llama.py LlamaRMSNorm, called at the three norm sites of
+ * pointllm.py:173-178 / :227) folded around the Linear that consumes it:  Linear(norm(x)) = rstd(x) * (x . (W*g)^T).
+ *   esb_retile_weight_scaled_bf16: like esb_retile_weight_bf16 with column k multiplied by the norm weight g[k] (bf16).
+ *   esb_gemm_skinny_normed_bf16:   like esb_gemm_skinny_bf16, plus
+ *     scale_src != NULL: accumulator row m is multiplied by rstd[m] before the residual is added;  scale_parts == 0:
+ *       scale_src[m] is rstd itself (esb_rmsnorm_fwd's rstd output); scale_parts > 0: scale_src is [scale_parts][64] partial
+ *       sums of squares of x (as left by ssq_out of the GEMM that produced x) and rstd = rsqrt(sum / K + eps);
+ *     ssq_out != NULL: [ceil(N/128)][64] fp32, entry [t][m] = sum over the 128 output columns of tile t of bf16(C[m,:])^2,
+ *       summed in a fixed order (deterministic) - the next norm's statistics without a separate pass over C. */
+int esb_retile_weight_scaled_bf16(const void* W, int64_t ldw, int N, int K, const void* col_scale, void* out, void* stream);
+int esb_gemm_skinny_normed_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
+                                const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,
+                                int w_tiled, const float* scale_src, int scale_parts, float eps, float* ssq_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------ trajectory tokens
  * utils/utils.py:13-16 discretize_action: out[i] = np.digitize(x[i], np.linspace(-1,1,num_bins)) - 1 + id_offset

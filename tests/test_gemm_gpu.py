@@ -97,3 +97,50 @@ def test_gemm_dispatches_skinny_for_decode_rows():
     finally:
         ops.skinny_enabled = True
     torch.testing.assert_close(y1.float(), y0.float(), atol=2e-2, rtol=1.6e-2)
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(32, 4096, 4096, 0), (32, 1000, 512, 1), (50, 640, 1024, 4), (7, 4096, 11008, 0),
+                                          (32, 12288, 4096, 0)])
+def test_skinny_folded_rmsnorm(M, N, K, splits):
+    """RMSNorm folded around the decode-step GEMM (esb_gemm_skinny_normed_bf16 + esb_retile_weight_scaled_bf16):
+    (a) rstd * (x . (W*g)^T) == Linear(LlamaRMSNorm(x)) within bf16 rounding; (b) ssq_out of a producing GEMM (with residual) is
+    the exact per-row sum of squares of its bf16 output, deterministic; (c) a consumer fed with those partials == the
+    consumer fed with rstd from the stand-alone rmsnorm kernel."""
+    g = torch.Generator().manual_seed(M * 7 + N + K)
+    eps = 1e-6
+    x = (torch.randn(M, K, generator=g) * 3.0).bfloat16().cuda()
+    gam = (1.0 + 0.2 * torch.randn(K, generator=g)).bfloat16().cuda()
+    w = (torch.randn(N, K, generator=g) * 0.03).bfloat16().cuda()
+    xf = x.float()
+    rstd_ref = torch.rsqrt((xf * xf).mean(-1, keepdim=True) + eps)
+    ref = ((xf * rstd_ref).bfloat16().float() * gam.float()).bfloat16().float() @ w.float().T      # HF order of roundings
+    tw = ops.retile_weight(w, gam)
+    _, rstd = ops.rmsnorm(x, gam, eps, want_rstd=True)
+    got = ops.gemm_skinny(x, tw, row_scale=(rstd, 0), eps=eps, force_splits=splits)
+    err = float((got.float() - ref).norm() / ref.norm())
+    assert err < 8e-3, err
+    # (b) producer: out = a @ w2^T + res, statistics of out
+    a = (torch.randn(M, N, generator=g)).bfloat16().cuda()
+    w2 = (torch.randn(K, N, generator=g) * 0.05).bfloat16().cuda()
+    res = torch.randn(M, K, generator=g).bfloat16().cuda()
+    nt = (K + 127) // 128
+    ssq = torch.full((nt, 64), -1.0, device="cuda")
+    out = ops.gemm_skinny(a, w2, residual=res, ssq_out=ssq, force_splits=splits)
+    plain = ops.gemm_skinny(a, w2, residual=res, force_splits=splits)
+    assert torch.equal(out, plain)
+    of = out.float()
+    pad = torch.zeros(M, nt * 128, device="cuda")
+    pad[:, :K] = of * of
+    tile_ref = pad.view(M, nt, 128).sum(-1).T                                  # [nt, M]
+    torch.testing.assert_close(ssq[:, :M], tile_ref, rtol=2e-6, atol=1e-6)
+    ssq2 = torch.empty_like(ssq)
+    ops.gemm_skinny(a, w2, residual=res, ssq_out=ssq2, force_splits=splits)
+    assert torch.equal(ssq[:, :M], ssq2[:, :M])
+    # (c) consumer from the partial sums == consumer from the rmsnorm kernel's rstd (same rsqrtf, sums differ by an ulp)
+    w3 = (torch.randn(256, K, generator=g) * 0.03).bfloat16().cuda()
+    tw3 = ops.retile_weight(w3, gam)
+    c1 = ops.gemm_skinny(out, tw3, row_scale=(ssq, nt), eps=eps)
+    _, r2 = ops.rmsnorm(out, gam, eps, want_rstd=True)
+    c2 = ops.gemm_skinny(out, tw3, row_scale=(r2, 0), eps=eps)
+    assert float((c1.float() - c2.float()).abs().max()) <= 2e-2 * float(c2.float().abs().max())
+    assert float((c1.float() - c2.float()).norm() / c2.float().norm()) < 2e-3

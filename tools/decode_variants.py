@@ -32,21 +32,38 @@ def run(t_new, graph):
     return e0.elapsed_time(e1)
 
 
+VARIANTS = {"fold_norm": (True, True, True), "plain": (True, True, False), "no_pdl": (True, False, False), "general_gemm": (False, False, False)}
+best = {k: (1e9, 1e9) for k in VARIANTS}
 seqs = {}
-for skinny, pdl, chain in ((True, True, True), (True, True, False), (True, True, True), (True, True, False), (True, False, False),
-                           (False, False, False)):
+
+
+def select(skinny, pdl, fold):
     ops.SKINNY_MAX_M = 64 if skinny else 0
     ops.skinny_enabled = skinny
     ops.pdl_enabled = pdl
-    ops.pdl_chain_enabled = chain
-    print("pdl", pdl, "chain", chain, end=" ")
-    for graph in (True,):
-        run(4, graph)
-        t1 = min(run(1, graph) for _ in range(2))
-        tT = min(run(T, graph) for _ in range(2))
-        print(f"skinny={skinny} graph={graph}: prefill+1 {t1:.1f} ms, {T} tokens {tT:.1f} ms -> {(tT - t1) / (T - 1):.3f} ms/token", flush=True)
+    ops.fold_norm_enabled = fold
+
+
+for rnd in range(4):                                     # round-robin so that a throttling episode hits every variant alike
+    for name, v in VARIANTS.items():
+        if rnd >= 2 and name in ("no_pdl", "general_gemm"):
+            continue
+        select(*v)
+        run(4, True)
+        t1 = run(1, True)
+        tT = run(T, True)
+        best[name] = (min(best[name][0], t1), min(best[name][1], tT))
+        print(f"round {rnd} {name}: prefill+1 {t1:.1f} ms, {T} tokens {tT:.1f} ms -> {(tT - t1) / (T - 1):.3f} ms/token", flush=True)
+for name, (t1, tT) in best.items():
+    print(f"best {name}: {(tT - t1) / (T - 1):.3f} ms/token")
+for name, v in VARIANTS.items():
+    select(*v)
     out = model.generate(max_length=12, use_cuda_graph=True, **args)
-    seqs[(skinny, pdl, chain)] = out.sequences.cpu()
-ref = seqs[(True, False, False)]
+    seqs[name] = (out.sequences.cpu(), torch.stack(out.scores).float().cpu())
+ref = seqs["no_pdl"]
 for k, v in seqs.items():
-    print(k, "ids equal to the no-PDL run:", bool(torch.equal(v, ref)))
+    sc, rc = v[1].clone(), ref[1].clone()
+    sc[~torch.isfinite(sc)] = 0
+    rc[~torch.isfinite(rc)] = 0
+    rel = [float((sc[t] - rc[t]).norm() / rc[t].norm()) for t in range(sc.shape[0])]
+    print(k, "ids equal to the no_pdl run:", bool(torch.equal(v[0], ref[0])), "scores rel-L2 per step:", [round(x, 4) for x in rel[:4]])
