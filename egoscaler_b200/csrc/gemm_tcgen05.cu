@@ -12,6 +12,7 @@
 //   warps 4..7    : epilogue       (tcgen05.ld 32x32b -> bias / activation / residual -> bf16|fp32 global)
 // Pipelines: smem ring full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue), static tile scheduler.
 // Ragged M/N/K edges rely on TMA zero fill for loads and on masked stores in the epilogue.
+#include <cstdlib>
 #include "common.cuh"
 #include "esb_internal.h"
 
@@ -37,7 +38,35 @@ struct GemmParams {
     int accumulate;           // fp32 out only: C += result
     float alpha;              // scales the product before bias
     int tiles_m, tiles_n;
+    // Tile walk + L2 policy, chosen per launch on the host (launch_gemm) to keep DRAM traffic near A + B + C:
+    //   raster_mode 0: M-groups of `group` row tiles; inside a group tiles are walked M-fastest across all of N, so the group's
+    //                  A panels (group * BM * K * 2 bytes, sized to fit L2) are re-read from L2 by every wave while each
+    //                  B panel is used by one wave only;  A is loaded evict_last, B evict_normal.
+    //   raster_mode 1: the mirror image - N-groups of `group` column panels walked N-fastest across all of M; the group's B
+    //                  panels persist in L2 (evict_last) and A streams through.
+    // C larger than L2 is written with streaming stores so that the output does not push the persisting operand out.
+    int raster_mode, group;
+    uint64_t a_policy, b_policy;
+    int c_stream;
 };
+
+ESB_DEVICE void tile_coords(const GemmParams& p, int t, int& tm, int& tn) {
+    if (p.raster_mode == 0) {
+        const int per_group = p.group * p.tiles_n;
+        const int g = t / per_group, r = t - g * per_group;
+        const int base = g * p.group;
+        const int gm = min(p.group, p.tiles_m - base);
+        tn = r / gm;
+        tm = base + (r - tn * gm);
+    } else {
+        const int per_group = p.group * p.tiles_m;
+        const int g = t / per_group, r = t - g * per_group;
+        const int base = g * p.group;
+        const int gn = min(p.group, p.tiles_n - base);
+        tm = r / gn;
+        tn = base + (r - tm * gn);
+    }
+}
 
 template <int BN>
 struct GemmSmem {
@@ -99,15 +128,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t % p.tiles_m) * BM;
-                const int n0 = (t / p.tiles_m) * BN;
+                int tm, tn;
+                tile_coords(p, t, tm, tn);
+                const int m0 = tm * BM, n0 = tn * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     uint8_t* sa = tiles + stage * S::STAGE_BYTES;
                     uint8_t* sb = sa + S::A_BYTES;
                     mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
-                    tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m0);
-                    tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n0);
+                    tma_load_2d_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
+                    tma_load_2d_hint(sb, &tma_b, &full_bar[stage], kb * BK, n0, p.b_policy);
                     if (++stage == S::STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -154,8 +184,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         const bool vec_ok_f32 = (p.out_fp32) && ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
         const bool res_vec_ok = p.res && ((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.res) & 15) == 0);
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const int m0 = (t % p.tiles_m) * BM;
-            const int n0 = (t / p.tiles_m) * BN;
+            int tm, tn;
+            tile_coords(p, t, tm, tn);
+            const int m0 = tm * BM, n0 = tn * BN;
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const int row = m0 + q * 32 + lane;
@@ -217,7 +248,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                                 u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
                                 u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
                                 u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-                                reinterpret_cast<uint4*>(cp)[g] = u;
+                                if (p.c_stream) __stcs(reinterpret_cast<uint4*>(cp) + g, u);
+                                else reinterpret_cast<uint4*>(cp)[g] = u;
                             }
                         } else {
 #pragma unroll
@@ -282,6 +314,7 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, long long rows, long lon
     cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 2};
     cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
     cuuint32_t estr[2] = {1, 1};
+    // L2 promotion 256 B vs 128 B vs none: no difference in DRAM bytes or time (ncu, profiles/r01_gemm_traffic_raster.txt)
     CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -330,6 +363,30 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     p.tiles_m = (p.M + BM - 1) / BM;
     p.tiles_n = (p.N + BN - 1) / BN;
     const int tiles = p.tiles_m * p.tiles_n;
+    // ---- tile walk: modelled DRAM bytes = persisting operand once + streamed operand once per group + C
+    static const int hints = [] { const char* e = getenv("ESB_GEMM_L2_HINTS"); return e ? atoi(e) : 7; }();
+    const double budget = 48.0 * (1 << 20);                   // bytes of one operand group kept L2-resident (126 MB L2, two halves)
+    const double a_panel = 2.0 * BM * p.K, b_panel = 2.0 * BN * p.K;
+    const double a_bytes = a_panel * p.tiles_m, b_bytes = b_panel * p.tiles_n;
+    const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2);
+    int gm = static_cast<int>(budget / a_panel);
+    gm = gm < 1 ? 1 : (gm > p.tiles_m ? p.tiles_m : gm);
+    const int groups_m = (p.tiles_m + gm - 1) / gm;
+    gm = (p.tiles_m + groups_m - 1) / groups_m;               // even groups
+    int gn = static_cast<int>(budget / b_panel);
+    gn = gn < 1 ? 1 : (gn > p.tiles_n ? p.tiles_n : gn);
+    const int groups_n = (p.tiles_n + gn - 1) / gn;
+    gn = (p.tiles_n + groups_n - 1) / groups_n;
+    const double cost_m = a_bytes + b_bytes * groups_m, cost_n = b_bytes + a_bytes * groups_n;
+    p.raster_mode = 0; p.group = p.tiles_m;                   // ESB_GEMM_L2_HINTS bit 2 off: the plain M-fastest walk
+    if (hints & 4) {
+        if (cost_m <= cost_n) { p.raster_mode = 0; p.group = gm; }
+        else { p.raster_mode = 1; p.group = gn; }
+    }
+    const bool persist_fits = (p.raster_mode == 0 ? a_panel * p.group : b_panel * p.group) <= 64.0 * (1 << 20);
+    p.a_policy = ((hints & 1) && p.raster_mode == 0 && persist_fits) ? kEvictLast : kEvictNormal;
+    p.b_policy = ((hints & 1) && p.raster_mode == 1 && persist_fits) ? kEvictLast : kEvictNormal;
+    p.c_stream = ((hints & 2) && !p.out_fp32 && c_bytes >= 96.0 * (1 << 20)) ? 1 : 0;
     const int grid = tiles < sms ? tiles : sms;
     gemm_bf16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
     return check_launch("gemm_bf16_tcgen05");
@@ -376,6 +433,7 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
     p.res = reinterpret_cast<const __nv_bfloat16*>(residual); p.ldr = ldr;
     p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
     p.tiles_m = p.tiles_n = 0;
+    p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;      // set by launch_gemm
     switch (bn) {
         case 256: return launch_gemm<256>(ta, tb, p, stream, sms);
         case 128: return launch_gemm<128>(ta, tb, p, stream, sms);

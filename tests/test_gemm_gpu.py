@@ -144,3 +144,19 @@ def test_skinny_folded_rmsnorm(M, N, K, splits):
     c2 = ops.gemm_skinny(out, tw3, row_scale=(r2, 0), eps=eps)
     assert float((c1.float() - c2.float()).abs().max()) <= 2e-2 * float(c2.float().abs().max())
     assert float((c1.float() - c2.float()).norm() / c2.float().norm()) < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 1024, 32768), (4000, 1000, 32768), (5568, 4096, 11008), (5568, 4096, 22016),
+                                   (5568, 4096, 12288)])
+def test_gemm_grouped_tile_walk(M, N, K):
+    """Shapes whose operand panels exceed the L2 budget, so launch_gemm walks the tiles in several M-groups (first shape) or
+    N-groups (the others - the down-proj forward and the two large data-gradient GEMMs of the 7B trunk among them): every
+    output tile must still be produced exactly once."""
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).bfloat16()
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a, w, out=out)
+    ref = _ref(a, w)
+    assert bool(torch.isfinite(out).all())
+    torch.testing.assert_close(out.float(), ref, atol=2e-2, rtol=1.6e-2)
