@@ -365,7 +365,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     const int tiles = p.tiles_m * p.tiles_n;
     // ---- tile walk: modelled DRAM bytes = persisting operand once + streamed operand once per group + C
     static const int hints = [] { const char* e = getenv("ESB_GEMM_L2_HINTS"); return e ? atoi(e) : 7; }();
-    const double budget = 48.0 * (1 << 20);                   // bytes of one operand group kept L2-resident (126 MB L2, two halves)
+    static const double budget_mb = [] { const char* e = getenv("ESB_GEMM_L2_BUDGET_MB"); return e ? atof(e) : 48.0; }();
+    const double budget = budget_mb * (1 << 20);              // bytes of one operand group kept L2-resident (126 MB L2, two halves)
     const double a_panel = 2.0 * BM * p.K, b_panel = 2.0 * BN * p.K;
     const double a_bytes = a_panel * p.tiles_m, b_bytes = b_panel * p.tiles_n;
     const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2);
