@@ -58,7 +58,8 @@ struct SkinnySmem {
 
 ESB_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BT, int SK_STAGES>
+// NORMED = false compiles the scale / sum-of-squares epilogue out (the plain token step keeps its 114-register kernel).
+template <int BT, int SK_STAGES, bool NORMED>
 __global__ void __launch_bounds__(SK_THREADS, SK_STAGES <= 4 ? 2 : 1)
 gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x,
                            const SkinnyParams p) {
@@ -186,7 +187,8 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
         const int nl = q * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
-        const bool scaled = p.scale_src != nullptr;
+        const bool scaled = NORMED && p.scale_src != nullptr;
+        float* const ssq_out = NORMED ? p.ssq_out : nullptr;
         if (scaled) {
             if (nl < 64) {
                 float sc = 1.0f;
@@ -230,7 +232,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                             const float of = __bfloat162float(ob);
                             sq = of * of;
                         }
-                        if (p.ssq_out) {
+                        if (ssq_out) {
                             sq = warp_sum(sq);
                             if (lane == 0) s_red[q][m] = sq;
                         }
@@ -245,9 +247,9 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
             mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1u;
-            if (p.splits == 1 && p.ssq_out) {
+            if (p.splits == 1 && ssq_out) {
                 epi_bar_sync();
-                if (nl < p.M) p.ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
+                if (nl < p.M) ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
                 epi_bar_sync();
             }
             if (p.splits > 1) {
@@ -262,7 +264,7 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                 epi_bar_sync();
                 if (*last_flag) {
                     __threadfence();
-                    {
+                    if (NORMED || n_ok) {
                         // fixed summation order s = 0..S-1 per element; 16 tokens x 4 slices of loads in flight
                         const float* base = p.partial + static_cast<size_t>(tile) * p.splits * (BT * SK_ROWS) + nl;
 #pragma unroll 1
@@ -306,16 +308,16 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
                                     const float of = __bfloat162float(ob);
                                     sq = of * of;
                                 }
-                                if (p.ssq_out) {
+                                if (ssq_out) {
                                     sq = warp_sum(sq);
                                     if (lane == 0 && m < 64) s_red[q][m] = sq;
                                 }
                             }
                         }
                     }
-                    if (p.ssq_out) {
+                    if (ssq_out) {
                         epi_bar_sync();
-                        if (nl < p.M) p.ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
+                        if (nl < p.M) ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
                         epi_bar_sync();
                     }
                 }
@@ -334,14 +336,16 @@ gemm_skinny_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_w, const __gr
 template <int BT, int SK_STAGES>
 int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyParams& p, int grid, bool pdl, cudaStream_t stream) {
     using S = SkinnySmem<BT, SK_STAGES>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_skinny_tcgen05_kernel<BT, SK_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+    const bool normed = p.scale_src != nullptr || p.ssq_out != nullptr;
+    auto kernel = normed ? gemm_skinny_tcgen05_kernel<BT, SK_STAGES, true> : gemm_skinny_tcgen05_kernel<BT, SK_STAGES, false>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[normed]) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
         if (e != cudaSuccess) {
             set_last_error("cudaFuncSetAttribute(gemm_skinny<%d>): %s", BT, cudaGetErrorString(e));
             return ESB_ERR_CUDA;
         }
-        attr_set = true;
+        attr_set[normed] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
@@ -353,7 +357,7 @@ int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyPara
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_skinny_tcgen05_kernel<BT, SK_STAGES>, tw, tx, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, tw, tx, p);
     if (e != cudaSuccess) {
         set_last_error("gemm_skinny launch: %s", cudaGetErrorString(e));
         return ESB_ERR_CUDA;
