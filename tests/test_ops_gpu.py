@@ -173,6 +173,17 @@ def test_cross_entropy_and_argmax():
     t = torch.zeros(2, 64, device="cuda", dtype=torch.bfloat16)
     t[0, 5] = t[0, 9] = 3.0
     assert ops.argmax_rows(t, 64).tolist() == [5, 0]
+    # rows that are not 16-byte aligned (odd leading dimension / offset view) take the scalar path; ragged tails; ties across vectors
+    for V2, ld2, off in ((1001, 1003, 1), (32262, 32264, 0), (77, 80, 3), (8, 8, 0), (4099, 4104, 0)):
+        b2 = rnd(9, ld2 + 8, seed=V2, scale=2.0)
+        lg = b2[:, off:off + V2]
+        lg[3, V2 - 1] = 50.0                                  # maximum in the ragged tail
+        lg[4, 2] = lg[4, V2 // 2] = 60.0                      # tie: first index wins
+        sc2 = torch.empty(9, V2, device="cuda")
+        got = ops.argmax_rows(lg, V2, scores=sc2)
+        assert torch.equal(got, lg.float().argmax(-1)), (V2, ld2, off)
+        assert int(got[3]) == V2 - 1 and int(got[4]) == 2
+        assert torch.equal(sc2, lg.float())
 
 
 def test_adamw_matches_torch():
