@@ -47,31 +47,49 @@ ESB_DEVICE void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, u
                  : "memory");
 }
 
-// D = rowsum(dO o O), packed with lse * log2(e); one warp per (b, i, h), i runs over the padded length Lqp.
+// D = rowsum(dO o O), packed with lse * log2(e).  One warp per (b, h, 8 consecutive rows of the padded length Lqp): a 16-lane half
+// covers one 256-byte row with 16-byte loads, and all 8 loads of a thread are issued before the first use (HBM-bound kernel).
 __global__ void __launch_bounds__(128) attn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ o, long long o_bs, long long o_rs,
                                                              const __nv_bfloat16* __restrict__ dout, long long do_bs, long long do_rs,
                                                              const float* __restrict__ lse, float2* __restrict__ stats, int B, int H,
                                                              int Lq, int Lqp) {
     const long long gw = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
-    const long long total = static_cast<long long>(B) * Lqp * H;
+    const int groups = Lqp >> 3;
+    const long long total = static_cast<long long>(B) * H * groups;
     if (gw >= total) return;
-    const int h = static_cast<int>(gw % H);
-    const long long t = gw / H;
-    const int i = static_cast<int>(t % Lqp);
-    const int b = static_cast<int>(t / Lqp);
-    float2 out = make_float2(INFINITY, 0.0f);
-    if (i < Lq) {
-        const __nv_bfloat16* op = o + b * o_bs + static_cast<long long>(i) * o_rs + static_cast<long long>(h) * BT_HD;
-        const __nv_bfloat16* dp = dout + b * do_bs + static_cast<long long>(i) * do_rs + static_cast<long long>(h) * BT_HD;
-        const uint2 a = *reinterpret_cast<const uint2*>(op + lane * 4);
-        const uint2 d = *reinterpret_cast<const uint2*>(dp + lane * 4);
-        const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y);
-        const float acc = warp_sum(a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y);
-        const float l = lse[(static_cast<long long>(b) * H + h) * Lq + i];
-        out = make_float2(l == -INFINITY ? INFINITY : l * LOG2E, acc);
+    const int g8 = static_cast<int>(gw % groups);
+    const long long t = gw / groups;
+    const int h = static_cast<int>(t % H);
+    const int b = static_cast<int>(t / H);
+    const int half = lane >> 4, l16 = lane & 15;
+    uint4 av[4], dv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int i = g8 * 8 + 2 * k + half;
+        av[k] = dv[k] = make_uint4(0u, 0u, 0u, 0u);
+        if (i < Lq) {
+            av[k] = *reinterpret_cast<const uint4*>(o + b * o_bs + static_cast<long long>(i) * o_rs + static_cast<long long>(h) * BT_HD + l16 * 8);
+            dv[k] = *reinterpret_cast<const uint4*>(dout + b * do_bs + static_cast<long long>(i) * do_rs + static_cast<long long>(h) * BT_HD + l16 * 8);
+        }
     }
-    if (lane == 0) stats[(static_cast<long long>(b) * H + h) * Lqp + i] = out;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int i = g8 * 8 + 2 * k + half;
+        const float2 a0 = unpack_bf16x2(av[k].x), a1 = unpack_bf16x2(av[k].y), a2 = unpack_bf16x2(av[k].z), a3 = unpack_bf16x2(av[k].w);
+        const float2 d0 = unpack_bf16x2(dv[k].x), d1 = unpack_bf16x2(dv[k].y), d2 = unpack_bf16x2(dv[k].z), d3 = unpack_bf16x2(dv[k].w);
+        float acc = a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
+#pragma unroll
+        for (int sft = 8; sft > 0; sft >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, sft);
+        if (l16 == 0) {
+            float2 out = make_float2(INFINITY, 0.0f);
+            if (i < Lq) {
+                const float l = lse[(static_cast<long long>(b) * H + h) * Lq + i];
+                out = make_float2(l == -INFINITY ? INFINITY : l * LOG2E, acc);
+            }
+            stats[(static_cast<long long>(b) * H + h) * Lqp + i] = out;
+        }
+    }
 }
 
 // Write 32 consecutive bf16 (16 packed words) of row r, columns [32*half, 32*half+32), into a [128 x 64] K-major
@@ -514,10 +532,11 @@ int attn_bwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k,
                    long long do_rs, const float* lse, float* stats_ws, void* dq, long long dq_bs, long long dq_rs, void* dk,
                    long long dk_bs, long long dk_rs, void* dv, long long dv_bs, long long dv_rs, const uint8_t* kmask,
                    long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s) {
-    if ((dq_rs & 7) || (dk_rs & 7) || (dv_rs & 7) || (dq_bs & 7) || (dk_bs & 7) || (dv_bs & 7) || (o_rs & 3) || (do_rs & 7) ||
+    if ((dq_rs & 7) || (dk_rs & 7) || (dv_rs & 7) || (dq_bs & 7) || (dk_bs & 7) || (dv_bs & 7) || (o_rs & 7) || (o_bs & 7) ||
+        (do_rs & 7) || (do_bs & 7) || (reinterpret_cast<uintptr_t>(o) & 15) || (reinterpret_cast<uintptr_t>(dout) & 15) ||
         (reinterpret_cast<uintptr_t>(dq) & 15) || (reinterpret_cast<uintptr_t>(dk) & 15) || (reinterpret_cast<uintptr_t>(dv) & 15) ||
         (reinterpret_cast<uintptr_t>(stats_ws) & 15)) {
-        set_last_error("attn_bwd: gradients / workspace must keep 16-byte alignment");
+        set_last_error("attn_bwd: o / dout / gradients / workspace must keep 16-byte alignment");
         return ESB_ERR_INVALID_ARG;
     }
     static bool attr_set = false;
@@ -544,7 +563,7 @@ int attn_bwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k,
     if ((rc = make_tma_3d_bf16(&tv128, v, cols, Lk, B, v_rs, v_bs, 64, BT_TILE))) return rc;
 
     float2* stats = reinterpret_cast<float2*>(stats_ws);
-    const long long warps = static_cast<long long>(B) * Lqp * H;
+    const long long warps = static_cast<long long>(B) * H * (Lqp / 8);          // Lqp is a multiple of 128
     attn_bwd_stats_kernel<<<static_cast<unsigned>((warps + 3) / 4), 128, 0, s>>>(
         static_cast<const __nv_bfloat16*>(o), o_bs, o_rs, static_cast<const __nv_bfloat16*>(dout), do_bs, do_rs, lse, stats, B, H, Lq, Lqp);
 
