@@ -344,7 +344,7 @@ def decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks):
 
     run(4)                                                                  # warm-up (allocator, lazy operands)
     ms1, _ = run(1)
-    ms_full = min(run(T)[0] for _ in range(3))
+    ms_full = min(run(T)[0] for _ in range(5))               # ~1 s each; the pool shows multi-second slow episodes
     d, f, n, V = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers, cfg.vocab_size
     per_tok_ms = (ms_full - ms1) / max(1, T - 1)
     ctx_mean = P + T / 2.0
