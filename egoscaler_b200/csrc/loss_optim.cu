@@ -175,18 +175,43 @@ int greedy_update(const long long* next, long long* tokens_out, int* unfinished,
 }
 
 // AdamW (decoupled weight decay), fp32 master p/m/v, grad fp32 * grad_scale, writes bf16 copy (optional).
+struct AdamWConst { float lr, beta1, beta2, eps, wd, bc1, bc2_sqrt, grad_scale; };
+
+ESB_DEVICE void adamw_one(float& p, float g, float& m, float& v, const AdamWConst& c) {
+    // explicit roundings: the 16-byte and the scalar loop must agree bit for bit (no compiler-chosen FMA contraction)
+    const float gi = __fmul_rn(g, c.grad_scale);
+    const float mi = __fmaf_rn(c.beta1, m, __fmul_rn(1.0f - c.beta1, gi));
+    const float vi = __fmaf_rn(c.beta2, v, __fmul_rn(__fmul_rn(1.0f - c.beta2, gi), gi));
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), c.bc2_sqrt), c.eps);
+    p = __fmaf_rn(-(c.lr / c.bc1), __fdiv_rn(mi, denom), __fmul_rn(p, 1.0f - c.lr * c.wd));
+    m = mi; v = vi;
+}
+
+// 30 B per parameter (p, m, v read + written, g read, bf16 copy written).  vec != 0: all arrays 16-byte aligned (bf16 copy 8-byte),
+// four parameters per thread with 16-byte accesses; the n % 4 tail and unaligned tensors take the scalar loop.
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                     float* __restrict__ v, __nv_bfloat16* __restrict__ p_bf16, long long n,
-                                                    float lr, float beta1, float beta2, float eps, float wd, float bc1, float bc2_sqrt,
-                                                    float grad_scale) {
+                                                    const AdamWConst c, int vec) {
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float gi = g[i] * grad_scale;
-        float pi = p[i] * (1.0f - lr * wd);
-        const float mi = beta1 * m[i] + (1.0f - beta1) * gi;
-        const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
-        const float denom = sqrtf(vi) / bc2_sqrt + eps;
-        pi -= (lr / bc1) * (mi / denom);
+    const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const long long n4 = vec ? (n >> 2) : 0;
+    for (long long i = tid; i < n4; i += stride) {
+        float4 pv = reinterpret_cast<float4*>(p)[i];
+        const float4 gv = __ldcs(reinterpret_cast<const float4*>(g) + i);
+        float4 mv = reinterpret_cast<float4*>(m)[i];
+        float4 vv = reinterpret_cast<float4*>(v)[i];
+        adamw_one(pv.x, gv.x, mv.x, vv.x, c);
+        adamw_one(pv.y, gv.y, mv.y, vv.y, c);
+        adamw_one(pv.z, gv.z, mv.z, vv.z, c);
+        adamw_one(pv.w, gv.w, mv.w, vv.w, c);
+        reinterpret_cast<float4*>(p)[i] = pv;
+        reinterpret_cast<float4*>(m)[i] = mv;
+        reinterpret_cast<float4*>(v)[i] = vv;
+        if (p_bf16) reinterpret_cast<uint2*>(p_bf16)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+    }
+    for (long long i = (n4 << 2) + tid; i < n; i += stride) {
+        float pi = p[i], mi = m[i], vi = v[i];
+        adamw_one(pi, g[i], mi, vi, c);
         p[i] = pi; m[i] = mi; v[i] = vi;
         if (p_bf16) p_bf16[i] = __float2bfloat16_rn(pi);
     }
@@ -197,9 +222,12 @@ int adamw(float* p, const float* g, float* m, float* v, void* p_bf16, long long 
     if (step < 1) { set_last_error("adamw: step must be >= 1"); return ESB_ERR_INVALID_ARG; }
     const float bc1 = 1.0f - powf(beta1, static_cast<float>(step));
     const float bc2s = sqrtf(1.0f - powf(beta2, static_cast<float>(step)));
-    const long long want = (n + 255) / 256, cap = static_cast<long long>(device_sm_count()) * 16;
-    adamw_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, s>>>(p, g, m, v, static_cast<__nv_bfloat16*>(p_bf16), n, lr, beta1,
-                                                                           beta2, eps, wd, bc1, bc2s, grad_scale);
+    const auto al = [](const void* q, uintptr_t a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; };
+    const int vec = al(p, 16) && al(g, 16) && al(m, 16) && al(v, 16) && (!p_bf16 || al(p_bf16, 8)) ? 1 : 0;
+    const long long items = vec ? (n + 3) / 4 : n;
+    const long long want = (items + 255) / 256, cap = static_cast<long long>(device_sm_count()) * 32;
+    const AdamWConst c{lr, beta1, beta2, eps, wd, bc1, bc2s, grad_scale};
+    adamw_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, s>>>(p, g, m, v, static_cast<__nv_bfloat16*>(p_bf16), n, c, vec);
     return check_launch("adamw");
 }
 

@@ -199,6 +199,16 @@ def test_adamw_matches_torch():
         ops.adamw_(p, g * step * 2, m, v, pb, 2e-3, 0.9, 0.999, 1e-8, 0.01, step, grad_scale=0.5)
     torch.testing.assert_close(p, ref.detach(), atol=1e-6, rtol=1e-5)
     assert torch.equal(pb, p.bfloat16())
+    # unaligned views take the scalar loop and must give bit-identical results to the 16-byte path
+    big = [torch.zeros(n + 1, device="cuda") for _ in range(3)]
+    pu, mu, vu = (t[1:] for t in big)
+    pu.copy_(p0)
+    pbu = torch.empty(n + 1, device="cuda", dtype=torch.bfloat16)[1:]
+    pa, ma, va = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    for step in range(1, 4):
+        ops.adamw_(pu, g * step * 2, mu, vu, pbu, 2e-3, 0.9, 0.999, 1e-8, 0.01, step, grad_scale=0.5)
+        ops.adamw_(pa, g * step * 2, ma, va, pb, 2e-3, 0.9, 0.999, 1e-8, 0.01, step, grad_scale=0.5)
+    assert torch.equal(pu, pa) and torch.equal(mu, ma) and torch.equal(vu, va) and torch.equal(pbu, pb)
 
 
 def test_embed_splice_fwd_bwd_and_layout():
