@@ -195,7 +195,7 @@ class _Blocks(nn.Module):
 
     def __init__(self, dim: int, depth: int, heads: int, drop_path_rate: float = 0.0):
         super().__init__()
-        dpr = [v.item() for v in torch.linspace(0, drop_path_rate, depth)]            # point_encoder.py:134
+        dpr = [v.item() for v in torch.linspace(0, drop_path_rate, depth, device="cpu")]            # point_encoder.py:134
         self.blocks = nn.ModuleList([_Block(dim, heads, dpr[i]) for i in range(depth)])
 
     def forward(self, x, pos, drop_u=None):
