@@ -72,6 +72,12 @@ class TrajVLMConfig:
         return TrajVLMConfig(hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=4)
 
     @staticmethod
+    def tiny_hd128() -> "TrajVLMConfig":
+        """Tiny trunk with the full-size head width (2 heads x 128): the parity-test size that runs the same head_dim-128
+        tcgen05 attention / decode-attention kernels as the full-size config."""
+        return TrajVLMConfig(hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=2)
+
+    @staticmethod
     def tiny_base() -> "TrajVLMConfig":
         """Tiny LLM + the base PointBERT encoder (SURVEY 8d config E at parity-test size)."""
         return TrajVLMConfig(hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=4,

@@ -227,11 +227,11 @@ def golden_model(name="traj_vlm_tiny", batch=2, new_tokens=152):
 
 
 def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unfreeze_lm=False, batch=2, new_tokens=24,
-                   point="v12", unfreeze_pc=False):
+                   point="v12", unfreeze_pc=False, hd128=False):
     """Smaller fixtures for the other recipes of SURVEY 8d: (a) ``--unfreeze_language_model`` (model_arch.py:40-45):
     gradients of every LLM-layer tensor; (b) config E: the base PointBERT encoder yaml (trans 1152, 12 heads x 96,
     k=48, enc 512, single-Linear projector) with the default freezing: logits / loss / trainable grads / greedy ids."""
-    llm = LlmCfg.tiny()
+    llm = LlmCfg.tiny_hd128() if hd128 else LlmCfg.tiny()
     m = ref_shim.build_reference_model(llm, point_cfg_name)
     sd = synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True)
     m.load_state_dict(sd, strict=True)
@@ -245,6 +245,8 @@ def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unf
     if not unfreeze_pc:
         m.model.point_backbone.eval()                      # model_arch.py:121-122
     cfg = TrajVLMConfig.tiny() if point == "v12" else TrajVLMConfig.tiny_base()
+    if hd128:
+        cfg = TrajVLMConfig.tiny_hd128()
     bt = synth.make_batch(cfg, batch, seed=1)
     ids, mask, pc = bt["tokens"], bt["attention_masks"], bt["pcrgbs"]
     P = bt["prompts"].shape[1]
@@ -315,6 +317,141 @@ def golden_variant(name, point_cfg_name="PointTransformer_8192point_2layer", unf
         out["greedy_step_top2gap"] = (sl.topk(2, -1).values[..., 0] - sl.topk(2, -1).values[..., 1]).numpy()
     np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
     print(f"{name}.npz: loss={out['loss']:.6f} size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
+
+
+def golden_trained(name="traj_vlm_hd128_trained", batch=2, new_tokens=152, steps=400, lr=2e-2):
+    """A fixture whose greedy decode is a REAL trajectory (every earlier greedy golden emitted 1-2
+    distinct ids), on a trunk with the full-size head width (2 heads x 128) so the head_dim-128 tcgen05 attention, its
+    backward and the decode attention are pinned to the reference, not only to op tests.
+
+    Recipe (all of it reproducible from this file): det_state_dict weights; the REAL reference model is over-fitted on the
+    synthetic batch for ``steps`` Adam steps, training only rows 32000..32261 of ``embed_tokens`` / ``lm_head`` (point +
+    trajectory vocabulary) and the RMSNorm weights - small enough to store.  The trained values are rounded to bf16, loaded
+    back, and every golden quantity is produced by the reference from the ROUNDED weights."""
+    llm = LlmCfg.tiny_hd128()
+    m = ref_shim.build_reference_model(llm)
+    sd = synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True)
+    m.load_state_dict(sd, strict=True)
+    cfg = TrajVLMConfig.tiny_hd128()
+    bt = synth.make_batch(cfg, batch, seed=1)
+    ids, mask, pc = bt["tokens"], bt["attention_masks"], bt["pcrgbs"]
+    P = bt["prompts"].shape[1]
+    lo, hi = 32000, llm.vocab_size
+    for p_ in m.parameters():
+        p_.requires_grad = False
+    norm_names = [k for k, _ in m.named_parameters() if k.endswith("layernorm.weight") or k == "model.norm.weight"]
+    named = dict(m.named_parameters())
+    train = [named["model.embed_tokens.weight"], named["lm_head.weight"]] + [named[k] for k in norm_names]
+    for p_ in train:
+        p_.requires_grad = True
+    m.eval()                                                   # no dropout anywhere; encoder on running stats
+    opt = torch.optim.Adam(train, lr=lr)
+    rowmask = torch.zeros(llm.vocab_size, 1)
+    rowmask[lo:hi] = 1.0
+
+    def loss_of(logits):
+        lg = logits[:, P - 1:-1, :]
+        return torch.nn.functional.cross_entropy(lg.reshape(-1, lg.shape[-1]), ids[:, P:].flatten(), ignore_index=llm.pad_token_id)
+
+    for it in range(steps):
+        opt.zero_grad(set_to_none=True)
+        loss = loss_of(_ref_forward(m, ids, mask, pc).logits)
+        loss.backward()
+        named["model.embed_tokens.weight"].grad.mul_(rowmask)
+        named["lm_head.weight"].grad.mul_(rowmask)
+        opt.step()
+        if it % 25 == 0 or it == steps - 1:
+            print(f"  overfit step {it}: loss {loss.item():.5f}", flush=True)
+    with torch.no_grad():
+        for p_ in train:
+            p_.copy_(p_.to(torch.bfloat16).float())
+    delta = {"rows_lo": np.int64(lo), "embed_rows": named["model.embed_tokens.weight"][lo:hi].detach().numpy().copy(),
+             "lm_head_rows": named["lm_head.weight"][lo:hi].detach().numpy().copy()}
+    for k in norm_names:
+        delta[f"norm/{k}"] = named[k].detach().numpy().copy()
+    # ---- goldens from the rounded weights, default freezing of model_arch.py:33-51
+    for p_ in m.parameters():
+        p_.requires_grad = True
+    for p_ in m.model.point_backbone.parameters():
+        p_.requires_grad = False
+    for p_ in m.model.layers.parameters():
+        p_.requires_grad = False
+    m.train(); m.model.layers.eval(); m.model.point_backbone.eval()
+    m.zero_grad(set_to_none=True)
+    out = dict(fps_seed=np.int64(FPS_SEED), fps_start=_fps_start(pc.shape[1], batch).numpy(), tokens=ids.numpy(),
+               prompt_len=np.int64(P), torch_version=np.array(torch.__version__),
+               transformers_version=np.array(__import__("transformers").__version__), **delta)
+    logits = _ref_forward(m, ids, mask, pc).logits
+    loss = loss_of(logits)
+    loss.backward()
+    L = logits.detach()
+    rng = np.random.default_rng(3)
+    cols = np.sort(np.concatenate([rng.choice(32000, 256, replace=False), np.arange(32000, 32262)]))
+    rows = np.sort(np.concatenate([np.arange(0, 8), np.arange(510, 530), np.arange(P - 4, L.shape[1])]))
+    out.update(logit_rows=rows, logit_cols=cols, logits_sub=L[:, rows][:, :, cols].numpy(), logits_lse=torch.logsumexp(L, -1).numpy(),
+               loss=np.float64(loss.item()))
+    for k, p_ in m.named_parameters():
+        if p_.grad is None:
+            continue
+        g = p_.grad.detach()
+        out[f"gradnorm/{k}"] = np.float64(g.norm().item())
+        flat = g.flatten()
+        sel = torch.from_numpy(rng.choice(flat.numel(), min(4096, flat.numel()), replace=False)).long()
+        out[f"gradidx/{k}"] = sel.numpy()
+        out[f"gradval/{k}"] = flat[sel].numpy()
+    # ---- manual KV-cache greedy decode (SURVEY 8c) with EOS handling of HF greedy search
+    m.eval()
+    _, _, ru = ref_shim.load()
+    with torch.no_grad():
+        msk = bt["prompt_masks"].clone()
+        r = _ref_forward(m, bt["prompts"].clone(), msk, pc, use_cache=True)
+        past = r.past_key_values
+        step_logits = [r.logits[:, -1].float()]
+        unfinished = torch.ones(batch, dtype=torch.long)
+        gen = []
+        for t in range(new_tokens):
+            nxt = step_logits[-1].argmax(-1)
+            nxt = nxt * unfinished + llm.pad_token_id * (1 - unfinished)
+            gen.append(nxt)
+            unfinished = unfinished & (nxt != llm.eos_token_id).long()
+            msk = torch.cat((msk, torch.ones(batch, 1, dtype=torch.bool)), 1)
+            if t == new_tokens - 1 or unfinished.max() == 0:
+                break
+            r = m(input_ids=nxt[:, None], attention_mask=msk, past_key_values=past, use_cache=True, return_dict=True)
+            past = r.past_key_values
+            step_logits.append(r.logits[:, -1].float())
+        gen = torch.stack(gen, 1)
+        sl = torch.stack(step_logits, 1)
+        out["greedy_ids"] = gen.numpy()
+        out["greedy_step_logits_sub"] = sl[:, :, cols].numpy()
+        t2 = sl.topk(2, -1).values
+        out["greedy_step_top2gap"] = (t2[..., 0] - t2[..., 1]).numpy()
+        # post-processing of train.py:240-246 with the REAL str_to_float on the decoded string (tokens spelled as the
+        # tokenizer of builder.py:33-46 would: "<pK>" joined by spaces, "<tsep>" separators)
+        maxmin = [2.5, 0.1]
+        names = {32003: "<ts>", 32004: "<tsep>", 32005: "<te>"}
+        for b in range(batch):
+            toks = gen[b].tolist()
+            if llm.eos_token_id in toks:
+                toks = toks[:toks.index(llm.eos_token_id)]
+            s, prev_bin = "", False
+            for t_ in toks:
+                if 32006 <= t_ < 32262:
+                    s += (" " if prev_bin else "") + f"<p{t_ - 32006}>"
+                    prev_bin = True
+                else:
+                    s += names.get(t_, "?")
+                    prev_bin = False
+            rr = ru.str_to_float(s, maxmin, "val", rt2=True, num_bins=256)
+            out[f"greedy_poses_rt2/{b}"] = np.zeros((0, 6), np.float32) if rr is None else rr
+            o = tt.ids_to_poses(gen[b].tolist())
+            out[f"greedy_poses_raw/{b}"] = np.zeros((0, 6), np.float32) if o is None else o
+        out["maxmin"] = np.array(maxmin)
+    agree = (gen == ids[:, P:P + gen.shape[1]]).float().mean().item()
+    np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
+    print(f"{name}.npz: loss={out['loss']:.6f} greedy==training sequence on {agree:.3f} of steps, "
+          f"distinct ids {len(np.unique(out['greedy_ids']))}, min top2 gap {out['greedy_step_top2gap'].min():.3f}, "
+          f"size={os.path.getsize(os.path.join(GOLD, name + '.npz')) / 1e6:.2f} MB")
 
 
 def golden_metrics():
@@ -436,6 +573,13 @@ if __name__ == "__main__":
     import sys
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "trained":
+        golden_trained()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "hd128":
+        # 2 heads x 128: forward / loss / gradients of EVERY LLM-layer tensor / greedy ids through the head_dim-128 kernels
+        golden_variant("traj_vlm_hd128_unfrozen_lm", unfreeze_lm=True, hd128=True)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "metrics":
         golden_metrics()
         sys.exit(0)

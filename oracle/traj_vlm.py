@@ -70,6 +70,11 @@ class LlmCfg:
         return LlmCfg()
 
     @staticmethod
+    def tiny_hd128() -> "LlmCfg":
+        """Tiny trunk with the FULL-size head width (2 heads x 128): pins the head_dim-128 attention / decode kernels."""
+        return LlmCfg(num_heads=2)
+
+    @staticmethod
     def full() -> "LlmCfg":
         return LlmCfg(hidden_size=4096, intermediate_size=11008, num_layers=32, num_heads=32)
 

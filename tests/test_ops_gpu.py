@@ -128,6 +128,60 @@ def test_attention_fwd_bwd(hd, H, L, causal):
         close(dqkv[:, :, j], qf.grad[:, :, j], 2.5e-2)
 
 
+def _collate_like_mask(B, L):
+    """Key-padding masks shaped like collate_fn's (dataset.py:150-194): 515 point-block tokens, a description padded to 20
+    (pads sit MID-sequence, before the separator), trajectory tokens, tail padding."""
+    kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+    g = torch.Generator().manual_seed(5)
+    for b in range(B):
+        dl = int(torch.randint(8, 21, (1,), generator=g))
+        kmask[b, 515 + dl:535] = 0
+        kmask[b, L - int(torch.randint(0, 24, (1,), generator=g)):] = 0 if b % 2 else 1
+    return kmask
+
+
+def test_attention_fwd_bwd_at_bench_shape():
+    """The exact launch shape bench.py times (BASELINE configs[1]): B=8, 32 heads x 128, L=696, causal + collate-like key
+    padding, against fp32 torch: forward, lse and all three gradients of the tcgen05 kernels."""
+    B, H, hd, L = 8, 32, 128, 696
+    d = H * hd
+    qkv = rnd(B, L, 3, H, hd, seed=17)
+    kmask = _collate_like_mask(B, L)
+    o, lse = ops.attention(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal=True, kmask=kmask, want_lse=True)
+    qf = qkv.float().requires_grad_(True)
+    ref_o, ref_lse = _attn_ref(qf[:, :, 0], qf[:, :, 1], qf[:, :, 2], True, kmask)
+    close(o, ref_o, 1.5e-2)
+    assert (lse - ref_lse).abs().max() < 2e-2
+    do = rnd(B, L, d, seed=18)
+    ref_o.backward(do.float())
+    dqkv = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask)
+    for j in range(3):
+        close(dqkv[:, :, j], qf.grad[:, :, j], 2.5e-2)
+    # per-row check on the rows just after the padded gap (where a mask bug would show first)
+    for b in (0, 3):
+        r = slice(535, 540)
+        close(o[b, r], ref_o[b, r], 1.5e-2)
+
+
+def test_attention_prefill_at_bench_shape():
+    """Decode prefill of BASELINE configs[3]: P=544 prompt queries against the static KV cache (row stride = max_len),
+    32 heads x 128, then one cached token on top of it."""
+    B, H, hd, P, Lmax = 4, 32, 128, 544, 696
+    d = H * hd
+    kc, vc = rnd(B, Lmax, d, seed=21), rnd(B, Lmax, d, seed=22)
+    kmask = _collate_like_mask(B, Lmax)
+    kmask[:, P:] = 1
+    q = rnd(B, P, H, hd, seed=23)
+    o = ops.attention(q, kc[:, :P].view(B, P, H, hd), vc[:, :P].view(B, P, H, hd), causal=True, kmask=kmask, q_pos0=0)
+    ref, _ = _attn_ref(q, kc[:, :P].view(B, P, H, hd), vc[:, :P].view(B, P, H, hd), True, kmask)
+    close(o, ref, 1.5e-2)
+    q1 = rnd(B, 3 * d, seed=24)
+    od = ops.attention_decode(q1, kc, vc, H, hd, kmask=kmask, len_static=P + 1)
+    ref1, _ = _attn_ref(q1[:, :d].reshape(B, 1, H, hd), kc[:, :P + 1].view(B, P + 1, H, hd), vc[:, :P + 1].view(B, P + 1, H, hd),
+                        False, kmask)
+    close(od, ref1.view(B, d), 1.5e-2)
+
+
 @pytest.mark.parametrize("hd,H", [(64, 4), (128, 32)])
 def test_attention_prefill_with_cache_and_decode(hd, H):
     B, d, Lmax, P = 3, H * hd, 96, 70

@@ -10,7 +10,7 @@ from oracle import traj_tokenizer as tt
 from oracle.traj_vlm import LlmCfg, PointCfg, TrajVLMOracle, train_loss, greedy_decode
 from egoscaler_b200 import synth
 from egoscaler_b200.config import TrajVLMConfig
-from conftest import GOLDEN
+from conftest import GOLDEN, apply_trained_delta
 
 
 @pytest.fixture(scope="module")
@@ -179,10 +179,10 @@ def test_sampling_filter_matches_hf_processors():
 
 
 # ------------------------------------------------------------------ other recipes (fixtures: make_golden.py variants)
-def _variant_check(name, point_cfg, vlm_cfg, unfreeze_lm, min_grads):
+def _variant_check(name, point_cfg, vlm_cfg, unfreeze_lm, min_grads, llm=None):
     gv = np.load(os.path.join(GOLDEN, name + ".npz"))
     torch.manual_seed(0)
-    m = TrajVLMOracle(LlmCfg.tiny(), point_cfg)
+    m = TrajVLMOracle(llm or LlmCfg.tiny(), point_cfg)
     m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
     m.configure_trainable(unfreeze_language_model=unfreeze_lm)
     m.eval()
@@ -223,6 +223,43 @@ def _variant_check(name, point_cfg, vlm_cfg, unfreeze_lm, min_grads):
 def test_oracle_unfrozen_language_model_matches_reference():
     """--unfreeze_language_model (model_arch.py:40-45): gradients of every LLM-layer tensor."""
     _variant_check("traj_vlm_tiny_unfrozen_lm", PointCfg(), TrajVLMConfig.tiny(), True, 9 + 2 * 9)
+
+
+def test_oracle_hd128_unfrozen_language_model_matches_reference():
+    """The full-size head width (2 heads x 128) at parity-test size: every LLM-layer gradient vs the real reference."""
+    _variant_check("traj_vlm_hd128_unfrozen_lm", PointCfg(), TrajVLMConfig.tiny_hd128(), True, 9 + 2 * 9, llm=LlmCfg.tiny_hd128())
+
+
+def test_oracle_hd128_trained_greedy_trajectory_matches_reference():
+    """traj_vlm_hd128_trained.npz: the over-fitted reference model decodes a REAL trajectory; the restatement must emit
+    the same 152 ids (the reference's smallest top-2 margin is > 8), the same logits, and the same poses as the
+    reference's own str_to_float on the decoded string."""
+    g = np.load(os.path.join(GOLDEN, "traj_vlm_hd128_trained.npz"))
+    m = TrajVLMOracle(LlmCfg.tiny_hd128(), PointCfg())
+    m.load_state_dict(apply_trained_delta(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), g), strict=True)
+    m.configure_trainable()
+    m.eval()
+    bt = synth.make_batch(TrajVLMConfig.tiny_hd128(), 2, seed=1)
+    assert np.array_equal(bt["tokens"].numpy(), g["tokens"])
+    P = int(g["prompt_len"])
+    start = torch.from_numpy(g["fps_start"])
+    logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=start, training=True)
+    loss = train_loss(logits, bt["tokens"], P, 0)
+    sub = logits.detach()[:, g["logit_rows"]][:, :, g["logit_cols"]].numpy()
+    np.testing.assert_allclose(sub, g["logits_sub"], atol=2e-3, rtol=1e-4)
+    assert abs(loss.item() - float(g["loss"])) < 1e-5
+    ref = g["greedy_ids"]
+    assert len(np.unique(ref)) > 100 and float(g["greedy_step_top2gap"].min()) > 1.0        # a real, decisive trajectory
+    ids, scores = greedy_decode(m, bt["prompts"], bt["prompt_masks"], bt["pcrgbs"], 152, fps_start=start, return_scores=True)
+    gen = ids[:, P:].numpy()
+    assert np.array_equal(gen[:, :ref.shape[1]], ref)
+    assert np.array_equal(ref, g["tokens"][:, P:P + ref.shape[1]])            # ... and it IS the training trajectory
+    sl = torch.stack(scores, 1)[:, :, g["logit_cols"]].numpy()
+    np.testing.assert_allclose(sl, g["greedy_step_logits_sub"][:, :sl.shape[1]], atol=2e-3, rtol=1e-4)
+    for b in range(2):
+        raw = tt.ids_to_poses(gen[b].tolist())
+        assert np.array_equal(raw, g[f"greedy_poses_raw/{b}"]) and raw.shape == (20, 6)
+        assert np.array_equal(tt.rt2_scaler(raw.copy(), g["maxmin"].tolist()), g[f"greedy_poses_rt2/{b}"])
 
 
 def test_oracle_base_encoder_matches_reference():
