@@ -42,6 +42,10 @@ def parse():
     ap.add_argument("--encoder", default="v12", choices=["v12", "base"],
                     help="point encoder yaml: v12 = PointTransformer_8192point_2layer (default), base = PointTransformer_base_8192point "
                          "(BASELINE configs[4], SURVEY 8d config E)")
+    ap.add_argument("--verify-dp", action="store_true",
+                    help="N>1: only run the numeric check of the gradient exchange (dp_check) and print it")
+    ap.add_argument("--dp-check-batch", type=int, default=1, help="samples per rank in the dp_check")
+    ap.add_argument("--no-dp-check", action="store_true")
     ap.add_argument("--recipe", default="default", choices=["default", "unfreeze_lm", "unfreeze_pc"],
                     help="freezing recipe of model_arch.py:33-51: default, --unfreeze_language_model, --unfreeze_pc_encoder")
     return ap.parse_args()
@@ -209,6 +213,14 @@ def run_b200(args):
         return
     model.train()
     tr = Trainer(model, lr=2e-5, world_size=world)
+    dpc = None
+    if world > 1 and (args.verify_dp or not args.no_dp_check):
+        dpc = dp_check(torch, dist, tr, cfg, args, dev, world, rank)
+        if args.verify_dp:
+            if rank == 0:
+                print(json.dumps({"dp_check": dpc, "n_gpus": world}), flush=True)
+            dist.destroy_process_group()
+            return
     nb = 4
     hb = host_batches(torch, cfg, B, nb, seed0=1000 * (rank + 1))          # different data per rank, same weights
     P = hb[0]["prompts"].shape[1]
@@ -298,6 +310,8 @@ def run_b200(args):
                      "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P, args.recipe) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
         "loss": round(float(loss_res), 4),
     }
+    if dpc is not None:
+        line["dp_check"] = dpc
     if not args.no_decode:
         del tr
         torch.cuda.empty_cache()
@@ -311,6 +325,97 @@ def run_b200(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
+    """SURVEY 8d config C correctness: "post-all-reduce grads == 1-GPU grads on the concatenated batch" (what DeepSpeed's
+    ZeRO-1 engine guarantees at train.py:92-125,183-184).  Every rank takes its shard of ONE global batch, runs
+    forward/backward with the real NCCL exchange, then recomputes the whole global batch locally without any exchange and
+    compares: default recipe - every all-reduced gradient; unfreeze_lm - each LLM-layer unit on its ZeRO-1 OWNER rank
+    (reduce-to-owner); unfreeze_pc - the local recomputation runs shard by shard, because the train-mode BatchNorm of the
+    point encoder uses per-rank batch statistics exactly like the reference (no SyncBN, model_arch.py:121-122).  Then one
+    optimizer step is taken and the updated bf16 weights must be bit-identical on all ranks (broadcast-from-owner)."""
+    from egoscaler_b200 import synth
+    b = args.dp_check_batch
+    gb = synth.make_batch(cfg, b * world, seed=4242, random_desc_len=True)
+    gb = {k: v.to(dev) for k, v in gb.items()}
+    P = gb["prompts"].shape[1]
+    starts = torch.randint(0, gb["pcrgbs"].shape[1], (b * world,), generator=torch.Generator().manual_seed(99)).to(dev)
+    drop_u = None
+    if tr.enc_train is not None:
+        depth = len(tr.enc_train["pk"].blocks)
+        drop_u = torch.rand(depth, 2, b * world, generator=torch.Generator().manual_seed(98)).to(dev)
+    ntok = (gb["tokens"][:, P:] != cfg.pad_token_id).sum(1)
+    equal_counts = bool((ntok == ntok[0]).all())                         # mean-of-means == global mean only then
+
+    def fb(lo, hi, sync):
+        return tr.forward_backward(gb["tokens"][lo:hi], gb["attention_masks"][lo:hi], gb["pcrgbs"][lo:hi], P, starts[lo:hi],
+                                   None if drop_u is None else drop_u[:, :, lo:hi].contiguous(), sync=sync)
+
+    lo, hi = rank * b, (rank + 1) * b
+    tr.zero_grad()
+    loss_shard = fb(lo, hi, True)
+    tr._wait_reduce()
+    torch.cuda.synchronize()
+    got = {n: tr.grad[n].clone() for n in tr.names}
+    for u, (k, li, _) in enumerate(tr.trunk_units):
+        if tr.dp.owns(u):
+            got[f"unit{u}:{k}.{li}"] = tr.wgrad[k][li].clone()
+    tr.zero_grad()
+    if tr.enc_train is not None:
+        losses = [fb(r * b, (r + 1) * b, False) for r in range(world)]
+        loss_ref = sum(float(x) for x in losses) / world
+        ref_scale = 1.0                                                   # sum over shards of per-shard means, like the exchange
+    else:
+        loss_ref = float(fb(0, b * world, False))
+        ref_scale = float(world)                                          # global mean * world == sum of equal-count shard means
+    worst, worst_name, n_cmp = 0.0, "", 0
+    for name, g in got.items():
+        if name.startswith("unit"):
+            u = int(name[4:name.index(":")])
+            k, li, _ = tr.trunk_units[u]
+            ref = tr.wgrad[k][li]
+        else:
+            ref = tr.grad[name]
+        ref = ref.double() * ref_scale
+        den = float(ref.norm())
+        if den == 0.0:
+            continue
+        rel = float((g.double() - ref).norm()) / den
+        n_cmp += 1
+        if rel > worst:
+            worst, worst_name = rel, name
+    del got
+    # one real step: weights must stay bit-identical across ranks
+    tr.zero_grad()
+    fb(lo, hi, True)
+    tr.optimizer_step()
+    sums = []
+    bits = lambda t: t.detach().contiguous().view(torch.int16 if t.element_size() == 2 else torch.int32).long().sum().double()
+    for n in tr.names:
+        sums.append(bits(tr.param[n]))
+    for _, _, t in tr.trunk_units:
+        sums.append(bits(t))
+    chk = torch.stack(sums)
+    mx, mn = chk.clone(), chk.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+    identical = bool((mx == mn).all())
+    w = torch.tensor([worst, float(loss_shard)], device=dev, dtype=torch.float64)
+    wmax = w.clone()
+    dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
+    wsum = w.clone()
+    dist.all_reduce(wsum, op=dist.ReduceOp.SUM)
+    names = [None] * world
+    dist.all_gather_object(names, (worst, worst_name))
+    worst_all = max(names, key=lambda t: t[0])
+    return {"ranks": world, "per_rank_batch": b, "recipe": args.recipe, "encoder": args.encoder,
+            "max_rel_l2": round(float(wmax[0]), 6), "worst_tensor": worst_all[1], "tensors_compared_rank0": n_cmp,
+            "tolerance": 2e-2, "ok": bool(float(wmax[0]) <= 2e-2 and identical),
+            "loss_mean_over_ranks": round(float(wsum[1]) / world, 5), "loss_single_gpu_global_batch": round(loss_ref, 5),
+            "equal_token_counts": equal_counts, "weights_bit_identical_after_step": identical,
+            "reference": ("per-shard recomputation on one GPU (per-rank BatchNorm statistics, no SyncBN)" if tr.enc_train is not None
+                          else "one GPU on the concatenated global batch")}
 
 
 def decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks):

@@ -36,12 +36,12 @@ int esb_point_layout(const int64_t* ids, int B, int L, int64_t patch_id, int64_t
     return point_layout(CLLP(ids), B, L, patch_id, start_id, end_id, n_point, info, ST(stream));
 }
 int esb_embed_splice_fwd(const int64_t* ids, const void* embed, const void* feats, const int32_t* splice_pos, int n_point,
-                         void* x, int B, int L, int d, void* stream) {
-    return embed_splice_fwd(CLLP(ids), embed, feats, splice_pos, n_point, x, B, L, d, ST(stream));
+                         void* x, int B, int L, int d, int64_t vocab_size, void* stream) {
+    return embed_splice_fwd(CLLP(ids), embed, feats, splice_pos, n_point, x, B, L, d, vocab_size, ST(stream));
 }
 int esb_embed_splice_bwd(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, float* dembed,
-                         void* dfeats, int64_t padding_idx, int B, int L, int d, void* stream) {
-    return embed_splice_bwd(CLLP(ids), dx, splice_pos, n_point, dembed, dfeats, padding_idx, B, L, d, ST(stream));
+                         void* dfeats, int64_t padding_idx, int B, int L, int d, int64_t vocab_size, void* stream) {
+    return embed_splice_bwd(CLLP(ids), dx, splice_pos, n_point, dembed, dfeats, padding_idx, B, L, d, vocab_size, ST(stream));
 }
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream) {

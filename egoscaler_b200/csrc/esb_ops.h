@@ -53,9 +53,9 @@ int gelu(const void* z, const void* dy, void* y, long long n, int backward, cuda
 int point_layout(const long long* ids, int B, int L, long long patch_id, long long start_id, long long end_id, int n_point,
                  int* info, cudaStream_t s);
 int embed_splice_fwd(const long long* ids, const void* embed, const void* feats, const int* splice_pos, int n_point, void* x,
-                     int B, int L, int d, cudaStream_t s);
+                     int B, int L, int d, long long vocab, cudaStream_t s);
 int embed_splice_bwd(const long long* ids, const void* dx, const int* splice_pos, int n_point, float* dembed, void* dfeats,
-                     long long padding_idx, int B, int L, int d, cudaStream_t s);
+                     long long padding_idx, int B, int L, int d, long long vocab, cudaStream_t s);
 int copy_rows(const void* src, long long src_bstride_bytes, long long src_ld_bytes, void* dst, long long dst_bstride_bytes,
               long long dst_ld_bytes, int batches, int rows, int row_bytes, cudaStream_t s);
 int transpose_bf16(const void* in, long long ld_in, void* out, long long ld_out, int R, int C, cudaStream_t s);

@@ -54,7 +54,7 @@ __global__ void point_layout_kernel(const long long* __restrict__ ids, int B, in
 //                                                                                  : embed[ids[b, l], :]
 __global__ void __launch_bounds__(256) embed_splice_fwd_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ embed,
                                                                const __nv_bfloat16* __restrict__ feats, const int* __restrict__ splice_pos,
-                                                               int n_point, __nv_bfloat16* __restrict__ x, int B, int L, int d) {
+                                                               int n_point, __nv_bfloat16* __restrict__ x, int B, int L, int d, long long vocab) {
     const int dv = d >> 3;
     const long long total = static_cast<long long>(B) * L * dv;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -67,8 +67,14 @@ __global__ void __launch_bounds__(256) embed_splice_fwd_kernel(const long long* 
         const uint4* src;
         if (sp >= 0 && l >= sp && l < sp + n_point)
             src = reinterpret_cast<const uint4*>(feats + (static_cast<long long>(b) * n_point + (l - sp)) * d) + v;
-        else
-            src = reinterpret_cast<const uint4*>(embed + ids[tok] * d) + v;
+        else {
+            const long long id = ids[tok];
+            if (id < 0 || id >= vocab) {                      // torch raises a device assert; the raw-pointer ABI stays in bounds
+                reinterpret_cast<uint4*>(x + tok * d)[v] = make_uint4(0u, 0u, 0u, 0u);
+                continue;
+            }
+            src = reinterpret_cast<const uint4*>(embed + id * d) + v;
+        }
         reinterpret_cast<uint4*>(x + tok * d)[v] = __ldg(src);
     }
 }
@@ -78,7 +84,7 @@ __global__ void __launch_bounds__(256) embed_splice_fwd_kernel(const long long* 
 __global__ void __launch_bounds__(256) embed_splice_bwd_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ dx,
                                                                const int* __restrict__ splice_pos, int n_point,
                                                                float* __restrict__ dembed, __nv_bfloat16* __restrict__ dfeats,
-                                                               long long padding_idx, int B, int L, int d) {
+                                                               long long padding_idx, int B, int L, int d, long long vocab) {
     const int dv = d >> 3;
     const long long total = static_cast<long long>(B) * L * dv;
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -93,7 +99,7 @@ __global__ void __launch_bounds__(256) embed_splice_bwd_kernel(const long long* 
             if (dfeats) reinterpret_cast<uint4*>(dfeats + (static_cast<long long>(b) * n_point + (l - sp)) * d)[v] = g;
         } else if (dembed) {
             const long long id = ids[tok];
-            if (id == padding_idx) continue;
+            if (id == padding_idx || id < 0 || id >= vocab) continue;
             float* o = dembed + id * d + v * 8;
             const float2 a = unpack_bf16x2(g.x), bb = unpack_bf16x2(g.y), c = unpack_bf16x2(g.z), e = unpack_bf16x2(g.w);
             atomicAdd(o + 0, a.x); atomicAdd(o + 1, a.y); atomicAdd(o + 2, bb.x); atomicAdd(o + 3, bb.y);
@@ -181,20 +187,20 @@ int point_layout(const long long* ids, int B, int L, long long patch_id, long lo
     return check_launch("point_layout");
 }
 int embed_splice_fwd(const long long* ids, const void* embed, const void* feats, const int* splice_pos, int n_point, void* x,
-                     int B, int L, int d, cudaStream_t s) {
+                     int B, int L, int d, long long vocab, cudaStream_t s) {
     if (B <= 0 || L <= 0) return ESB_OK;
     if (d & 7) { set_last_error("embed_splice: d must be a multiple of 8"); return ESB_ERR_INVALID_ARG; }
     embed_splice_fwd_kernel<<<g_grid(static_cast<long long>(B) * L * (d / 8), 256), 256, 0, s>>>(
         ids, static_cast<const __nv_bfloat16*>(embed), static_cast<const __nv_bfloat16*>(feats), splice_pos, n_point,
-        static_cast<__nv_bfloat16*>(x), B, L, d);
+        static_cast<__nv_bfloat16*>(x), B, L, d, vocab);
     return check_launch("embed_splice_fwd");
 }
 int embed_splice_bwd(const long long* ids, const void* dx, const int* splice_pos, int n_point, float* dembed, void* dfeats,
-                     long long padding_idx, int B, int L, int d, cudaStream_t s) {
+                     long long padding_idx, int B, int L, int d, long long vocab, cudaStream_t s) {
     if (B <= 0 || L <= 0) return ESB_OK;
     if (d & 7) { set_last_error("embed_splice: d must be a multiple of 8"); return ESB_ERR_INVALID_ARG; }
     embed_splice_bwd_kernel<<<g_grid(static_cast<long long>(B) * L * (d / 8), 256), 256, 0, s>>>(
-        ids, static_cast<const __nv_bfloat16*>(dx), splice_pos, n_point, dembed, static_cast<__nv_bfloat16*>(dfeats), padding_idx, B, L, d);
+        ids, static_cast<const __nv_bfloat16*>(dx), splice_pos, n_point, dembed, static_cast<__nv_bfloat16*>(dfeats), padding_idx, B, L, d, vocab);
     return check_launch("embed_splice_bwd");
 }
 int copy_rows(const void* src, long long src_bstride_bytes, long long src_ld_bytes, void* dst, long long dst_bstride_bytes,

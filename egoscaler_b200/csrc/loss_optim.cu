@@ -27,7 +27,9 @@ __global__ void __launch_bounds__(256) ce_fwd_bwd_kernel(__nv_bfloat16* __restri
     const long long row = blockIdx.x;
     __nv_bfloat16* lp = logits + row * ld;
     const long long tgt = targets[row];
-    const bool ignored = (tgt == ignore_index);
+    // a target outside [0, V) that is not ignore_index (torch raises a device assert there) is treated as ignored: the raw-pointer
+    // ABI must never read or write out of bounds (e.g. the reference's IGNORE_INDEX = -100 while ignore_index = pad = 0)
+    const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
     MaxSum acc = {-INFINITY, 0.0f};
     if (!ignored) {
         for (int i = threadIdx.x; i < V; i += blockDim.x) acc = ms_combine(acc, MaxSum{__bfloat162float(lp[i]), 1.0f});
@@ -61,12 +63,12 @@ __global__ void __launch_bounds__(256) ce_fwd_bwd_kernel(__nv_bfloat16* __restri
 }
 
 // count non-ignored targets -> inv_count = 1/max(count,1)... (count==0 -> NaN mean like torch: 0/0) ; single block
-__global__ void ce_count_kernel(const long long* __restrict__ targets, long long n, long long ignore_index, float* inv_count) {
+__global__ void ce_count_kernel(const long long* __restrict__ targets, long long n, long long ignore_index, int V, float* inv_count) {
     __shared__ int cnt;
     if (threadIdx.x == 0) cnt = 0;
     __syncthreads();
     int c = 0;
-    for (long long i = threadIdx.x; i < n; i += blockDim.x) c += (targets[i] != ignore_index);
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) c += (targets[i] != ignore_index && targets[i] >= 0 && targets[i] < V);
     atomicAdd(&cnt, c);
     __syncthreads();
     if (threadIdx.x == 0) *inv_count = 1.0f / static_cast<float>(cnt);
@@ -89,7 +91,7 @@ __global__ void ce_reduce_kernel(const float* __restrict__ row_loss, long long n
 int cross_entropy(void* logits, long long ld, long long rows, int V, const long long* targets, long long ignore_index,
                   float* row_loss, float* scratch_inv_count, float* loss, int write_grad, cudaStream_t s) {
     if (rows <= 0) return ESB_OK;
-    ce_count_kernel<<<1, 1024, 0, s>>>(targets, rows, ignore_index, scratch_inv_count);
+    ce_count_kernel<<<1, 1024, 0, s>>>(targets, rows, ignore_index, V, scratch_inv_count);
     ce_fwd_bwd_kernel<<<static_cast<unsigned>(rows), 256, 0, s>>>(static_cast<__nv_bfloat16*>(logits), ld, V, targets, ignore_index,
                                                                   row_loss, scratch_inv_count, write_grad);
     ce_reduce_kernel<<<1, 1024, 0, s>>>(row_loss, rows, scratch_inv_count, loss);

@@ -46,7 +46,8 @@ class TrainPointEncoder:
         self.bn = {}
         for key, name in (("bn1", "encoder.first_conv.1"), ("bn3", "encoder.second_conv.1")):
             self.bn[key] = dict(gamma=_f32(g(name + ".weight")), beta=_f32(g(name + ".bias")),
-                                rm=g(name + ".running_mean"), rv=g(name + ".running_var"), name=name)
+                                rm=g(name + ".running_mean"), rv=g(name + ".running_var"),
+                                nbt=g(name + ".num_batches_tracked"), name=name)
         self.red_w, self.red_b = _bf(g("reduce_dim.weight")), _f32(g("reduce_dim.bias"))
         self.pos1_w, self.pos1_b = _pad_k(g("pos_embed.0.weight").detach(), KPAD), _f32(g("pos_embed.0.bias"))
         self.pos2_w, self.pos2_b = _bf(g("pos_embed.2.weight")), _f32(g("pos_embed.2.bias"))
@@ -71,6 +72,7 @@ def _bn_train_fwd(z: torch.Tensor, bn: dict, save: dict, key: str) -> torch.Tens
     s0, s1, mean, rstd, A, Cc = f(), f(), f(), f(), f(), f()
     ops.colsum2(z, None, s0, s1)
     ops.bn_coeffs(0, s0, s1, R, bn["gamma"], bn["beta"], mean, rstd, A, None, Cc, running_mean=bn["rm"], running_var=bn["rv"])
+    bn["nbt"].add_(1)                   # nn.BatchNorm1d bookkeeping (state_dict parity; momentum is fixed, the count is unused)
     y = ops.affine_cols(z, A, Cc, relu=True)
     save[key] = (z, y, mean, rstd)
     return y

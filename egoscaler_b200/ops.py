@@ -308,17 +308,17 @@ def embed_splice(ids, embed, feats, splice_pos, n_point: int) -> torch.Tensor:
     B, L = ids.shape
     d = embed.shape[1]
     x = torch.empty(B * L, d, device=ids.device, dtype=torch.bfloat16)
-    _l.call("esb_embed_splice_fwd", ids.data_ptr(), embed.data_ptr(), _p(feats), _p(splice_pos), n_point, x.data_ptr(), B, L, d, _stream())
+    _l.call("esb_embed_splice_fwd", ids.data_ptr(), embed.data_ptr(), _p(feats), _p(splice_pos), n_point, x.data_ptr(), B, L, d, embed.shape[0], _stream())
     return x
 
 
-def embed_splice_bwd(ids, dx, splice_pos, n_point: int, dembed, dfeats, padding_idx: int):
+def embed_splice_bwd(ids, dx, splice_pos, n_point: int, dembed, dfeats, padding_idx: int, vocab: Optional[int] = None):
     ids = ids.contiguous()
     B, L = ids.shape
     d = dx.shape[-1]
     assert dx.is_contiguous()
     _l.call("esb_embed_splice_bwd", ids.data_ptr(), dx.data_ptr(), _p(splice_pos), n_point, _p(dembed), _p(dfeats), padding_idx,
-            B, L, d, _stream())
+            B, L, d, int(vocab if vocab is not None else (dembed.shape[0] if dembed is not None else 1 << 62)), _stream())
 
 
 def copy_rows(src: torch.Tensor, dst: torch.Tensor):

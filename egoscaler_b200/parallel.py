@@ -37,10 +37,14 @@ class GradExchange:
         self.pg = process_group
         self.rank = 0
         self._pending: List = []
+        self._reduce_is_allreduce = False
         if self.world > 1:
             import torch.distributed as dist
             self.dist = dist
             self.rank = dist.get_rank(process_group)
+            # gloo has no device-tensor ``reduce`` (NCCL has): the single-GPU two-process Trainer test runs the owner
+            # reduction as an all-reduce there - same values on the owner, only more traffic
+            self._reduce_is_allreduce = dist.get_backend(process_group) == "gloo"
 
     # ---- ownership (ZeRO-1)
     def owner(self, unit: int) -> int:
@@ -61,6 +65,9 @@ class GradExchange:
 
     def reduce_to_owner_async(self, unit: int, tensor: torch.Tensor) -> None:
         if self.world == 1:
+            return
+        if self._reduce_is_allreduce and tensor.is_cuda:
+            self._pending.append(self.dist.all_reduce(tensor, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True))
             return
         self._pending.append(self.dist.reduce(tensor, dst=self._global(self.owner(unit)), op=self.dist.ReduceOp.SUM,
                                               group=self.pg, async_op=True))

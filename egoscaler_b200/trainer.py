@@ -44,6 +44,8 @@ class Trainer:
         self.warmup, self.total = warmup_steps, total_steps
         self.pg, self.world = process_group, world_size
         self.step_count = 0
+        if world_size > 1:
+            self._sync_initial_state()
         named = dict(model.named_parameters())
         # LLM-layer tensors are optimised as the PACKED kernel operands (q|k|v and gate|up share one buffer each; AdamW is
         # element-wise, so this equals stepping the reference's separate parameters); everything else by parameter name.
@@ -74,6 +76,29 @@ class Trainer:
         self.v = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.last_loss: Optional[torch.Tensor] = None
+        self._sync = world_size > 1
+
+    def _sync_initial_state(self):
+        """What ``deepspeed.initialize`` does at train.py:119-125: every rank starts from rank 0's parameters and buffers
+        (ranks seeded differently would otherwise train diverging replicas silently).  Packed q|k|v / gate|up parameters are
+        views of one buffer each, so the packed buffers are sent instead of their three / two views."""
+        import torch.distributed as dist
+        m = self.model
+        src = dist.get_global_rank(self.pg, 0) if self.pg is not None else 0
+        sent = []
+        for t in list(m.wqkv) + list(m.wgu):
+            sent.append(t)
+        skip = (".self_attn.q_proj.", ".self_attn.k_proj.", ".self_attn.v_proj.", ".mlp.gate_proj.", ".mlp.up_proj.")
+        for n, t in list(m.named_parameters()) + list(m.named_buffers()):
+            if any(k in n for k in skip):
+                continue
+            sent.append(t.detach())
+        hs = [dist.broadcast(t, src=src, group=self.pg, async_op=True) for t in sent]
+        for h in hs:
+            h.wait()
+        m.repack()
+        if self.enc_train is not None:
+            self.enc_train["pk"].refresh()
 
     def zero_grad(self):
         for g in self.grad.values():
@@ -85,8 +110,13 @@ class Trainer:
 
     # ------------------------------------------------------------------ forward + backward
     def forward_backward(self, tokens: torch.Tensor, attention_masks: torch.Tensor, pcrgbs: torch.Tensor, prompt_len: int,
-                         fps_start: Optional[torch.Tensor] = None, drop_u: Optional[torch.Tensor] = None) -> torch.Tensor:
+                         fps_start: Optional[torch.Tensor] = None, drop_u: Optional[torch.Tensor] = None,
+                         sync: bool = True) -> torch.Tensor:
+        """Forward + backward of one micro-batch; gradients ACCUMULATE into ``self.grad`` / ``self.wgrad``.  ``sync=False``
+        (DDP's ``no_sync``): queue no gradient exchange - for every micro-batch but the last of a --grad_accum_steps group
+        (train.py:183 lets DeepSpeed do the same), so already-summed gradients are never reduced twice."""
         m, cfg = self.model, self.model.cfg
+        self._sync = bool(sync) and self.world > 1
         dev = m.dev
         tokens = tokens.to(dev)
         B, L = tokens.shape
@@ -119,7 +149,7 @@ class Trainer:
         ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
         # ---- trunk backward (data gradients through the frozen layers)
         dx = m.trunk.backward(dh.view(B * L, d), B, L, kmask, saved, wgrad=self.wgrad,
-                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self.world > 1) else None)
+                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None)
         # ---- embedding scatter + projector
         dfeats = torch.empty(B, n_point, d, device=dev, dtype=torch.bfloat16)
         ops.embed_splice_bwd(tokens, dx, splice_pos, n_point, self.grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id)
@@ -137,7 +167,8 @@ class Trainer:
 
     # ------------------------------------------------------------------ data parallel (parallel.GradExchange)
     def _reduce_async(self, names: List[str]):
-        self.dp.allreduce_async(self.grad[n] for n in names)
+        if self._sync:
+            self.dp.allreduce_async(self.grad[n] for n in names)
 
     def _reduce_layer_async(self, li: int):
         """ZeRO-1 gradient exchange of one LLM layer, started as soon as its backward has been queued: every unit is

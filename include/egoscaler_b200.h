@@ -150,13 +150,14 @@ int esb_gelu(const void* z, const void* dy, void* y, int64_t n, int backward, vo
 int esb_point_layout(const int64_t* ids, int B, int L, int64_t patch_id, int64_t start_id, int64_t end_id, int n_point,
                      int32_t* info, void* stream);
 /* embed_tokens(input_ids) (pointllm.py:107) + splice of the projected point tokens (pointllm.py:134-171):
- * x[b,l] = feats[b, l - pos[b]] inside [pos[b], pos[b]+n_point), embed[ids[b,l]] elsewhere (pos[b] < 0: no splice). */
+ * x[b,l] = feats[b, l - pos[b]] inside [pos[b], pos[b]+n_point), embed[ids[b,l]] elsewhere (pos[b] < 0: no splice).
+ * ids outside [0, vocab_size) never touch memory: zero row forward, skipped backward. */
 int esb_embed_splice_fwd(const int64_t* ids, const void* embed, const void* feats, const int32_t* splice_pos, int n_point,
-                         void* x, int B, int L, int d, void* stream);
+                         void* x, int B, int L, int d, int64_t vocab_size, void* stream);
 /* Backward: point rows -> dfeats (bf16 copy), other rows scatter-added into dembed (fp32, row padding_idx skipped as
  * nn.Embedding(padding_idx) does). */
 int esb_embed_splice_bwd(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, float* dembed,
-                         void* dfeats, int64_t padding_idx, int B, int L, int d, void* stream);
+                         void* dfeats, int64_t padding_idx, int B, int L, int d, int64_t vocab_size, void* stream);
 /* Batched strided row copy (logits slice train.py:174-175, hidden-row gathers); all byte strides multiples of 16. */
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream);

@@ -167,6 +167,7 @@ def test_unfrozen_point_encoder_gradients_and_step(name, base):
             ref = gv[f"{st}/{nm}"]
             got = sd[f"model.point_backbone.encoder.{nm}.{st}"].float().cpu().numpy()
             assert np.abs(got - ref).max() <= 2e-2 * np.abs(ref).max() + 1e-4, (nm, st)
+        assert int(sd[f"model.point_backbone.encoder.{nm}.num_batches_tracked"]) == 1       # nn.BatchNorm1d bookkeeping
     # optimizer step updates encoder parameters and the eval-mode packed operands; loss decreases on the same batch
     w0 = sd["model.point_backbone.blocks.blocks.3.mlp.fc1.weight"].clone()
     tr.optimizer_step()
