@@ -17,6 +17,7 @@ import os
 import sys
 import threading
 import time
+import time as time_mod
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -35,6 +36,8 @@ def parse():
     ap.add_argument("--config", default="full", choices=["full", "tiny"])
     ap.add_argument("--batch", type=int, default=8, help="per-GPU batch (train.py --bs 8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the stock eager-PyTorch-on-this-GPU baseline")
+    ap.add_argument("--no-traj-tokens", action="store_true", help="skip the quantize/dequantize kernel measurement")
     ap.add_argument("--no-decode", action="store_true", help="skip the batched greedy-decode measurement")
     ap.add_argument("--decode-only", action="store_true", help="profiling aid: build the model and run only the decode measurement")
     ap.add_argument("--decode-batch", type=int, default=32, help="sequences per GPU (BASELINE configs[3]: 256 / 8 GPUs)")
@@ -57,6 +60,12 @@ def workload_name(cfgname, B, encoder="v12", recipe="default"):
         rec = {"default": "default freezing", "unfreeze_lm": "--unfreeze_language_model", "unfreeze_pc": "--unfreeze_pc_encoder"}[recipe]
         return f"full-size traj-VLM bf16 training step (LLaMA-7B dims, {enc}, B={B}/GPU, L=696, P=544, {rec})"
     return f"tiny traj-VLM training step (d=256, 2 layers, B={B}/GPU, L=696)"
+
+
+def config_dict(args, B, world, L=696, P=544):
+    """The `config` object of the JSON line - identical for our arm and the reference arm (the driver compares them)."""
+    return {"workload": workload_name(args.config, B, args.encoder, args.recipe), "per_gpu_batch": B, "global_batch": B * world,
+            "seq_len": L, "prompt_len": P, "parallelism": f"dp{world}", "l2": "working set (13.5 GB of weights per pass) >> 126 MB L2"}
 
 
 def flops_per_sample_train(cfg, L=696, T=152, recipe="default"):
@@ -268,17 +277,23 @@ def run_b200(args):
         step_resident(i)
     sampler = ClockSampler(local)
     sampler.start()
-    timer = GemmTimer(torch)
-    ops.gemm_timer = timer
     l0 = esb_lib.launch_count
-    ms_res, loss_res = timed(step_resident, args.steps)
+    ms_res, loss_res = timed(step_resident, args.steps)                    # headline: no per-kernel events in this pass
     launches = (esb_lib.launch_count - l0) // args.steps
-    ops.gemm_timer = None
-    torch.cuda.synchronize()
-    gemm_ms = timer.total_ms()
     for i in range(2):
         step_e2e(i)
     ms_e2e, loss_e2e = timed(step_e2e, args.steps)
+    # roofline pass: the same resident step with a CUDA-event pair around every GEMM launch (644 events per step cost
+    # ~1 % of host time, so this pass is NOT the headline)
+    timer = GemmTimer(torch)
+    ops.gemm_timer = timer
+    gsteps = max(2, min(args.steps, 8))
+    ms_gpass, _ = timed(step_resident, gsteps)
+    ops.gemm_timer = None
+    torch.cuda.synchronize()
+    gemm_ms = timer.total_ms() / gsteps * args.steps                       # scaled to K steps: formulas below stay per-K
+    timer.flops = timer.flops / gsteps * args.steps
+    timer.n = timer.n // gsteps * args.steps
     clocks = sampler.stop()
 
     peaks = {}
@@ -297,29 +312,46 @@ def run_b200(args):
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": round(ms_res / args.steps, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic (collate_fn-shaped batches, random-init weights)",
-        "config": {"workload": workload_name(args.config, B, args.encoder, args.recipe), "per_gpu_batch": B, "global_batch": B * world, "seq_len": L,
-                   "prompt_len": P, "parallelism": f"dp{world}", "l2": "working set (13.5 GB of weights per pass) >> 126 MB L2"},
+        "config": config_dict(args, B, world, L, P),
         "e2e": {"value": round(e2e, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                 "ms_per_step": round(ms_e2e / args.steps, 3)},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel", "achieved": round(achieved_tf, 1), "peak": peak_tf,
                      "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": gemm_traffic(), "peak_source": peak_src,
+                     "traffic_source": "committed ncu --set full capture (profiles/gemm_traffic.json), not measured in this run",
+                     "timing": "CUDA events around every GEMM launch in a separate pass of the same resident step "
+                               f"({gsteps} steps, {round(ms_gpass / gsteps, 3)} ms/step with events)",
                      "launches_per_step": timer.n // args.steps, "gemm_ms_per_step": round(gemm_ms / args.steps, 3),
-                     "gemm_share_of_step": round(gemm_ms / ms_res, 4),
+                     "gemm_share_of_step": round(gemm_ms / args.steps / (ms_gpass / gsteps), 4),
                      "step_model_tflops": round(flops_per_sample_train(cfg, L, L - P, args.recipe) * B / (ms_res / args.steps * 1e-3) / 1e12, 1)},
         "loss": round(float(loss_res), 4),
     }
     if dpc is not None:
         line["dp_check"] = dpc
+    tr = None                                                          # frees optimizer state + gradient buffers
+    torch.cuda.empty_cache()
     if not args.no_decode:
-        del tr
-        torch.cuda.empty_cache()
         line["decode"] = decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks)
+    if not args.no_traj_tokens and args.recipe == "default":
+        try:
+            line["traj_tokens"] = traj_tokens_bench(torch, dev, peaks, with_cpu=(rank == 0 and world == 1))
+        except Exception as e:
+            line["traj_tokens"] = {"error": repr(e)[:300]}
+    if rank == 0 and world == 1 and not args.no_gpu_baseline and args.recipe == "default":
+        try:
+            model = None
+            torch.cuda.empty_cache()
+            line["gpu_baseline"] = gpu_eager_baseline(torch, cfg, args, dev, B)
+            line["gpu_baseline"]["speedup_of_value"] = round(value / line["gpu_baseline"]["value"], 3)
+        except Exception as e:
+            line["gpu_baseline"] = {"value": None, "error": repr(e)[:300]}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"] = cpu_reference_step(args, budget_s=min(args.cpu_budget_s, 60.0), max_steps=1)
+                line["cpu_baseline"] = cpu_reference_step(args, budget_s=min(args.cpu_budget_s, 45.0), max_steps=2, warmup=1)
+                if line["cpu_baseline"].get("value"):
+                    line["vs_cpu_port"] = round(e2e / line["cpu_baseline"]["value"], 1)      # e2e arm / CPU port (vs_baseline stays null: BASELINE.md publishes no number)
             except Exception as e:  # the baseline is informative; the GPU numbers stand without it
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
@@ -418,6 +450,151 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
                           else "one GPU on the concatenated global batch")}
 
 
+def traj_tokens_bench(torch, dev, peaks, with_cpu=True):
+    """north_star's trajectory-token kernel pair on SURVEY 8d's workload: 2^24 float32 values uniform in [-1.05, 1.05] with every
+    exact bin edge and NaN / +-inf specials mixed in.  quantize = discretize_action (utils/utils.py:13-16): 4 B in + 8 B (int64
+    id) out = 12 B/value; dequantize = token_to_action + float32 cast (:18-21,:96): 8 B in + 4 B out = 12 B/value.  Three rotating
+    buffer sets (600 MB) so no launch finds its data in the 126 MB L2.  CPU baseline: the NumPy oracle round trip on the same
+    values on the host."""
+    import numpy as np
+    from egoscaler_b200 import ops
+    n = 1 << 24
+    g = torch.Generator(device=dev).manual_seed(5)
+    nset = 3
+    xs = []
+    edges = torch.linspace(-1, 1, 256, dtype=torch.float64).float().to(dev)
+    special = torch.tensor([float("nan"), float("inf"), float("-inf"), -1.0, 1.0, 0.0], device=dev)
+    for _ in range(nset):
+        x = torch.rand(n, device=dev, generator=g) * 2.1 - 1.05
+        x[:256] = edges
+        x[256:262] = special
+        xs.append(x[torch.randperm(n, device=dev, generator=g)].contiguous())
+    ids = [ops.traj_quantize(x, 256, 32006) for x in xs]
+    outs = [ops.traj_dequantize(i.view(-1, 6)[: n // 6], 256, 32006) for i in ids]        # warm-up + outputs for the check
+    reps = 30
+
+    def time(fn):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for r in range(reps):
+            fn(r % nset)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    obuf = [torch.empty_like(i) for i in ids]
+    fbuf = [torch.empty(n // 6, 6, device=dev) for _ in ids]
+    lq = lambda k: ops._l.call("esb_traj_quantize", xs[k].data_ptr(), 0, n, 256, 32006, obuf[k].data_ptr(), ops._stream())
+    ld = lambda k: ops._l.call("esb_traj_dequantize", ids[k].data_ptr(), n // 6, 256, 32006, 0, 0.0, 0.0, fbuf[k].data_ptr(), ops._stream())
+    lq(0); ld(0)
+    ms_q, ms_d = time(lq), time(ld)
+    hbm = float(peaks.get("hbm_gbs", 6400.0))
+    gq = 12.0 * n / (ms_q * 1e-3) / 1e9
+    gd = 12.0 * (n // 6 * 6) / (ms_d * 1e-3) / 1e9
+    out = {"values": n, "bytes_per_value": 12,
+           "quantize": {"us": round(ms_q * 1e3, 2), "achieved": round(gq, 1), "peak": hbm, "unit": "GB/s", "frac": round(gq / hbm, 4)},
+           "dequantize": {"us": round(ms_d * 1e3, 2), "achieved": round(gd, 1), "peak": hbm, "unit": "GB/s", "frac": round(gd / hbm, 4)},
+           "l2": "3 rotating buffer sets of 201 MB each > 126 MB L2"}
+    if with_cpu:
+        from oracle import traj_tokenizer as tt
+        xh = xs[0].cpu().numpy()
+        t0 = time_mod.time()
+        q = np.asarray(tt.discretize_action(xh, 256))
+        t1 = time_mod.time()
+        dq = np.asarray(tt.token_to_action(q, 256)).astype(np.float32)
+        t2 = time_mod.time()
+        ok = bool(np.array_equal(q + 32006, ids[0].cpu().numpy()))
+        valid = (q >= 0)
+        ok_d = bool(np.array_equal(dq.reshape(-1)[: n // 6 * 6][valid[: n // 6 * 6]],
+                                   outs[0].cpu().numpy().reshape(-1)[valid[: n // 6 * 6]]))
+        out["cpu_baseline"] = {"kind": "port", "cores": 1, "sample": "the same 2^24 values, NumPy np.digitize / table lookup (oracle/traj_tokenizer.py)",
+                               "quantize_gbs": round(12.0 * n / (t1 - t0) / 1e9, 3), "dequantize_gbs": round(12.0 * n / (t2 - t1) / 1e9, 3)}
+        out["bit_exact_vs_cpu"] = ok and ok_d
+    return out
+
+
+def gpu_eager_baseline(torch, cfg, args, dev, B, steps=5, warmup=3):
+    """BASELINE.md 3b / SURVEY 8d config B "reference timing": the same module in stock eager PyTorch on the SAME GPU - the oracle
+    restatement (plain nn.Linear / nn.Embedding / F.cross_entropy) moved to cuda, bf16 weights for the frozen parts like the
+    DeepSpeed bf16 engine (train.py:97-98), autocast(bf16) (train.py:166), attention through F.scaled_dot_product_attention with
+    the 4-D padding+causal mask HF builds, torch.optim.AdamW (train.py:113).  cuBLASLt + SDPA + ~3k eager launches: what
+    train.py:166-184 runs on a GPU today.  Informative only; never on the product path."""
+    import torch.nn.functional as F
+    from egoscaler_b200 import synth
+    from oracle import traj_vlm as ov
+
+    def sdpa_forward(self, x, cos, sin, mask, cache):
+        Bq, Lq, _ = x.shape
+        q = self.q_proj(x).view(Bq, Lq, self.heads, self.hd).transpose(1, 2)
+        k = self.k_proj(x).view(Bq, Lq, self.heads, self.hd).transpose(1, 2)
+        v = self.v_proj(x).view(Bq, Lq, self.heads, self.hd).transpose(1, 2)
+        cos, sin = cos.to(q.dtype), sin.to(q.dtype)
+        q = q * cos + ov._rot_half(q) * sin
+        k = k * cos + ov._rot_half(k) * sin
+        o = F.scaled_dot_product_attention(q, k, v, attn_mask=mask.expand(Bq, 1, Lq, Lq))
+        return self.o_proj(o.transpose(1, 2).reshape(Bq, Lq, -1))
+
+    llm = ov.LlmCfg.full() if args.config == "full" else ov.LlmCfg.tiny()
+    pc = ov.PointCfg() if args.encoder == "v12" else ov.PointCfg.base()
+    old_fwd = ov._SelfAttn.forward
+    ov._SelfAttn.forward = sdpa_forward
+    try:
+        with torch.device("meta"):
+            m = ov.TrajVLMOracle(llm, pc)
+        m = m.to_empty(device=dev)
+        gen = torch.Generator(device=dev).manual_seed(0)
+        with torch.no_grad():
+            for n_, p in list(m.named_parameters()) + list(m.named_buffers()):
+                if not p.dtype.is_floating_point:
+                    p.zero_()
+                elif n_.endswith("running_var") or (p.dim() == 1 and not n_.endswith("bias") and not n_.endswith("running_mean")):
+                    p.fill_(1.0)
+                elif p.dim() == 1:
+                    p.zero_()
+                else:
+                    p.normal_(0.0, 0.02, generator=gen)
+        m.configure_trainable()
+        m.to(torch.bfloat16)                                            # DeepSpeed bf16 engine: every parameter in bf16 (train.py:97-98)
+        m.train()
+        m.model.layers.eval()
+        m.model.point_backbone.eval()
+        opt = torch.optim.AdamW([q for q in m.parameters() if q.requires_grad], lr=2e-5)
+        bts = [{k: v.to(dev) for k, v in synth.make_batch(cfg, B, seed=500 + i, random_desc_len=True).items()} for i in range(2)]
+        P = bts[0]["prompts"].shape[1]
+        start = torch.zeros(B, dtype=torch.long, device=dev)
+
+        def step(i):
+            bt = bts[i % 2]
+            opt.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=start, training=True)
+                loss = ov.train_loss(logits, bt["tokens"], P, cfg.pad_token_id)
+            loss.backward()
+            opt.step()
+            return loss
+
+        for i in range(warmup):
+            step(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            loss = step(i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        res = {"value": round(B / (ms * 1e-3), 3), "unit": UNIT, "ms_per_step": round(ms, 2), "steps": steps, "warmup": warmup,
+               "per_gpu_batch": B, "loss": round(float(loss), 4),
+               "what": "stock eager PyTorch on this GPU: oracle module on cuda, bf16 trunk, autocast(bf16), SDPA with the HF 4-D mask, "
+                       f"torch.optim.AdamW; torch {torch.__version__}"}
+    finally:
+        ov._SelfAttn.forward = old_fwd
+    del m, opt
+    torch.cuda.empty_cache()
+    return res
+
+
 def decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks):
     """BASELINE configs[3]: batched greedy trajectory generation with the static KV cache, batch-sharded (no
     collective): `--decode-batch` prompts per GPU of P=544 tokens (point block + description + first pose), T=152 new
@@ -465,10 +642,12 @@ def decode_bench(torch, dist, model, cfg, args, dev, world, rank, peaks):
 
 
 # ------------------------------------------------------------------------------------------------ CPU oracle port
-def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 0):
+def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 1):
     """Times the reference algorithm's training step (oracle/traj_vlm.py, plain fp32 PyTorch restatement of
-    pointllm.py:181-253 + train.py:166-184) on the host cores, on a bounded sample of the workload: ONE sample
-    (B=1) of the same config per step.  kind="port": /root/reference does not exist on the GPU box."""
+    pointllm.py:181-253 + train.py:166-184) on the host cores, on a bounded sample of the workload: the largest per-step batch
+    b in {B, B/2, ..., 1} whose fp32 activations fit in host RAM next to the 27 GB of fp32 weights (the GPU arm's B = 8 needs
+    ~115 GB).  Same init recipe as the GPU arm (N(0, 0.02) LLM / head, fan-in scaled encoder).  kind="port": /root/reference
+    does not exist on the GPU box."""
     import psutil
     import torch
     from egoscaler_b200 import synth
@@ -477,20 +656,29 @@ def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 0):
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    cfg = TrajVLMConfig.full() if args.config == "full" else TrajVLMConfig.tiny()
-    llm = LlmCfg.full() if args.config == "full" else LlmCfg.tiny()
-    layers = llm.num_layers
-    need_gb = 4e-9 * (llm.num_layers * (4 * llm.hidden_size ** 2 + 3 * llm.hidden_size * llm.intermediate_size)
-                      + 2 * llm.vocab_size * llm.hidden_size) * 1.35 + 8
+    enc = getattr(args, "encoder", "v12")
+    if args.config == "full":
+        cfg = TrajVLMConfig.full() if enc == "v12" else TrajVLMConfig.full_base()
+        llm = LlmCfg.full()
+    else:
+        cfg = TrajVLMConfig.tiny() if enc == "v12" else TrajVLMConfig.tiny_base()
+        llm = LlmCfg.tiny()
+    d, f, nl, V, L = llm.hidden_size, llm.intermediate_size, llm.num_layers, llm.vocab_size, 696
+    w_gb = 4e-9 * (nl * (4 * d * d + 3 * d * f) + 2 * V * d)
+    # fp32 autograd state per sample: ~(10 d + 5 f) floats per token per layer + 2 L^2 H attention maps + logits (x3 for CE)
+    act_gb = 4e-9 * (nl * (L * (10 * d + 5 * f) + 2 * L * L * llm.num_heads) + 3 * L * V)
     avail_gb = psutil.virtual_memory().available / 1e9
     note = ""
-    if need_gb > avail_gb:                      # not enough host RAM for 27 GB of fp32 weights: fewer layers, say so
-        layers = max(1, int(llm.num_layers * (avail_gb - 12) / need_gb))
-        llm.num_layers = layers
-        note = f" (host RAM {avail_gb:.0f} GB: {layers} of {cfg.num_hidden_layers} layers)"
+    b = max(1, int(getattr(args, "batch", 1)))
+    while b > 1 and w_gb * 1.1 + 6 + 1.3 * b * act_gb > 0.8 * avail_gb:     # conservative: never drive the host out of memory
+        b //= 2
+    if w_gb * 1.1 + 6 + act_gb > avail_gb:       # not even one sample next to all layers: fewer layers, say so
+        llm.num_layers = max(1, int(nl * (avail_gb - 8) / (w_gb * 1.1 + act_gb)))
+        note = f" (host RAM {avail_gb:.0f} GB: {llm.num_layers} of {nl} layers)"
     with torch.device("meta"):
-        m = TrajVLMOracle(llm, PointCfg())
+        m = TrajVLMOracle(llm, PointCfg() if enc == "v12" else PointCfg.base())
     m = m.to_empty(device="cpu")
+    g = torch.Generator().manual_seed(0)
     with torch.no_grad():
         for n_, p in list(m.named_parameters()) + list(m.named_buffers()):
             if not p.dtype.is_floating_point:
@@ -499,21 +687,23 @@ def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 0):
                 p.fill_(1.0)
             elif p.dim() == 1:
                 p.zero_()
+            elif "point_backbone" in n_ or "point_proj" in n_:
+                p.normal_(0.0, 1.0 / (p.shape[1] ** 0.5), generator=g)
             else:
-                p.uniform_(-0.035, 0.035)
+                p.normal_(0.0, 0.02, generator=g)
     m.configure_trainable()
     m.train()
     m.model.layers.eval()
     m.model.point_backbone.eval()
     opt = torch.optim.AdamW([q for q in m.parameters() if q.requires_grad], lr=2e-5)
-    bt = synth.make_batch(cfg, 1, seed=5)
+    bt = synth.make_batch(cfg, b, seed=5, random_desc_len=True)
     P = bt["prompts"].shape[1]
     times = []
     t_begin = time.time()
     for i in range(warmup + max_steps):
         t0 = time.time()
         opt.zero_grad(set_to_none=True)
-        logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=torch.zeros(1, dtype=torch.long), training=True)
+        logits = m(bt["tokens"], bt["attention_masks"], bt["pcrgbs"], fps_start=torch.zeros(b, dtype=torch.long), training=True)
         loss = train_loss(logits, bt["tokens"], P, cfg.pad_token_id)
         loss.backward()
         opt.step()
@@ -523,26 +713,26 @@ def cpu_reference_step(args, budget_s: float, max_steps: int, warmup: int = 0):
         if time.time() - t_begin > budget_s and times:
             break
     t = sum(times) / len(times)
-    return {"value": round(1.0 / t, 5), "unit": UNIT, "cores": cores, "kind": "port", "steps_timed": len(times),
-            "s_per_step": round(t, 3),
-            "sample": f"1 sample (B=1) per step of the same workload, fp32, torch {torch.__version__} CPU, "
-                      f"{torch.get_num_threads()} threads{note}"}
+    return {"value": round(b / t, 5), "unit": UNIT, "cores": cores, "kind": "port", "steps_timed": len(times), "warmup": warmup,
+            "s_per_step": round(t, 3), "batch_per_step": b,
+            "sample": f"{b} sample(s) per step of the same workload (host RAM {avail_gb:.0f} GB bounds the batch), fp32, "
+                      f"torch {torch.__version__} CPU, {torch.get_num_threads()} threads{note}"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # keep the whole run within a few minutes whatever K/W the driver asks for
+    # keep the whole run within a few minutes whatever K/W the driver asks for: the budget stops the loop early
     warm = 1 if args.warmup > 0 else 0
     cb = cpu_reference_step(args, budget_s=args.cpu_budget_s, max_steps=max(1, args.steps), warmup=warm)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world,
-        "steps": cb["steps_timed"], "steps_requested": args.steps, "warmup": warm,
+        "steps": cb["steps_timed"], "steps_requested": args.steps, "warmup": warm, "warmup_requested": args.warmup,
         "ms_per_step": round(cb["s_per_step"] * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic (collate_fn-shaped batch, random-init weights)",
-        "config": {"workload": workload_name(args.config, args.batch), "sample": cb["sample"]},
+        "dtype": "f32", "data": "synthetic (collate_fn-shaped batches, random-init weights)",
+        "config": config_dict(args, args.batch, world),
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

@@ -94,3 +94,34 @@ class TrajVLMConfig:
 
     def to_dict(self):
         return asdict(self)
+
+
+def config_from_hf(hf) -> TrajVLMConfig:
+    """The HF / PointLLM config object the reference passes around (``AutoConfig.from_pretrained(model_name)``,
+    builder.py:14; fields read at pointllm.py:32-59) -> TrajVLMConfig.  ``vocab_size`` is taken as given: build the
+    config with the post-``add_trajectory_token`` size (32262) - see ``TrajPointLLMForCausalLM.resize_token_embeddings``."""
+    if hf is None:
+        return TrajVLMConfig.full()
+    g = lambda k, dflt: getattr(hf, k, dflt) if not isinstance(hf, dict) else hf.get(k, dflt)
+    name = g("point_backbone_config_name", "PointTransformer_8192point_2layer")
+    if "base" in str(name):
+        point = PointEncoderConfig.base()
+    else:
+        point = PointEncoderConfig.v12()
+    heads = int(g("num_attention_heads", 32))
+    kv = g("num_key_value_heads", heads)
+    if kv is not None and int(kv) != heads:
+        raise ValueError("egoscaler_b200 implements multi-head attention (LLaMA-7B / Vicuna): num_key_value_heads must equal "
+                         "num_attention_heads")
+    rope = g("rope_theta", None)
+    if rope is None:
+        rp = g("rope_parameters", None) or {}
+        rope = rp.get("rope_theta", 10000.0) if isinstance(rp, dict) else 10000.0
+    pad = g("pad_token_id", 0)
+    return TrajVLMConfig(hidden_size=int(g("hidden_size", 4096)), intermediate_size=int(g("intermediate_size", 11008)),
+                         num_hidden_layers=int(g("num_hidden_layers", 32)), num_attention_heads=heads,
+                         vocab_size=int(g("vocab_size", VOCAB_SIZE)), rms_norm_eps=float(g("rms_norm_eps", 1e-6)),
+                         rope_theta=float(rope), max_position_embeddings=int(g("max_position_embeddings", 2048)),
+                         pad_token_id=int(0 if pad is None else pad), bos_token_id=int(g("bos_token_id", 1) or 1),
+                         eos_token_id=int(g("eos_token_id", 2) or 2),
+                         mm_use_point_start_end=bool(g("mm_use_point_start_end", True)), point=point)

@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .config import (TrajVLMConfig, POINT_PATCH_TOKEN_ID, POINT_START_TOKEN_ID, POINT_END_TOKEN_ID)
+from .config import (TrajVLMConfig, POINT_PATCH_TOKEN_ID, POINT_START_TOKEN_ID, POINT_END_TOKEN_ID, config_from_hf)
 from .encoder import (PackedPointEncoder, PackedProjector, point_encoder_forward, projector_forward)
 from .llm import KVCache, LayerWeights, LlamaTrunk
 from .params import ParamTree
@@ -46,9 +46,35 @@ class _ModelView:
 
 
 class TrajPointLLMForCausalLM(ParamTree):
-    def __init__(self, cfg: TrajVLMConfig, device="cuda", unfreeze_pc_encoder: bool = False,
-                 unfreeze_language_model: bool = False):
+    def __init__(self, *args, **kwargs):
+        """Two call forms:
+
+        * the reference's ``TrajPointLLMForCausalLM(args, config, model_name)`` (model_arch.py:13-24): ``args`` carries
+          ``unfreeze_pc_encoder`` / ``unfreeze_language_model`` (train.py:344-345), ``config`` is the HF / PointLLM config
+          object (``config_from_hf``), ``model_name`` a checkpoint directory or file whose ``state_dict`` is loaded when it
+          exists (the reference's ``from_pretrained`` at model_arch.py:26-31); optional ``device=``;
+        * the native ``TrajPointLLMForCausalLM(cfg: TrajVLMConfig, device="cuda", unfreeze_pc_encoder=False,
+          unfreeze_language_model=False)``.
+        """
+        ref_args = model_name = hf_config = None
+        if args and isinstance(args[0], TrajVLMConfig):
+            cfg = args[0]
+            device = args[1] if len(args) > 1 else kwargs.pop("device", "cuda")
+            unfreeze_pc_encoder = bool(kwargs.pop("unfreeze_pc_encoder", False))
+            unfreeze_language_model = bool(kwargs.pop("unfreeze_language_model", False))
+        else:
+            names = ("args", "config", "model_name")
+            vals = dict(zip(names, args))
+            vals.update({k: kwargs.pop(k) for k in names if k in kwargs})
+            ref_args, hf_config, model_name = vals.get("args"), vals.get("config"), vals.get("model_name")
+            cfg = hf_config if isinstance(hf_config, TrajVLMConfig) else config_from_hf(hf_config)
+            device = kwargs.pop("device", "cuda")
+            unfreeze_pc_encoder = bool(getattr(ref_args, "unfreeze_pc_encoder", False))
+            unfreeze_language_model = bool(getattr(ref_args, "unfreeze_language_model", False))
+        if kwargs:
+            raise TypeError(f"unexpected arguments: {sorted(kwargs)}")
         super().__init__(cfg, device)
+        self.args, self.config, self.model_name = ref_args, hf_config if hf_config is not None else cfg, model_name
         self.cfg = cfg
         self.dev = torch.device(device)
         p = cfg.point
@@ -72,6 +98,71 @@ class TrajPointLLMForCausalLM(ParamTree):
         self._lm_head_tiled = None                          # decode-layout copy of lm_head (ops.retile_weight)
         self._lm_head_folded = False                        # ... with model.norm folded into its columns
         self.v_pad = (cfg.vocab_size + 7) // 8 * 8          # logits leading dimension (16-byte rows)
+        self._enc_train = None                              # train-mode point encoder operands (--unfreeze_pc_encoder)
+        self._versions = None                               # autograd version counters the derived operands were built from
+        if model_name is not None:
+            self.load_pretrained_weights()
+
+    # ------------------------------------------------------------------ checkpoint (model_arch.py:26-31)
+    def load_pretrained_weights(self):
+        """``load_state_dict(parent_state_dict, strict=False)`` of model_arch.py:26-31 from ``model_name``: a directory
+        holding ``pytorch_model*.bin`` / ``*.safetensors`` shards or a single state-dict file.  A name that is not a path
+        (a hub id: no network here) leaves the random initialisation in place and says so."""
+        import glob
+        import os
+        import warnings
+        path = os.path.expanduser(str(self.model_name))
+        files = []
+        if os.path.isdir(path):
+            files = sorted(glob.glob(os.path.join(path, "*.safetensors"))) or sorted(glob.glob(os.path.join(path, "pytorch_model*.bin")))
+        elif os.path.isfile(path):
+            files = [path]
+        if not files:
+            warnings.warn(f"egoscaler_b200: no checkpoint files under {path!r}; parameters keep their initial values")
+            return
+        own = self.state_dict()
+        for f in files:
+            if f.endswith(".safetensors"):
+                from safetensors.torch import load_file
+                part = load_file(f)
+            else:
+                part = torch.load(f, map_location="cpu", weights_only=True)
+            for k, v in part.items():
+                if k not in own:
+                    continue
+                t = own[k]
+                if t.dim() == 2 and v.dim() == 2 and v.shape[0] < t.shape[0] and v.shape[1] == t.shape[1]:
+                    t[:v.shape[0]].copy_(v)                 # vocabulary grown by add_trajectory_token (builder.py:33-46)
+                else:
+                    t.copy_(v.view(t.shape))
+        self.repack()
+
+    def resize_token_embeddings(self, new_num_tokens: int, mean_resizing: bool = False):
+        """builder.py:44.  The parameter tree is allocated at ``cfg.vocab_size`` rows already (32262 after
+        add_trajectory_token); rows a smaller checkpoint did not provide keep their N(0, 0.02) initialisation, which is
+        what HF does for ``mean_resizing=False``.  Any other size would need a re-allocation: refuse loudly."""
+        if int(new_num_tokens) != self.cfg.vocab_size:
+            raise ValueError(f"egoscaler_b200 allocates embed_tokens / lm_head at cfg.vocab_size={self.cfg.vocab_size}; "
+                             f"build the config with vocab_size={int(new_num_tokens)} instead of resizing")
+        return self.model.embed_tokens
+
+    def initialize_tokenizer_point_backbone_config_wo_embedding(self, tokenizer):
+        """pointllm.py:281-300: read the point-token ids from the tokenizer into ``point_backbone_config``."""
+        c = self.point_backbone_config
+        for key, tok in (("point_patch_token", c["default_point_patch_token"]), ("point_start_token", c["default_point_start_token"]),
+                         ("point_end_token", c["default_point_end_token"])):
+            if hasattr(tokenizer, "convert_tokens_to_ids"):
+                c[key] = int(tokenizer.convert_tokens_to_ids([tok])[0])
+
+    def enc_train(self):
+        """Operands of the train-mode point encoder (BatchNorm batch statistics + DropPath), or None when it is frozen /
+        the module is in eval mode (model_arch.py:110-124)."""
+        if not self.unfreeze_pc_encoder:
+            return None
+        if self._enc_train is None:
+            from .encoder_train import TrainPointEncoder
+            self._enc_train = {"pk": TrainPointEncoder(self.cfg, self.named())}
+        return self._enc_train
 
     # ------------------------------------------------------------------ reference API surface
     def get_model(self) -> _ModelView:
@@ -120,6 +211,46 @@ class TrajPointLLMForCausalLM(ParamTree):
         self._trunk = LlamaTrunk(self.cfg, layers, self.dev)
         self._lm_head_T = None
         self._lm_head_tiled = None
+        if self._enc_train is not None:
+            self._enc_train["pk"].refresh()
+        self._versions = self._version_signature()
+
+    def _version_signature(self):
+        named = self.named()
+        proj = tuple(named[n]._version for pair in self.projector_params() for n in pair)
+        head = (self.lm_head.weight._version,)
+        enc = tuple(t._version for n, t in named.items() if n.startswith("model.point_backbone."))
+        trunk = tuple((self.wqkv[i]._version, self.wgu[i]._version,
+                       named[f"model.layers.{i}.self_attn.o_proj.weight"]._version, named[f"model.layers.{i}.mlp.down_proj.weight"]._version)
+                      for i in range(self.cfg.num_hidden_layers))
+        return {"proj": proj, "head": head, "enc": enc, "trunk": trunk}
+
+    def sync_derived(self):
+        """Rebuild the operand copies derived from parameters that an external optimizer (torch.optim.AdamW / DeepSpeed
+        stepping ``model.parameters()``) has updated in place since they were built: fp32 projector biases and transposed
+        projector weights, the contraction-major lm_head / trunk copies, the decode-layout copies, the folded point-encoder
+        operands.  Detection = autograd version counters (in-place updates bump them); ``Trainer`` refreshes explicitly."""
+        if self._trunk is None:
+            self.repack()
+            return
+        sig = self._version_signature()
+        old = self._versions
+        if old == sig:
+            return
+        if old is None or old["proj"] != sig["proj"]:
+            self._packed_proj.refresh()
+        if old is None or old["head"] != sig["head"]:
+            self._lm_head_T = None
+            self._lm_head_tiled = None
+        if old is None or old["enc"] != sig["enc"]:
+            self.repack_encoder()
+            if self._enc_train is not None:
+                self._enc_train["pk"].refresh()
+        if old is not None and old["trunk"] != sig["trunk"]:
+            for i, lw in enumerate(self._trunk.layers):
+                if old["trunk"][i] != sig["trunk"][i]:
+                    lw.refresh_derived()
+        self._versions = sig
 
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
         r = super().load_state_dict(state_dict, strict=strict, assign=False)
@@ -238,20 +369,33 @@ class TrajPointLLMForCausalLM(ParamTree):
         return out
 
     # ------------------------------------------------------------------ forward / generate (reference signatures)
-    @torch.no_grad()
     def forward(self, input_ids=None, attention_mask=None, past_key_values: Optional[KVCache] = None, inputs_embeds=None,
                 labels=None, use_cache=None, output_attentions=None, output_hidden_states=None, point_clouds=None,
-                return_dict=None, fps_start=None) -> CausalLMOutput:
+                return_dict=None, fps_start=None, drop_u=None) -> CausalLMOutput:
         """model_arch.py:53-75 -> pointllm.py:195-253.  Logits for all positions, bf16 (what autocast gives the
-        reference on GPU).  ``past_key_values`` follows the parent class' semantics."""
+        reference on GPU).  ``past_key_values`` follows the parent class' semantics.
+
+        With autograd enabled (and no KV cache) the logits carry a ``grad_fn``: ``loss.backward()`` on anything computed
+        from them runs the hand-written CUDA backward and fills ``.grad`` of the trainable parameters, so the reference's
+        loop body (train.py:165-184) and any ``torch.optim`` / DeepSpeed optimizer work unchanged (autograd.py)."""
         if inputs_embeds is not None or labels is not None:
             raise NotImplementedError("inputs_embeds / labels are never passed by the reference entry points")
+        self.sync_derived()
         cache = past_key_values
         B, L = input_ids.shape
-        if use_cache and cache is None:
-            cache = KVCache.allocate(self.cfg, B, max(self.cfg.max_position_embeddings, L), self.dev)
-        h, _ = self.hidden_states(input_ids, attention_mask, point_clouds, fps_start, cache)
-        logits = self.logits_from_hidden(h).view(B, L, self.cfg.vocab_size)
+        if torch.is_grad_enabled() and cache is None and not use_cache:
+            names = tuple(self.trainable_names())
+            if names:
+                from .autograd import TrajVLMFunction
+                named = dict(self.named_parameters())
+                logits = TrajVLMFunction.apply(self, input_ids, attention_mask, point_clouds, fps_start, drop_u, names,
+                                               *[named[n] for n in names])
+                return CausalLMOutput(logits=logits, past_key_values=None)
+        with torch.no_grad():
+            if use_cache and cache is None:
+                cache = KVCache.allocate(self.cfg, B, max(self.cfg.max_position_embeddings, L), self.dev)
+            h, _ = self.hidden_states(input_ids, attention_mask, point_clouds, fps_start, cache)
+            logits = self.logits_from_hidden(h).view(B, L, self.cfg.vocab_size)
         return CausalLMOutput(logits=logits, past_key_values=cache)
 
     __call__ = forward

@@ -17,7 +17,7 @@ from typing import Dict, List, Optional
 import torch
 
 from . import ops
-from .encoder import projector_backward
+from .autograd import backward_from_hidden, forward_hidden_train
 from .model import TrajPointLLMForCausalLM
 from .parallel import GradExchange
 
@@ -36,10 +36,7 @@ class Trainer:
                  weight_decay: float = 0.01, warmup_steps: int = 0, total_steps: int = 0, process_group=None,
                  world_size: int = 1):
         self.model = model
-        self.enc_train = None               # --unfreeze_pc_encoder (model_arch.py:36-38,121-122): encoder_train.py
-        if model.unfreeze_pc_encoder:
-            from .encoder_train import TrainPointEncoder
-            self.enc_train = {"pk": TrainPointEncoder(model.cfg, model.named())}
+        self.enc_train = model.enc_train()  # --unfreeze_pc_encoder (model_arch.py:36-38,121-122): encoder_train.py
         self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
         self.warmup, self.total = warmup_steps, total_steps
         self.pg, self.world = process_group, world_size
@@ -118,17 +115,11 @@ class Trainer:
         m, cfg = self.model, self.model.cfg
         self._sync = bool(sync) and self.world > 1
         dev = m.dev
-        tokens = tokens.to(dev)
-        B, L = tokens.shape
+        h, ctx = forward_hidden_train(m, tokens, attention_masks, pcrgbs, fps_start, drop_u)
+        tokens = ctx.tokens
+        B, L = ctx.B, ctx.L
         P, d, V = int(prompt_len), cfg.hidden_size, cfg.vocab_size
         Tn = L - P
-        n_point = m.point_backbone_config["point_token_len"]
-        kmask = m._kmask(attention_masks, dev)
-        saved, proj_saved = [], []
-        if self.enc_train is not None:
-            self.enc_train["drop_u"] = drop_u               # injected DropPath uniforms [depth, 2, B] (None: drawn on device)
-        h, splice_pos = m.hidden_states(tokens, attention_masks, pcrgbs, fps_start, None, saved, proj_saved,
-                                        enc_train=self.enc_train)
         # ---- head: rows P-1 .. L-2 only (train.py:174)
         hs = torch.empty(B, Tn, d, device=dev, dtype=torch.bfloat16)
         ops.copy_rows(h.view(B, L, d)[:, P - 1:L - 1, :], hs)
@@ -147,21 +138,10 @@ class Trainer:
         self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
         dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)
         ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
-        # ---- trunk backward (data gradients through the frozen layers)
-        dx = m.trunk.backward(dh.view(B * L, d), B, L, kmask, saved, wgrad=self.wgrad,
-                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None)
-        # ---- embedding scatter + projector
-        dfeats = torch.empty(B, n_point, d, device=dev, dtype=torch.bfloat16)
-        ops.embed_splice_bwd(tokens, dx, splice_pos, n_point, self.grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id)
-        pw = [w for w, _ in m.projector_params()]
-        pb = [b for _, b in m.projector_params()]
-        dtok = projector_backward(m._packed_proj, proj_saved, dfeats.view(B * n_point, d), [self.grad[n] for n in pw],
-                                  [self.grad[n] for n in pb], need_input_grad=self.enc_train is not None)
-        self._reduce_async(["model.embed_tokens.weight"] + pw + pb)
-        if self.enc_train is not None:
-            from .encoder_train import train_backward
-            train_backward(self.enc_train["pk"], self.enc_train.pop("saved"), dtok, self.grad)
-            self._reduce_async([n for n in self.names if n.startswith("model.point_backbone.")])
+        # ---- trunk backward (data gradients through the frozen layers), embedding scatter, projector, encoder
+        backward_from_hidden(m, ctx, dh.view(B * L, d), self.grad, self.wgrad,
+                             on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None,
+                             on_ready=self._reduce_async)
         self.last_loss = loss
         return loss
 
@@ -194,7 +174,8 @@ class Trainer:
                 p.detach().copy_(self.master[n])
         if self.trunk_units:
             self._trunk_step(lr, scale)
-        # refresh derived operands of the trainable tensors
+        # refresh derived operands of the trainable tensors (the fused AdamW kernel writes the parameters through raw
+        # pointers, so autograd's version counters - what model.sync_derived watches - do not move)
         self.model._lm_head_T = None
         self.model._lm_head_tiled = None
         self.model._packed_proj.refresh()

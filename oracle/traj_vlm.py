@@ -88,10 +88,11 @@ def fps(xyz: torch.Tensor, npoint: int, start: Optional[torch.Tensor] = None) ->
     [B, npoint, 3] (the reference returns ``index_points(xyz, centroids)``).
     """
     B, N, _ = xyz.shape
-    centroids = torch.zeros(B, npoint, dtype=torch.long)
-    distance = torch.ones(B, N) * 1e10
-    farthest = torch.randint(0, N, (B,), dtype=torch.long) if start is None else start.clone()
-    batch = torch.arange(B)
+    dev = xyz.device                     # device-agnostic: bench.py's gpu_baseline runs this same code on cuda
+    centroids = torch.zeros(B, npoint, dtype=torch.long, device=dev)
+    distance = torch.ones(B, N, device=dev) * 1e10
+    farthest = (torch.randint(0, N, (B,), dtype=torch.long) if start is None else start.clone()).to(dev)
+    batch = torch.arange(B, device=dev)
     for i in range(npoint):
         centroids[:, i] = farthest
         c = xyz[batch, farthest, :].view(B, 1, 3)
@@ -113,7 +114,7 @@ def knn_group(pts: torch.Tensor, center: torch.Tensor, k: int) -> torch.Tensor:
     d += torch.sum(center ** 2, -1).view(B, -1, 1)
     d += torch.sum(xyz ** 2, -1).view(B, 1, N)
     idx = torch.topk(d, k, dim=-1, largest=False, sorted=False)[1]           # [B,G,k]
-    bidx = torch.arange(B).view(B, 1, 1)
+    bidx = torch.arange(B, device=pts.device).view(B, 1, 1)
     nb = pts[bidx, idx, :]                                                    # [B,G,k,C]
     nb = torch.cat((nb[..., :3] - center.unsqueeze(2), nb[..., 3:]), dim=-1)
     return nb
@@ -187,7 +188,7 @@ class _Block(nn.Module):
         if self.drop_path == 0.0 or not self.training:
             return y
         keep = 1.0 - self.drop_path
-        r = torch.rand((y.shape[0], 1, 1), dtype=y.dtype) if u is None else u.reshape(-1, 1, 1).to(y.dtype)
+        r = torch.rand((y.shape[0], 1, 1), dtype=y.dtype, device=y.device) if u is None else u.reshape(-1, 1, 1).to(y.dtype)
         return y.div(keep) * (keep + r).floor()
 
     def forward(self, x, u=None):
@@ -255,7 +256,7 @@ class _RMSNorm(nn.Module):
 
 def rope_tables(head_dim: int, theta: float, positions: torch.Tensor):
     """HF LlamaRotaryEmbedding (modeling_llama.py:117-135): fp32 freqs, cat(freqs, freqs)."""
-    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32, device=positions.device) / head_dim))
     fr = positions.float()[:, None] * inv[None, :]
     emb = torch.cat((fr, fr), dim=-1)
     return emb.cos(), emb.sin()
@@ -364,7 +365,7 @@ class _Model(nn.Module):
                 if (ids == c.point_patch_token).sum() != n:
                     raise ValueError("The number of point patch tokens should be the same as the number of point patches.")
                 m = torch.where(ids == c.point_patch_token)[0]
-                if (m != torch.arange(m[0], m[0] + n)).any():
+                if (m != torch.arange(int(m[0]), int(m[0]) + n, device=m.device)).any():
                     raise ValueError("The point patch tokens should be consecutive.")
                 e = torch.cat((e[:m[0]], f, e[m[0] + n:]), dim=0)
             out.append(e)
@@ -378,10 +379,10 @@ class _Model(nn.Module):
             x = self.splice(input_ids, x, feats)
         B, Lq, _ = x.shape
         past = 0 if (cache is None or cache[0][0] is None) else cache[0][0].shape[2]
-        pos = torch.arange(past, past + Lq)                                        # HF :394-397
+        pos = torch.arange(past, past + Lq, device=x.device)                                        # HF :394-397
         cos, sin = rope_tables(self.c.hidden_size // self.c.num_heads, self.c.rope_theta, pos)
         Lk = past + Lq
-        causal = torch.arange(Lk)[None, :] <= pos[:, None]                         # [Lq,Lk]
+        causal = torch.arange(Lk, device=x.device)[None, :] <= pos[:, None]                         # [Lq,Lk]
         mask = causal[None, None]
         if attention_mask is not None:
             mask = mask & attention_mask.bool()[:, None, None, :Lk]
