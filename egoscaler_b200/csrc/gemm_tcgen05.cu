@@ -48,7 +48,24 @@ struct GemmParams {
     int raster_mode, group;
     uint64_t a_policy, b_policy;
     int c_stream;
+    // Fused epilogues (template parameter EPI; VERDICT r1 next #5 - the HBM-bound kernels that ran behind the GEMMs):
+    //   EPI_SWIGLU  : B = packed gate|up weight [2f, K]; a tile multiplies 128 gate rows AND the matching 128 up rows (two TMA
+    //                 boxes per stage), the epilogue writes act = silu(gate) * up [M, f] and, when C2 != null, gate|up [M, 2f]
+    //                 (kept for the backward) - replaces silu_mul_fwd (HF LlamaMLP, modeling_llama.py:171-184).
+    //   EPI_DSWIGLU : the d(act) = dOut . Wdown GEMM; the epilogue reads gate|up (aux) and writes d(gate|up) to C2 [M, 2f]
+    //                 without materialising d(act) - replaces silu_mul_bwd.
+    //   EPI_ROPE    : the q|k|v projection; heads of 128 columns below rope_cols get apply_rotary_pos_emb
+    //                 (modeling_llama.py:138-168) with the same bf16 rounding order as rope_kernel - replaces rope.
+    void* C2;
+    long long ldc2;
+    const __nv_bfloat16* aux;
+    long long ld_aux;
+    int f;
+    const __nv_bfloat16* cos_tab;
+    const __nv_bfloat16* sin_tab;
+    int rope_L, rope_pos0, rope_cols;
 };
+enum : int { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_DSWIGLU = 2, EPI_ROPE = 3 };
 
 ESB_DEVICE void tile_coords(const GemmParams& p, int t, int& tm, int& tn) {
     if (p.raster_mode == 0) {
@@ -78,10 +95,49 @@ struct GemmSmem {
     static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024;   // +1024 alignment slack
 };
 
-template <int BN>
+// bf16 stores of 32 consecutive columns of one row (vector path when aligned and complete)
+ESB_DEVICE void store_row32_bf16(__nv_bfloat16* cp, const uint32_t* packed, int ncols, bool vec_ok, int stream) {
+    if (vec_ok && ncols == 32) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint4 u = make_uint4(packed[g * 4 + 0], packed[g * 4 + 1], packed[g * 4 + 2], packed[g * 4 + 3]);
+            if (stream) __stcs(reinterpret_cast<uint4*>(cp) + g, u);
+            else reinterpret_cast<uint4*>(cp)[g] = u;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j < ncols) {
+                const uint32_t w = packed[j >> 1];
+                const unsigned short h = (j & 1) ? static_cast<unsigned short>(w >> 16) : static_cast<unsigned short>(w & 0xffffu);
+                cp[j] = __ushort_as_bfloat16(h);
+            }
+    }
+}
+// 32 consecutive bf16 columns of one row -> 16 packed words
+ESB_DEVICE void load_row32_bf16(const __nv_bfloat16* rp, uint32_t* packed, int ncols, bool vec_ok) {
+    if (vec_ok && ncols == 32) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + g);
+            packed[g * 4 + 0] = u.x; packed[g * 4 + 1] = u.y; packed[g * 4 + 2] = u.z; packed[g * 4 + 3] = u.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const unsigned short lo = (2 * j < ncols) ? __bfloat16_as_ushort(rp[2 * j]) : 0;
+            const unsigned short hi = (2 * j + 1 < ncols) ? __bfloat16_as_ushort(rp[2 * j + 1]) : 0;
+            packed[j] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+        }
+    }
+}
+
+template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const GemmParams p) {
+    static_assert(EPI == EPI_PLAIN || BN == 256, "fused epilogues are built on the 128x256 tile");
+    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;      // output columns per tile
     using S = GemmSmem<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -130,14 +186,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 int tm, tn;
                 tile_coords(p, t, tm, tn);
-                const int m0 = tm * BM, n0 = tn * BN;
+                const int m0 = tm * BM, n0 = tn * BN_OUT;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     uint8_t* sa = tiles + stage * S::STAGE_BYTES;
                     uint8_t* sb = sa + S::A_BYTES;
                     mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
                     tma_load_2d_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
-                    tma_load_2d_hint(sb, &tma_b, &full_bar[stage], kb * BK, n0, p.b_policy);
+                    if constexpr (EPI == EPI_SWIGLU) {
+                        // rows [n0, n0+128) of the gate half and the SAME rows of the up half (box = 128 rows): accumulator
+                        // columns [0,128) = gate, [128,256) = up of output columns n0..n0+127.  A gate box that runs past f
+                        // reads up rows (never stored: columns >= f are masked); an up box past 2f is zero-filled.
+                        tma_load_2d_hint(sb, &tma_b, &full_bar[stage], kb * BK, n0, p.b_policy);
+                        tma_load_2d_hint(sb + 128 * BK * 2, &tma_b, &full_bar[stage], kb * BK, p.f + n0, p.b_policy);
+                    } else {
+                        tma_load_2d_hint(sb, &tma_b, &full_bar[stage], kb * BK, n0, p.b_policy);
+                    }
                     if (++stage == S::STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -186,12 +250,115 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             int tm, tn;
             tile_coords(p, t, tm, tn);
-            const int m0 = tm * BM, n0 = tn * BN;
+            const int m0 = tm * BM, n0 = tn * BN_OUT;
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < p.M;
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+            if constexpr (EPI == EPI_SWIGLU) {
+                // act = bf16(bf16(silu(g)) * u) exactly like silu_mul_fwd_kernel on the bf16-rounded projections
+                __nv_bfloat16* act = reinterpret_cast<__nv_bfloat16*>(p.C);
+                __nv_bfloat16* gu = reinterpret_cast<__nv_bfloat16*>(p.C2);
+                const bool v_act = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(act) & 15) == 0);
+                const bool v_gu = gu && ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
+#pragma unroll 1
+                for (int c = 0; c < 4; ++c) {
+                    const int col0 = n0 + c * 32;
+                    if (col0 >= p.f) break;
+                    uint32_t rg[32], ru[32];
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), rg);
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(128 + c * 32), ru);
+                    tmem_ld_wait();
+                    const int ncols = min(32, p.f - col0);
+                    uint32_t pg[16], pu[16], pa[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        pg[j] = pack_bf16x2(__uint_as_float(rg[2 * j]), __uint_as_float(rg[2 * j + 1]));
+                        pu[j] = pack_bf16x2(__uint_as_float(ru[2 * j]), __uint_as_float(ru[2 * j + 1]));
+                        const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
+                        pa[j] = pack_bf16x2(bf16_round(silu(gv.x)) * uv.x, bf16_round(silu(gv.y)) * uv.y);
+                    }
+                    if (row_ok) {
+                        store_row32_bf16(act + static_cast<long long>(row) * p.ldc + col0, pa, ncols, v_act, 0);
+                        if (gu) {
+                            store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + col0, pg, ncols, v_gu, p.c_stream);
+                            store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + p.f + col0, pu, ncols, v_gu, p.c_stream);
+                        }
+                    }
+                }
+            } else if constexpr (EPI == EPI_DSWIGLU) {
+                // d(gate|up) from d(act) (this tile, rounded to bf16 like the materialised tensor was) and the saved gate|up:
+                // the arithmetic of silu_mul_bwd_kernel
+                const __nv_bfloat16* gu = p.aux;
+                __nv_bfloat16* dgu = reinterpret_cast<__nv_bfloat16*>(p.C2);
+                const bool v_in = ((p.ld_aux & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
+                const bool v_out = ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(dgu) & 15) == 0);
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    const int col0 = n0 + c * 32;
+                    if (col0 >= p.N) break;
+                    uint32_t r[32];
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
+                    tmem_ld_wait();
+                    const int ncols = min(32, p.N - col0);
+                    if (row_ok) {
+                        uint32_t pg[16], pu[16], og[16], ou[16];
+                        load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + col0, pg, ncols, v_in);
+                        load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + p.f + col0, pu, ncols, v_in);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
+                            const float2 dv = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])));
+                            const float s0 = 1.0f / (1.0f + __expf(-gv.x)), s1 = 1.0f / (1.0f + __expf(-gv.y));
+                            og[j] = pack_bf16x2(dv.x * uv.x * s0 * (1.0f + gv.x * (1.0f - s0)), dv.y * uv.y * s1 * (1.0f + gv.y * (1.0f - s1)));
+                            ou[j] = pack_bf16x2(dv.x * gv.x * s0, dv.y * gv.y * s1);
+                        }
+                        store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + col0, og, ncols, v_out, p.c_stream);
+                        store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + p.f + col0, ou, ncols, v_out, p.c_stream);
+                    }
+                }
+            } else if constexpr (EPI == EPI_ROPE) {
+                // two heads of 128 columns per tile; column j pairs with j + 64 (rotate_half)
+                __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C);
+                const bool v_out = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+                const int pos = p.rope_pos0 + (row_ok ? row % p.rope_L : 0);
+                const __nv_bfloat16* cp_ = p.cos_tab + static_cast<long long>(pos) * 64;
+                const __nv_bfloat16* sp_ = p.sin_tab + static_cast<long long>(pos) * 64;
+#pragma unroll 1
+                for (int hc = 0; hc < 4; ++hc) {                     // (head in tile, 32-column chunk of the first half)
+                    const int h = hc >> 1, c = hc & 1;
+                    const int head0 = n0 + h * 128;
+                    if (head0 >= p.N) break;
+                    uint32_t lo[32], hi[32];
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + c * 32), lo);
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + 64 + c * 32), hi);
+                    tmem_ld_wait();
+                    uint32_t o1[16], o2[16];
+                    const bool rot = head0 < p.rope_cols;
+                    uint32_t cw[16], sw[16];
+                    if (rot && row_ok) {
+                        load_row32_bf16(cp_ + c * 32, cw, 32, true);
+                        load_row32_bf16(sp_ + c * 32, sw, 32, true);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        o1[j] = pack_bf16x2(__uint_as_float(lo[2 * j]), __uint_as_float(lo[2 * j + 1]));
+                        o2[j] = pack_bf16x2(__uint_as_float(hi[2 * j]), __uint_as_float(hi[2 * j + 1]));
+                        if (rot && row_ok) {
+                            const float2 x1 = unpack_bf16x2(o1[j]), x2 = unpack_bf16x2(o2[j]);
+                            const float2 cc = unpack_bf16x2(cw[j]), ss = unpack_bf16x2(sw[j]);
+                            o1[j] = pack_bf16x2(bf16_round(x1.x * cc.x) - bf16_round(x2.x * ss.x), bf16_round(x1.y * cc.y) - bf16_round(x2.y * ss.y));
+                            o2[j] = pack_bf16x2(bf16_round(x2.x * cc.x) + bf16_round(x1.x * ss.x), bf16_round(x2.y * cc.y) + bf16_round(x1.y * ss.y));
+                        }
+                    }
+                    if (row_ok) {
+                        __nv_bfloat16* rp = out + static_cast<long long>(row) * p.ldc + head0 + c * 32;
+                        store_row32_bf16(rp, o1, 32, v_out, 0);
+                        store_row32_bf16(rp + 64, o2, 32, v_out, 0);
+                    }
+                }
+            } else {
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 const int col0 = n0 + c * 32;
@@ -276,6 +443,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                     }
                 }
             }
+            }   // EPI_PLAIN
             tc_fence_before();
             mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
@@ -348,12 +516,13 @@ int make_tma_3d_bf16(CUtensorMap* map, const void* ptr, long long cols, long lon
     return ESB_OK;
 }
 
-template <int BN>
+template <int BN, int EPI = EPI_PLAIN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
     using S = GemmSmem<BN>;
+    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
         if (e != cudaSuccess) {
             set_last_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e));
             return ESB_ERR_CUDA;
@@ -361,7 +530,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
         attr_set = true;
     }
     p.tiles_m = (p.M + BM - 1) / BM;
-    p.tiles_n = (p.N + BN - 1) / BN;
+    p.tiles_n = (p.N + BN_OUT - 1) / BN_OUT;
     const int tiles = p.tiles_m * p.tiles_n;
     // ---- tile walk: modelled DRAM bytes = persisting operand once + streamed operand once per group + C
     static const int hints = [] { const char* e = getenv("ESB_GEMM_L2_HINTS"); return e ? atoi(e) : 7; }();
@@ -369,7 +538,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     const double budget = budget_mb * (1 << 20);              // bytes of one operand group kept L2-resident (126 MB L2, two halves)
     const double a_panel = 2.0 * BM * p.K, b_panel = 2.0 * BN * p.K;
     const double a_bytes = a_panel * p.tiles_m, b_bytes = b_panel * p.tiles_n;
-    const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2);
+    const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2) * ((EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
     int gm = static_cast<int>(budget / a_panel);
     gm = gm < 1 ? 1 : (gm > p.tiles_m ? p.tiles_m : gm);
     const int groups_m = (p.tiles_m + gm - 1) / gm;
@@ -389,7 +558,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     p.b_policy = ((hints & 1) && p.raster_mode == 1 && persist_fits) ? kEvictLast : kEvictNormal;
     p.c_stream = ((hints & 2) && !p.out_fp32 && c_bytes >= 96.0 * (1 << 20)) ? 1 : 0;
     const int grid = tiles < sms ? tiles : sms;
-    gemm_bf16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
+    gemm_bf16_tcgen05_kernel<BN, EPI><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
     return check_launch("gemm_bf16_tcgen05");
 }
 
@@ -435,6 +604,8 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
     p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
     p.tiles_m = p.tiles_n = 0;
     p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;      // set by launch_gemm
+    p.C2 = nullptr; p.ldc2 = 0; p.aux = nullptr; p.ld_aux = 0; p.f = 0; p.cos_tab = p.sin_tab = nullptr;
+    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0;
     switch (bn) {
         case 256: return launch_gemm<256>(ta, tb, p, stream, sms);
         case 128: return launch_gemm<128>(ta, tb, p, stream, sms);
@@ -443,6 +614,76 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
             set_last_error("gemm_bf16: unsupported BN %d", bn);
             return ESB_ERR_INVALID_ARG;
     }
+}
+
+// ----------------------------------------------------------------------------- fused-epilogue entry points
+static int fused_common(GemmParams& p, const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, const char* who) {
+    if (K <= 0 || !A || !B) { set_last_error("%s: bad arguments (M=%d N=%d K=%d)", who, M, N, K); return ESB_ERR_INVALID_ARG; }
+    if ((lda & 7) || (ldb & 7) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) {
+        set_last_error("%s: A/B must be 16-byte aligned with leading dimensions that are multiples of 8", who);
+        return ESB_ERR_INVALID_ARG;
+    }
+    p.M = M; p.N = N; p.K = K; p.C = nullptr; p.ldc = 0; p.bias = nullptr; p.res = nullptr; p.ldr = 0;
+    p.act = 0; p.out_fp32 = 0; p.accumulate = 0; p.alpha = 1.0f; p.tiles_m = p.tiles_n = 0;
+    p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;
+    p.C2 = nullptr; p.ldc2 = 0; p.aux = nullptr; p.ld_aux = 0; p.f = 0; p.cos_tab = p.sin_tab = nullptr;
+    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0;
+    return ESB_OK;
+}
+
+// act [M, f] = silu(A . Wg^T) * (A . Wu^T), Wgu = [Wg ; Wu] packed [2f, K]; gu [M, 2f] optional (saved for the backward)
+int gemm_swiglu_bf16(const void* A, long long lda, const void* Wgu, long long ldw, void* act, long long ld_act, void* gu,
+                     long long ld_gu, int M, int f, int K, cudaStream_t stream) {
+    if (M <= 0 || f <= 0) return ESB_OK;
+    GemmParams p;
+    int rc = fused_common(p, A, lda, Wgu, ldw, M, f, K, "gemm_swiglu_bf16");
+    if (rc) return rc;
+    if (!act) { set_last_error("gemm_swiglu_bf16: act is null"); return ESB_ERR_INVALID_ARG; }
+    CUtensorMap ta, tb;
+    rc = make_tma_2d_bf16(&ta, A, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tma_2d_bf16(&tb, Wgu, 2LL * f, K, ldw, 128);
+    if (rc) return rc;
+    p.C = act; p.ldc = ld_act; p.C2 = gu; p.ldc2 = ld_gu; p.f = f;
+    return launch_gemm<256, EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());
+}
+
+// dgu [M, 2f] = dSwiGLU(gu, dOut . WdownT^T) with WdownT [f, K=d] (contraction-major copy of down_proj)
+int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long long ldb, const void* gu, long long ld_gu, void* dgu,
+                      long long ld_dgu, int M, int f, int K, cudaStream_t stream) {
+    if (M <= 0 || f <= 0) return ESB_OK;
+    GemmParams p;
+    int rc = fused_common(p, dOut, lda, WdownT, ldb, M, f, K, "gemm_dswiglu_bf16");
+    if (rc) return rc;
+    if (!gu || !dgu) { set_last_error("gemm_dswiglu_bf16: gu / dgu is null"); return ESB_ERR_INVALID_ARG; }
+    CUtensorMap ta, tb;
+    rc = make_tma_2d_bf16(&ta, dOut, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tma_2d_bf16(&tb, WdownT, f, K, ldb, 256);
+    if (rc) return rc;
+    p.aux = static_cast<const __nv_bfloat16*>(gu); p.ld_aux = ld_gu; p.C2 = dgu; p.ldc2 = ld_dgu; p.f = f;
+    return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
+}
+
+// C [M, N] = rope(A . W^T): heads of 128 columns starting below rope_cols are rotated at position pos0 + (row % L)
+int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                   const void* cos_tab, const void* sin_tab, int L, int pos0, int rope_cols, int head_dim, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return ESB_OK;
+    GemmParams p;
+    int rc = fused_common(p, A, lda, W, ldw, M, N, K, "gemm_rope_bf16");
+    if (rc) return rc;
+    if (head_dim != 128 || (N & 127) || (rope_cols & 127) || !C || !cos_tab || !sin_tab || L <= 0) {
+        set_last_error("gemm_rope_bf16: needs head_dim 128, N and rope_cols multiples of 128 (N=%d rope_cols=%d hd=%d)", N, rope_cols, head_dim);
+        return ESB_ERR_INVALID_ARG;
+    }
+    CUtensorMap ta, tb;
+    rc = make_tma_2d_bf16(&ta, A, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tma_2d_bf16(&tb, W, N, K, ldw, 256);
+    if (rc) return rc;
+    p.C = C; p.ldc = ldc; p.cos_tab = static_cast<const __nv_bfloat16*>(cos_tab); p.sin_tab = static_cast<const __nv_bfloat16*>(sin_tab);
+    p.rope_L = L; p.rope_pos0 = pos0; p.rope_cols = rope_cols;
+    return launch_gemm<256, EPI_ROPE>(ta, tb, p, stream, device_sm_count());
 }
 
 }  // namespace esb

@@ -140,11 +140,17 @@ class LlamaTrunk:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
             else:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps), None
+            roped = False
             if decode:
                 qkv = ops.gemm_skinny(xn, w.tqkv, weights_const=True)
+            elif ops.fuse_rope and cache is None and hd == 128 and x.shape[0] > ops.SKINNY_MAX_M:
+                qkv = ops.gemm_rope(xn, w.wqkv, self.cos, self.sin, L, pos0, 2 * d, hd)     # projection + RoPE in one launch
+                roped = True
             else:
                 qkv = ops.gemm(xn, w.wqkv)                                        # [T, 3d]
-            if cache is not None:
+            if roped:
+                pass
+            elif cache is not None:
                 ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
                           kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len, pos_ptr=pos_dev)
             else:
@@ -167,8 +173,11 @@ class LlamaTrunk:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps, want_rstd=True)
             else:
                 hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps), None
-            gu = ops.gemm_skinny(hn, w.tgu, weights_const=True) if decode else ops.gemm(hn, w.wgu)
-            a = ops.silu_mul(gu)
+            if not decode and ops.fuse_swiglu and x.shape[0] > ops.SKINNY_MAX_M:
+                a, gu = ops.gemm_swiglu(hn, w.wgu, want_gu=saved is not None)     # gate|up projection + SwiGLU in one launch
+            else:
+                gu = ops.gemm_skinny(hn, w.tgu, weights_const=True) if decode else ops.gemm(hn, w.wgu)
+                a = ops.silu_mul(gu)
             out = ops.gemm_skinny(a, w.tdown, residual=h, weights_const=True) if decode else ops.gemm(a, w.wdown, residual=h)
             if saved is not None:
                 saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu))
@@ -211,8 +220,11 @@ class LlamaTrunk:
         for li in reversed(range(len(self.layers))):
             w, s = self.layers[li], saved[li]
             w.ensure_transposed()
-            da = ops.gemm(dout, w.wdownT)                                         # [T, f]
-            dgu = ops.silu_mul_bwd(s.gu, da)                                      # [T, 2f]
+            if ops.fuse_dswiglu and dout.shape[0] > ops.SKINNY_MAX_M:
+                dgu = ops.gemm_dswiglu(dout, w.wdownT, s.gu)                      # [T, 2f]: d(act) GEMM + dSwiGLU, one launch
+            else:
+                da = ops.gemm(dout, w.wdownT)                                     # [T, f]
+                dgu = ops.silu_mul_bwd(s.gu, da)                                  # [T, 2f]
             dhn = ops.gemm(dgu, w.wguT)                                           # [T, d]
             if wgrad is not None:
                 hn = ops.rmsnorm(s.h, w.ln2, c.rms_norm_eps)

@@ -166,6 +166,62 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
     return out
 
 
+# Fused GEMM epilogues of the training / prefill step (llm.py switches on them).  Each one is bit-identical to the pair of
+# launches it replaces (tests/test_gemm_gpu.py), so they can be toggled for A/B timing without touching parity.
+fuse_swiglu = True        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
+fuse_dswiglu = True       # d(act) GEMM + dSwiGLU              (esb_gemm_dswiglu_bf16)
+fuse_rope = True          # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
+
+
+def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):
+    """a [M,K], wgu [2f,K] = [gate ; up] -> (act [M,f], gu [M,2f] or None)."""
+    _chk(a, torch.bfloat16, "gemm_swiglu.a"); _chk(wgu, torch.bfloat16, "gemm_swiglu.wgu")
+    assert a.dim() == 2 and wgu.dim() == 2 and a.shape[1] == wgu.shape[1] and a.stride(1) == 1 and wgu.stride(1) == 1
+    M, K = a.shape
+    f = wgu.shape[0] // 2
+    act = torch.empty(M, f, device=a.device, dtype=torch.bfloat16)
+    gu = torch.empty(M, 2 * f, device=a.device, dtype=torch.bfloat16) if want_gu else None
+    if gemm_timer is not None:
+        gemm_timer.before(M, 2 * f, K)
+    _l.call("esb_gemm_swiglu_bf16", a.data_ptr(), a.stride(0), wgu.data_ptr(), wgu.stride(0), act.data_ptr(), act.stride(0),
+            _p(gu), 0 if gu is None else gu.stride(0), M, f, K, _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
+    return act, gu
+
+
+def gemm_dswiglu(dout: torch.Tensor, wdownT: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    """dout [M,d], wdownT [f,d] (down_proj^T), gu [M,2f] -> dgu [M,2f] = dSwiGLU(gu, dout . down_proj)."""
+    _chk(dout, torch.bfloat16, "gemm_dswiglu.dout"); _chk(wdownT, torch.bfloat16, "gemm_dswiglu.wdownT"); _chk(gu, torch.bfloat16, "gemm_dswiglu.gu")
+    M, K = dout.shape
+    f = wdownT.shape[0]
+    assert wdownT.shape[1] == K and gu.shape == (M, 2 * f) and gu.stride(1) == 1 and dout.stride(1) == 1 and wdownT.stride(1) == 1
+    dgu = torch.empty(M, 2 * f, device=dout.device, dtype=torch.bfloat16)
+    if gemm_timer is not None:
+        gemm_timer.before(M, f, K)
+    _l.call("esb_gemm_dswiglu_bf16", dout.data_ptr(), dout.stride(0), wdownT.data_ptr(), wdownT.stride(0), gu.data_ptr(), gu.stride(0),
+            dgu.data_ptr(), dgu.stride(0), M, f, K, _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
+    return dgu
+
+
+def gemm_rope(a: torch.Tensor, w: torch.Tensor, cos_tab, sin_tab, L: int, pos0: int, rope_cols: int, hd: int) -> torch.Tensor:
+    """a [M,K] . w [N,K]^T with rotary embedding applied to the 128-wide heads below column ``rope_cols``."""
+    _chk(a, torch.bfloat16, "gemm_rope.a"); _chk(w, torch.bfloat16, "gemm_rope.w")
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and a.stride(1) == 1 and w.stride(1) == 1 and cos_tab.shape[1] == 64 and cos_tab.is_contiguous()
+    out = torch.empty(M, N, device=a.device, dtype=torch.bfloat16)
+    if gemm_timer is not None:
+        gemm_timer.before(M, N, K)
+    _l.call("esb_gemm_rope_bf16", a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), out.data_ptr(), out.stride(0), M, N, K,
+            cos_tab.data_ptr(), sin_tab.data_ptr(), int(L), int(pos0), int(rope_cols), int(hd), _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ trajectory tokens
 def traj_quantize(x: torch.Tensor, num_bins: int = 256, id_offset: int = 0) -> torch.Tensor:
     """utils/utils.py:13-16 ``discretize_action`` (+ ``id_offset``); x float32 or float64, any shape."""

@@ -160,3 +160,82 @@ def test_gemm_grouped_tile_walk(M, N, K):
     ref = _ref(a, w)
     assert bool(torch.isfinite(out).all())
     torch.testing.assert_close(out.float(), ref, atol=2e-2, rtol=1.6e-2)
+
+
+# ------------------------------------------------------------------ fused epilogues == the two launches they replace, bit for bit
+def _rnd(*shape, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, device="cuda", generator=g) * scale).bfloat16()
+
+
+@pytest.mark.parametrize("M,f,K", [(1392, 688, 256), (300, 128, 256), (77, 40, 64), (5568, 11008, 4096)])
+def test_gemm_swiglu_fused_equals_gemm_then_silu_mul(M, f, K):
+    """HF LlamaMLP gate|up projection + act_fn(gate) * up (modeling_llama.py:171-184); ragged f (688 = tiny config) and the
+    full-size launch of the benchmark."""
+    a = _rnd(M, K, seed=1)
+    wgu = _rnd(2 * f, K, seed=2, scale=K ** -0.5)
+    gu_ref = ops.gemm(a, wgu)
+    act_ref = ops.silu_mul(gu_ref)
+    act, gu = ops.gemm_swiglu(a, wgu, want_gu=True)
+    assert torch.equal(gu, gu_ref)
+    assert torch.equal(act, act_ref)
+    act2, none = ops.gemm_swiglu(a, wgu, want_gu=False)
+    assert none is None and torch.equal(act2, act_ref)
+    ref = torch.nn.functional.silu(a.float() @ wgu[:f].float().t()) * (a.float() @ wgu[f:].float().t())
+    assert (act.float() - ref).abs().max() <= 2e-2 * ref.abs().max()
+
+
+@pytest.mark.parametrize("M,f,K", [(1392, 688, 256), (77, 40, 64), (5568, 11008, 4096)])
+def test_gemm_dswiglu_fused_equals_gemm_then_silu_mul_bwd(M, f, K):
+    dout = _rnd(M, K, seed=3)
+    wdT = _rnd(f, K, seed=4, scale=K ** -0.5)
+    gu = _rnd(M, 2 * f, seed=5)
+    ref = ops.silu_mul_bwd(gu, ops.gemm(dout, wdT))
+    got = ops.gemm_dswiglu(dout, wdT, gu)
+    assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("B,L,H,K,pos0", [(2, 696, 2, 256, 0), (3, 77, 2, 256, 5), (8, 696, 32, 4096, 0)])
+def test_gemm_rope_fused_equals_gemm_then_rope(B, L, H, K, pos0):
+    """q|k|v projection + apply_rotary_pos_emb (modeling_llama.py:138-168) at head_dim 128: tiny-hd128 config and the
+    full-size launch (N = 12288)."""
+    from egoscaler_b200.llm import rope_tables
+    hd, d = 128, H * 128
+    cos, sin = rope_tables(hd, 10000.0, 1024, "cuda")
+    a = _rnd(B * L, K, seed=6)
+    w = _rnd(3 * d, K, seed=7, scale=K ** -0.5)
+    ref = ops.gemm(a, w)
+    ops.rope_(ref, L, 2 * H, hd, cos, sin, pos0)
+    got = ops.gemm_rope(a, w, cos, sin, L, pos0, 2 * d, hd)
+    assert torch.equal(got, ref)
+    assert torch.equal(got[:, 2 * d:], ops.gemm(a, w)[:, 2 * d:])             # v is not rotated
+
+
+def test_trunk_fused_and_unfused_paths_agree_bitwise():
+    """llm.LlamaTrunk forward + backward with every fused epilogue on vs off (ops.fuse_* switches): identical hidden states
+    and identical input gradients - the switches only change how many launches a layer takes."""
+    from egoscaler_b200 import synth
+    from egoscaler_b200.config import TrajVLMConfig
+    from egoscaler_b200.model import TrajPointLLMForCausalLM
+    cfg = TrajVLMConfig.tiny_hd128()
+    m = TrajPointLLMForCausalLM(cfg, "cuda")
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    B, L, d = 2, 200, cfg.hidden_size
+    x = _rnd(B * L, d, seed=8)
+    dout = _rnd(B * L, d, seed=9)
+    kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+    kmask[0, 90:97] = 0
+    res = {}
+    old = (ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope)
+    try:
+        for on in (False, True):
+            ops.fuse_swiglu = ops.fuse_dswiglu = ops.fuse_rope = on
+            saved = []
+            h = m.trunk.forward(x.clone(), B, L, kmask, saved=saved)
+            dx = m.trunk.backward(dout.clone(), B, L, kmask, saved)
+            h_inf = m.trunk.forward(x.clone(), B, L, kmask)                     # inference form (gu not kept)
+            res[on] = (h, dx, h_inf)
+    finally:
+        ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope = old
+    for a_, b_ in zip(res[False], res[True]):
+        assert torch.equal(a_, b_)
