@@ -99,6 +99,15 @@ int esb_attn_bwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64
     return attn_bwd(q, q_bs, q_rs, k, k_bs, k_rs, v, v_bs, v_rs, o, o_bs, o_rs, dout, do_bs, do_rs, lse, dvec, dq, dq_bs, dq_rs, dk,
                     dk_bs, dk_rs, dv, dv_bs, dv_rs, kmask, kmask_ld, B, H, Lq, Lk, hd, causal, q_pos0, scale, ST(stream));
 }
+int esb_attn_bwd_rope(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64_t k_bs, int64_t k_rs, const void* v,
+                      int64_t v_bs, int64_t v_rs, const void* o, int64_t o_bs, int64_t o_rs, const void* dout, int64_t do_bs,
+                      int64_t do_rs, const float* lse, float* dvec, void* dq, int64_t dq_bs, int64_t dq_rs, void* dk, int64_t dk_bs,
+                      int64_t dk_rs, void* dv, int64_t dv_bs, int64_t dv_rs, const uint8_t* kmask, int64_t kmask_ld, int B, int H,
+                      int Lq, int Lk, int hd, int causal, int q_pos0, float scale, const void* rope_cos, const void* rope_sin,
+                      void* stream) {
+    return attn_bwd(q, q_bs, q_rs, k, k_bs, k_rs, v, v_bs, v_rs, o, o_bs, o_rs, dout, do_bs, do_rs, lse, dvec, dq, dq_bs, dq_rs, dk,
+                    dk_bs, dk_rs, dv, dv_bs, dv_rs, kmask, kmask_ld, B, H, Lq, Lk, hd, causal, q_pos0, scale, ST(stream), rope_cos, rope_sin);
+}
 int esb_attn_decode(const void* q, int64_t q_bs, const void* k, const void* v, int64_t kv_bs, int64_t kv_rs, void* o,
                     int64_t o_bs, const uint8_t* kmask, int64_t kmask_ld, const int32_t* len_ptr, int len_static, int B,
                     int H, int hd, float scale, void* stream) {

@@ -39,7 +39,33 @@ struct BwdTcParams {
     long long dq_bs, dq_rs, dk_bs, dk_rs, dv_bs, dv_rs, kmask_ld;
     int H, Lq, Lqp, Lk, causal, q_pos0;
     float scale, scale_log2;
+    // not NULL: dq / dk leave the kernels already multiplied by the TRANSPOSED rotary embedding (the backward of
+    // apply_rotary_pos_emb, modeling_llama.py:138-168) - tables [max_pos, 64] bf16, same rounding order as rope_kernel(inverse)
+    const __nv_bfloat16 *rope_cos, *rope_sin;
 };
+
+// Backward of the rotary embedding on one row: x1 = 32 columns of the first half of the head, x2 = the paired 32 columns of the
+// second half (fp32 accumulators, scaled and rounded to bf16 first like the materialised gradient was), cs/sn = the 32 table
+// entries.  out1 = x1 cos + x2 sin, out2 = x2 cos - x1 sin with every product rounded to bf16 (rope_kernel, sign = -1).
+ESB_DEVICE void rope_bwd_store(__nv_bfloat16* g1, __nv_bfloat16* g2, const uint32_t* a1, const uint32_t* a2, float mul,
+                               const __nv_bfloat16* cs, const __nv_bfloat16* sn) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint4 cu = __ldg(reinterpret_cast<const uint4*>(cs) + g), su = __ldg(reinterpret_cast<const uint4*>(sn) + g);
+        const uint32_t cw[4] = {cu.x, cu.y, cu.z, cu.w}, sw[4] = {su.x, su.y, su.z, su.w};
+        uint32_t o1[4], o2[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 x1 = unpack_bf16x2(pack_bf16x2(__uint_as_float(a1[g * 8 + 2 * j]) * mul, __uint_as_float(a1[g * 8 + 2 * j + 1]) * mul));
+            const float2 x2 = unpack_bf16x2(pack_bf16x2(__uint_as_float(a2[g * 8 + 2 * j]) * mul, __uint_as_float(a2[g * 8 + 2 * j + 1]) * mul));
+            const float2 cc = unpack_bf16x2(cw[j]), ss = unpack_bf16x2(sw[j]);
+            o1[j] = pack_bf16x2(bf16_round(x1.x * cc.x) + bf16_round(x2.x * ss.x), bf16_round(x1.y * cc.y) + bf16_round(x2.y * ss.y));
+            o2[j] = pack_bf16x2(bf16_round(x2.x * cc.x) - bf16_round(x1.x * ss.x), bf16_round(x2.y * cc.y) - bf16_round(x1.y * ss.y));
+        }
+        *reinterpret_cast<uint4*>(g1 + g * 8) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+        *reinterpret_cast<uint4*>(g2 + g * 8) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+    }
+}
 
 ESB_DEVICE void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
@@ -280,6 +306,23 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
             tc_fence_after();
         }
         __nv_bfloat16* gp = p.dq + static_cast<long long>(b) * p.dq_bs + static_cast<long long>(qrow) * p.dq_rs + static_cast<long long>(h) * BT_HD + half * 64;
+        if (p.rope_cos) {
+            // fused inverse RoPE: this thread takes columns [32 half, +32) and their rotation partners [64 + 32 half, +32)
+            uint32_t a1[32], a2[32];
+            if (nblk > 0) {
+                tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(256 + half * 32), a1);
+                tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(256 + 64 + half * 32), a2);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) a1[i] = a2[i] = 0u;
+            }
+            if (qrow < p.Lq) {
+                __nv_bfloat16* g0 = gp - half * 64 + half * 32;
+                rope_bwd_store(g0, g0 + 64, a1, a2, p.scale, p.rope_cos + static_cast<long long>(qpos) * 64 + half * 32,
+                               p.rope_sin + static_cast<long long>(qpos) * 64 + half * 32);
+            }
+        } else {
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
             uint32_t acc[32];
@@ -301,6 +344,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                     *reinterpret_cast<uint4*>(gp + c * 32 + g * 8) = u;
                 }
             }
+        }
         }
     }
     tc_fence_before();
@@ -489,8 +533,24 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
         }
         __nv_bfloat16* gv = p.dv + static_cast<long long>(b) * p.dv_bs + static_cast<long long>(key) * p.dv_rs + static_cast<long long>(h) * BT_HD + half * 64;
         __nv_bfloat16* gk = p.dk + static_cast<long long>(b) * p.dk_bs + static_cast<long long>(key) * p.dk_rs + static_cast<long long>(h) * BT_HD + half * 64;
+        if (p.rope_cos) {
+            uint32_t a1[32], a2[32];
+            if (nq > 0) {
+                tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(384 + half * 32), a1);
+                tmem_ld_32x32(tmem_lane + static_cast<uint32_t>(384 + 64 + half * 32), a2);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) a1[i] = a2[i] = 0u;
+            }
+            if (key < p.Lk) {
+                __nv_bfloat16* g0 = gk - half * 64 + half * 32;
+                rope_bwd_store(g0, g0 + 64, a1, a2, p.scale, p.rope_cos + static_cast<long long>(key) * 64 + half * 32,
+                               p.rope_sin + static_cast<long long>(key) * 64 + half * 32);
+            }
+        }
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < (p.rope_cos ? 2 : 4); ++c) {
             const bool is_k = c >= 2;
             const float mul = is_k ? p.scale : 1.0f;
             uint32_t acc[32];
@@ -531,7 +591,8 @@ int attn_bwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k,
                    long long v_bs, long long v_rs, const void* o, long long o_bs, long long o_rs, const void* dout, long long do_bs,
                    long long do_rs, const float* lse, float* stats_ws, void* dq, long long dq_bs, long long dq_rs, void* dk,
                    long long dk_bs, long long dk_rs, void* dv, long long dv_bs, long long dv_rs, const uint8_t* kmask,
-                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s) {
+                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s,
+                   const void* rope_cos, const void* rope_sin) {
     if ((dq_rs & 7) || (dk_rs & 7) || (dv_rs & 7) || (dq_bs & 7) || (dk_bs & 7) || (dv_bs & 7) || (o_rs & 7) || (o_bs & 7) ||
         (do_rs & 7) || (do_bs & 7) || (reinterpret_cast<uintptr_t>(o) & 15) || (reinterpret_cast<uintptr_t>(dout) & 15) ||
         (reinterpret_cast<uintptr_t>(dq) & 15) || (reinterpret_cast<uintptr_t>(dk) & 15) || (reinterpret_cast<uintptr_t>(dv) & 15) ||
@@ -571,6 +632,7 @@ int attn_bwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k,
     p.dq = static_cast<__nv_bfloat16*>(dq); p.dk = static_cast<__nv_bfloat16*>(dk); p.dv = static_cast<__nv_bfloat16*>(dv);
     p.stats = stats; p.kmask = kmask;
     p.dq_bs = dq_bs; p.dq_rs = dq_rs; p.dk_bs = dk_bs; p.dk_rs = dk_rs; p.dv_bs = dv_bs; p.dv_rs = dv_rs; p.kmask_ld = kmask_ld;
+    p.rope_cos = static_cast<const __nv_bfloat16*>(rope_cos); p.rope_sin = static_cast<const __nv_bfloat16*>(rope_sin);
     p.H = H; p.Lq = Lq; p.Lqp = Lqp; p.Lk = Lk; p.causal = causal; p.q_pos0 = q_pos0; p.scale = scale; p.scale_log2 = scale * LOG2E;
     dim3 gkv((Lk + BT_TILE - 1) / BT_TILE, H, B);
     attn_bwd_dkdv_tc_kernel<<<gkv, BT_THREADS, KV_SMEM, s>>>(tq64, tdo64, tk128, tv128, p);

@@ -47,7 +47,8 @@ int attn_bwd_tc128(const void* q, long long q_bs, long long q_rs, const void* k,
                    long long v_bs, long long v_rs, const void* o, long long o_bs, long long o_rs, const void* dout, long long do_bs,
                    long long do_rs, const float* lse, float* stats_ws, void* dq, long long dq_bs, long long dq_rs, void* dk,
                    long long dk_bs, long long dk_rs, void* dv, long long dv_bs, long long dv_rs, const uint8_t* kmask,
-                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s);
+                   long long kmask_ld, int B, int H, int Lq, int Lk, int causal, int q_pos0, float scale, cudaStream_t s,
+                   const void* rope_cos = nullptr, const void* rope_sin = nullptr);
 
 int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* C, long long ldc, int M, int N, int K,
               const float* bias, const void* residual, long long ldr, int act, int out_fp32, int accumulate, float alpha,

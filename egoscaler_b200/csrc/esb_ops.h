@@ -86,7 +86,8 @@ int attn_bwd(const void* q, long long q_bs, long long q_rs, const void* k, long 
              long long v_bs, long long v_rs, const void* o, long long o_bs, long long o_rs, const void* dout, long long do_bs,
              long long do_rs, const float* lse, float* dvec, void* dq, long long dq_bs, long long dq_rs, void* dk, long long dk_bs,
              long long dk_rs, void* dv, long long dv_bs, long long dv_rs, const uint8_t* kmask, long long kmask_ld, int B, int H,
-             int Lq, int Lk, int hd, int causal, int q_pos0, float scale, cudaStream_t s);
+             int Lq, int Lk, int hd, int causal, int q_pos0, float scale, cudaStream_t s, const void* rope_cos = nullptr,
+             const void* rope_sin = nullptr);
 int attn_decode(const void* q, long long q_bs, const void* k, const void* v, long long kv_bs, long long kv_rs, void* o,
                 long long o_bs, const uint8_t* kmask, long long kmask_ld, const int* len_ptr, int len_static, int B, int H,
                 int hd, float scale, cudaStream_t s);

@@ -83,7 +83,7 @@ class _Lib:
 
 _lib = None
 # kernels launched per entry point (everything else launches exactly one); bench.py reports the total
-KERNELS_PER_CALL = {"esb_cross_entropy": 3, "esb_attn_bwd": 3, "esb_rgbd_to_points": 3}
+KERNELS_PER_CALL = {"esb_cross_entropy": 3, "esb_attn_bwd": 3, "esb_attn_bwd_rope": 3, "esb_rgbd_to_points": 3}
 launch_count = 0
 
 

@@ -235,9 +235,11 @@ class LlamaTrunk:
             else:
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout)
             do = ops.gemm(dh, w.woT)                                              # [T, d]
+            fused_bwd = ops.fuse_rope_bwd and hd == 128
             dqkv = ops.attention_bwd(s.qkv.view(B, L, 3, H, hd), s.o.view(B, L, d), s.lse, do.view(B, L, d), causal=True,
-                                     kmask=kmask)                                 # [T, 3d]
-            ops.rope_(dqkv.view(B * L, 3 * d), L, 2 * H, hd, self.cos, self.sin, 0, inverse=True)
+                                     kmask=kmask, rope=(self.cos, self.sin) if fused_bwd else None)      # [T, 3d]
+            if not fused_bwd:
+                ops.rope_(dqkv.view(B * L, 3 * d), L, 2 * H, hd, self.cos, self.sin, 0, inverse=True)
             dxn = ops.gemm(dqkv.view(B * L, 3 * d), w.wqkvT)
             if wgrad is not None:
                 xn = ops.rmsnorm(s.x, w.ln1, c.rms_norm_eps)

@@ -171,6 +171,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
 fuse_swiglu = True        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
 fuse_dswiglu = True       # d(act) GEMM + dSwiGLU              (esb_gemm_dswiglu_bf16)
 fuse_rope = True          # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
+fuse_rope_bwd = True      # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope; head_dim 128 only)
 
 
 def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):
@@ -550,7 +551,7 @@ def knn_group(pts: torch.Tensor, centers: torch.Tensor, K: int, out_ld: int = 64
 
 
 def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, causal: bool,
-                  kmask: Optional[torch.Tensor] = None, scale: Optional[float] = None) -> torch.Tensor:
+                  kmask: Optional[torch.Tensor] = None, scale: Optional[float] = None, rope=None) -> torch.Tensor:
     """Self-attention backward on a packed projection: qkv [B,L,3,H,hd], o/dout [B,L,H*hd], lse [B,H,L]
     -> dqkv [B,L,3,H,hd] (gradients w.r.t. the post-RoPE q,k and v)."""
     _chk(qkv, torch.bfloat16, "attention_bwd.qkv"); _chk(dout, torch.bfloat16, "attention_bwd.dout")
@@ -561,11 +562,17 @@ def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: t
     bs, rs = qkv.stride(0), qkv.stride(1)
     es = qkv.element_size()
     d = H * hd
-    _l.call("esb_attn_bwd", qkv.data_ptr(), bs, rs, qkv.data_ptr() + d * es, bs, rs, qkv.data_ptr() + 2 * d * es, bs, rs,
+    args = (qkv.data_ptr(), bs, rs, qkv.data_ptr() + d * es, bs, rs, qkv.data_ptr() + 2 * d * es, bs, rs,
             o.data_ptr(), o.stride(0), o.stride(1), dout.data_ptr(), dout.stride(0), dout.stride(1), lse.data_ptr(),
             dvec.data_ptr(), dqkv.data_ptr(), bs, rs, dqkv.data_ptr() + d * es, bs, rs, dqkv.data_ptr() + 2 * d * es, bs, rs,
             _p(kmask), 0 if kmask is None else kmask.stride(0), B, H, L, L, hd, 1 if causal else 0, 0,
-            float(scale if scale is not None else hd ** -0.5), _stream())
+            float(scale if scale is not None else hd ** -0.5))
+    if rope is None:
+        _l.call("esb_attn_bwd", *args, _stream())
+    else:                   # (cos, sin) tables: dq / dk come back w.r.t. the pre-rotation projections (fused inverse RoPE)
+        cos_tab, sin_tab = rope
+        assert hd == 128 and cos_tab.shape[1] == 64 and cos_tab.shape[0] >= L and cos_tab.is_contiguous() and sin_tab.is_contiguous()
+        _l.call("esb_attn_bwd_rope", *args, cos_tab.data_ptr(), sin_tab.data_ptr(), _stream())
     return dqkv
 
 

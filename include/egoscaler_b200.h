@@ -235,6 +235,15 @@ int esb_attn_bwd(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64
                  int64_t do_rs, const float* lse, float* dvec, void* dq, int64_t dq_bs, int64_t dq_rs, void* dk, int64_t dk_bs,
                  int64_t dk_rs, void* dv, int64_t dv_bs, int64_t dv_rs, const uint8_t* kmask, int64_t kmask_ld, int B, int H,
                  int Lq, int Lk, int hd, int causal, int q_pos0, float scale, void* stream);
+/* esb_attn_bwd with the backward of apply_rotary_pos_emb (modeling_llama.py:138-168) fused into the dq / dk epilogues: the
+ * gradients leave the kernels w.r.t. the PRE-rotation q and k (position q_pos0 + query index / key index); rope_cos / rope_sin
+ * [max_pos, 64] bf16; head_dim 128 only.  Bit-identical to esb_attn_bwd followed by esb_rope(inverse). */
+int esb_attn_bwd_rope(const void* q, int64_t q_bs, int64_t q_rs, const void* k, int64_t k_bs, int64_t k_rs, const void* v,
+                      int64_t v_bs, int64_t v_rs, const void* o, int64_t o_bs, int64_t o_rs, const void* dout, int64_t do_bs,
+                      int64_t do_rs, const float* lse, float* dvec, void* dq, int64_t dq_bs, int64_t dq_rs, void* dk, int64_t dk_bs,
+                      int64_t dk_rs, void* dv, int64_t dv_bs, int64_t dv_rs, const uint8_t* kmask, int64_t kmask_ld, int B, int H,
+                      int Lq, int Lk, int hd, int causal, int q_pos0, float scale, const void* rope_cos, const void* rope_sin,
+                      void* stream);
 /* One query token per sequence against the KV cache (the per-token step of generate, pointllm.py:255-275).
  * Context length = len_static + (*len_ptr when not NULL), so a captured graph follows a device-side counter. */
 int esb_attn_decode(const void* q, int64_t q_bs, const void* k, const void* v, int64_t kv_bs, int64_t kv_rs, void* o,

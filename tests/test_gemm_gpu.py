@@ -226,16 +226,34 @@ def test_trunk_fused_and_unfused_paths_agree_bitwise():
     kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
     kmask[0, 90:97] = 0
     res = {}
-    old = (ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope)
+    old = (ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope, ops.fuse_rope_bwd)
     try:
         for on in (False, True):
-            ops.fuse_swiglu = ops.fuse_dswiglu = ops.fuse_rope = on
+            ops.fuse_swiglu = ops.fuse_dswiglu = ops.fuse_rope = ops.fuse_rope_bwd = on
             saved = []
             h = m.trunk.forward(x.clone(), B, L, kmask, saved=saved)
             dx = m.trunk.backward(dout.clone(), B, L, kmask, saved)
             h_inf = m.trunk.forward(x.clone(), B, L, kmask)                     # inference form (gu not kept)
             res[on] = (h, dx, h_inf)
     finally:
-        ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope = old
+        ops.fuse_swiglu, ops.fuse_dswiglu, ops.fuse_rope, ops.fuse_rope_bwd = old
     for a_, b_ in zip(res[False], res[True]):
         assert torch.equal(a_, b_)
+
+
+@pytest.mark.parametrize("B,L,H", [(2, 200, 2), (1, 77, 3), (8, 696, 32)])
+def test_attention_bwd_fused_inverse_rope_equals_two_launches(B, L, H):
+    """Attention backward with the transposed rotary embedding fused into the dq / dk epilogues (esb_attn_bwd_rope) ==
+    esb_attn_bwd followed by esb_rope(inverse), bit for bit, incl. the benchmark's launch shape."""
+    from egoscaler_b200.llm import rope_tables
+    hd, d = 128, H * 128
+    cos, sin = rope_tables(hd, 10000.0, 1024, "cuda")
+    qkv = _rnd(B, L, 3, H, hd, seed=11)
+    do = _rnd(B, L, d, seed=12)
+    kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+    kmask[0, L // 2:L // 2 + 6] = 0
+    o, lse = ops.attention(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal=True, kmask=kmask, want_lse=True)
+    ref = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask)
+    ops.rope_(ref.view(B * L, 3 * d), L, 2 * H, hd, cos, sin, 0, inverse=True)
+    got = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask, rope=(cos, sin))
+    assert torch.equal(got, ref)
