@@ -394,6 +394,8 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
         if tr.dp.owns(u):
             got[f"unit{u}:{k}.{li}"] = tr.wgrad[k][li].clone()
     tr.zero_grad()
+    sparse = tr.sparse_embed_exchange
+    tr.sparse_embed_exchange = False                                      # local recomputation: plain local scatter, no exchange
     if tr.enc_train is not None:
         losses = [fb(r * b, (r + 1) * b, False) for r in range(world)]
         loss_ref = sum(float(x) for x in losses) / world
@@ -401,6 +403,7 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
     else:
         loss_ref = float(fb(0, b * world, False))
         ref_scale = float(world)                                          # global mean * world == sum of equal-count shard means
+    tr.sparse_embed_exchange = sparse
     worst, worst_name, n_cmp = 0.0, "", 0
     for name, g in got.items():
         if name.startswith("unit"):

@@ -57,26 +57,31 @@ def forward_hidden_train(model, tokens, attention_masks, pcrgbs, fps_start=None,
 
 def backward_from_hidden(model, ctx: TrainCtx, dh: torch.Tensor, grad: Dict[str, torch.Tensor],
                          wgrad: Optional[Dict[str, List[torch.Tensor]]] = None, on_layer_done: Optional[Callable] = None,
-                         on_ready: Optional[Callable[[List[str]], None]] = None):
+                         on_ready: Optional[Callable[[List[str]], None]] = None, embed_exchange: Optional[Callable] = None):
     """dh [B*L, d] bf16 = d loss / d hidden (before the final norm).  Accumulates fp32 gradients into ``grad`` (by parameter
     name: embed_tokens, point_proj.*, point_backbone.* when it trains) and ``wgrad`` (packed LLM-layer units, only with
     --unfreeze_language_model).  ``on_ready(names)`` is called as soon as a group of gradients is final (the trainer starts
-    its all-reduce there)."""
+    its all-reduce there).  ``embed_exchange(tokens, dx, splice_pos, n_point)``: when given, the embed_tokens gradient is NOT
+    scattered here - the callback owns it (the trainer's sparse exchange between data-parallel ranks) and the embedding is left
+    out of ``on_ready``."""
     cfg = model.cfg
     B, L, d = ctx.B, ctx.L, cfg.hidden_size
     n_point = model.point_backbone_config["point_token_len"]
     dx = model.trunk.backward(dh, B, L, ctx.kmask, ctx.saved, wgrad=wgrad, on_layer_done=on_layer_done)
     has_points = ctx.splice_pos is not None and len(ctx.proj_saved) > 0
     dfeats = torch.empty(B, n_point, d, device=dx.device, dtype=torch.bfloat16) if has_points else None
-    ops.embed_splice_bwd(ctx.tokens, dx, ctx.splice_pos if has_points else None, n_point, grad["model.embed_tokens.weight"], dfeats,
-                         cfg.pad_token_id)
+    ops.embed_splice_bwd(ctx.tokens, dx, ctx.splice_pos if has_points else None, n_point,
+                         None if embed_exchange is not None else grad["model.embed_tokens.weight"], dfeats, cfg.pad_token_id,
+                         vocab=cfg.vocab_size)
+    if embed_exchange is not None:
+        embed_exchange(ctx.tokens, dx, ctx.splice_pos if has_points else None, n_point)
     pw = [w for w, _ in model.projector_params()]
     pb = [b for _, b in model.projector_params()]
     if has_points:
         dtok = projector_backward(model._packed_proj, ctx.proj_saved, dfeats.view(B * n_point, d), [grad[n] for n in pw],
                                   [grad[n] for n in pb], need_input_grad=ctx.enc_saved is not None)
     if on_ready is not None:
-        on_ready(["model.embed_tokens.weight"] + pw + pb)
+        on_ready(([] if embed_exchange is not None else ["model.embed_tokens.weight"]) + pw + pb)
     if ctx.enc_saved is not None and has_points:
         from .encoder_train import train_backward
         train_backward(model.enc_train()["pk"], ctx.enc_saved, dtok, grad)

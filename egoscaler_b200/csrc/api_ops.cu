@@ -43,6 +43,14 @@ int esb_embed_splice_bwd(const int64_t* ids, const void* dx, const int32_t* spli
                          void* dfeats, int64_t padding_idx, int B, int L, int d, int64_t vocab_size, void* stream) {
     return embed_splice_bwd(CLLP(ids), dx, splice_pos, n_point, dembed, dfeats, padding_idx, B, L, d, vocab_size, ST(stream));
 }
+int esb_embed_rows_pack(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, int rmax, void* rows_out,
+                        int64_t* ids_out, int64_t pad_id, int B, int L, int d, void* stream) {
+    return embed_rows_pack(CLLP(ids), dx, splice_pos, n_point, rmax, rows_out, reinterpret_cast<long long*>(ids_out), pad_id, B, L, d, ST(stream));
+}
+int esb_embed_scatter_rows(const int64_t* ids, const void* rows, float* dembed, int64_t pad_id, int64_t vocab_size, int R, int d,
+                           void* stream) {
+    return embed_scatter_rows(CLLP(ids), rows, dembed, pad_id, vocab_size, R, d, ST(stream));
+}
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream) {
     return copy_rows(src, src_bstride_bytes, src_ld_bytes, dst, dst_bstride_bytes, dst_ld_bytes, batches, rows, row_bytes, ST(stream));

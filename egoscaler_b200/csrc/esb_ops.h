@@ -56,6 +56,9 @@ int embed_splice_fwd(const long long* ids, const void* embed, const void* feats,
                      int B, int L, int d, long long vocab, cudaStream_t s);
 int embed_splice_bwd(const long long* ids, const void* dx, const int* splice_pos, int n_point, float* dembed, void* dfeats,
                      long long padding_idx, int B, int L, int d, long long vocab, cudaStream_t s);
+int embed_rows_pack(const long long* ids, const void* dx, const int* splice_pos, int n_point, int rmax, void* rows_out,
+                    long long* ids_out, long long pad, int B, int L, int d, cudaStream_t s);
+int embed_scatter_rows(const long long* ids, const void* rows, float* dembed, long long pad, long long vocab, int R, int d, cudaStream_t s);
 int copy_rows(const void* src, long long src_bstride_bytes, long long src_ld_bytes, void* dst, long long dst_bstride_bytes,
               long long dst_ld_bytes, int batches, int rows, int row_bytes, cudaStream_t s);
 int transpose_bf16(const void* in, long long ld_in, void* out, long long ld_out, int R, int C, cudaStream_t s);

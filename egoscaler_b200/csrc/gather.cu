@@ -108,6 +108,73 @@ __global__ void __launch_bounds__(256) embed_splice_bwd_kernel(const long long* 
     }
 }
 
+// ---- sparse exchange of the embedding gradient (data-parallel training) -------------------------------
+// Only the rows of embed_tokens named by this step's token ids receive gradient (<= B * (L - n_point) of 32262 rows), so the
+// ranks exchange (token id, gradient row) pairs instead of all-reducing the dense [V, d] fp32 matrix.
+// pack: compact the non-point rows of dx [B, L, d] to rows_out [B * rmax, d] (+ their token ids; unused slots carry `pad`).
+__global__ void __launch_bounds__(128) embed_rows_pack_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ dx,
+                                                              const int* __restrict__ splice_pos, int n_point, int rmax,
+                                                              __nv_bfloat16* __restrict__ rows_out, long long* __restrict__ ids_out,
+                                                              long long pad, int B, int L, int d) {
+    const int r = blockIdx.x % rmax, b = blockIdx.x / rmax;
+    const int sp = splice_pos ? splice_pos[b] : -1;
+    const int l = (sp >= 0 && r >= sp) ? r + n_point : r;
+    const bool valid = l < L;
+    if (threadIdx.x == 0) ids_out[blockIdx.x] = valid ? ids[static_cast<long long>(b) * L + l] : pad;
+    uint4* dst = reinterpret_cast<uint4*>(rows_out + static_cast<long long>(blockIdx.x) * d);
+    const uint4* src = reinterpret_cast<const uint4*>(dx + (static_cast<long long>(b) * L + (valid ? l : 0)) * d);
+    for (int v = threadIdx.x; v < (d >> 3); v += blockDim.x) dst[v] = valid ? src[v] : make_uint4(0u, 0u, 0u, 0u);
+}
+// scatter: dembed[id, :] += sum of the rows k with ids[k] == id, added in INCREASING k.  One CTA column-slice per row j does the
+// work for its id iff j is the first occurrence; every rank runs this on the same all-gathered (ids, rows), so all ranks hold
+// bit-identical gradients (an atomicAdd scatter would not: its summation order differs from rank to rank).
+constexpr int SCATTER_MAX_ROWS = 1 << 16;
+__global__ void __launch_bounds__(128) embed_scatter_rows_kernel(const long long* __restrict__ ids, const __nv_bfloat16* __restrict__ rows,
+                                                                 float* __restrict__ dembed, long long pad, long long vocab, int R, int d) {
+    __shared__ uint32_t match[SCATTER_MAX_ROWS / 32];
+    __shared__ int dup;
+    const int j = blockIdx.x;
+    const long long id = ids[j];
+    if (id == pad || id < 0 || id >= vocab) return;
+    const int words = (R + 31) >> 5;
+    if (threadIdx.x == 0) dup = 0;
+    __syncthreads();
+    for (int w = threadIdx.x; w < words; w += blockDim.x) {
+        uint32_t bits = 0;
+        const int k0 = w << 5;
+#pragma unroll 4
+        for (int i = 0; i < 32; ++i) {
+            const int k = k0 + i;
+            if (k < R && ids[k] == id) bits |= 1u << i;
+        }
+        match[w] = bits;
+        if (k0 < j) {                                               // an earlier occurrence owns this id
+            const uint32_t below = (j - k0 >= 32) ? 0xffffffffu : ((1u << (j - k0)) - 1u);
+            if (bits & below) dup = 1;
+        }
+    }
+    __syncthreads();
+    if (dup) return;
+    const int c0 = (blockIdx.y * blockDim.x + threadIdx.x) * 8;      // 8 columns per thread
+    if (c0 >= d) return;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int w = j >> 5; w < words; ++w) {
+        uint32_t bits = match[w];
+        while (bits) {
+            const int k = (w << 5) + __ffs(bits) - 1;
+            bits &= bits - 1;
+            const uint4 u = *reinterpret_cast<const uint4*>(rows + static_cast<long long>(k) * d + c0);
+            const float2 a = unpack_bf16x2(u.x), b2 = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), e = unpack_bf16x2(u.w);
+            acc[0] += a.x; acc[1] += a.y; acc[2] += b2.x; acc[3] += b2.y; acc[4] += c.x; acc[5] += c.y; acc[6] += e.x; acc[7] += e.y;
+        }
+    }
+    float4* o = reinterpret_cast<float4*>(dembed + id * d + c0);
+    float4 o0 = o[0], o1 = o[1];
+    o0.x += acc[0]; o0.y += acc[1]; o0.z += acc[2]; o0.w += acc[3];
+    o1.x += acc[4]; o1.y += acc[5]; o1.z += acc[6]; o1.w += acc[7];
+    o[0] = o0; o[1] = o1;
+}
+
 // Batched row copy (16-byte vectors): dst[b, r, :ncols] = src[b, r, :ncols]; strides in elements of `elem_bytes`.
 __global__ void __launch_bounds__(256) copy_rows_kernel(const uint8_t* __restrict__ src, long long src_bstride, long long src_ld,
                                                         uint8_t* __restrict__ dst, long long dst_bstride, long long dst_ld,
@@ -202,6 +269,24 @@ int embed_splice_bwd(const long long* ids, const void* dx, const int* splice_pos
     embed_splice_bwd_kernel<<<g_grid(static_cast<long long>(B) * L * (d / 8), 256), 256, 0, s>>>(
         ids, static_cast<const __nv_bfloat16*>(dx), splice_pos, n_point, dembed, static_cast<__nv_bfloat16*>(dfeats), padding_idx, B, L, d, vocab);
     return check_launch("embed_splice_bwd");
+}
+int embed_rows_pack(const long long* ids, const void* dx, const int* splice_pos, int n_point, int rmax, void* rows_out,
+                    long long* ids_out, long long pad, int B, int L, int d, cudaStream_t s) {
+    if (B <= 0 || rmax <= 0) return ESB_OK;
+    if (d & 7) { set_last_error("embed_rows_pack: d must be a multiple of 8"); return ESB_ERR_INVALID_ARG; }
+    embed_rows_pack_kernel<<<B * rmax, 128, 0, s>>>(ids, static_cast<const __nv_bfloat16*>(dx), splice_pos, n_point, rmax,
+                                                    static_cast<__nv_bfloat16*>(rows_out), ids_out, pad, B, L, d);
+    return check_launch("embed_rows_pack");
+}
+int embed_scatter_rows(const long long* ids, const void* rows, float* dembed, long long pad, long long vocab, int R, int d, cudaStream_t s) {
+    if (R <= 0) return ESB_OK;
+    if ((d & 7) || R > SCATTER_MAX_ROWS) {
+        set_last_error("embed_scatter_rows: d must be a multiple of 8 and R <= %d (R=%d d=%d)", SCATTER_MAX_ROWS, R, d);
+        return ESB_ERR_INVALID_ARG;
+    }
+    dim3 grid(R, (d / 8 + 127) / 128);
+    embed_scatter_rows_kernel<<<grid, 128, 0, s>>>(ids, static_cast<const __nv_bfloat16*>(rows), dembed, pad, vocab, R, d);
+    return check_launch("embed_scatter_rows");
 }
 int copy_rows(const void* src, long long src_bstride_bytes, long long src_ld_bytes, void* dst, long long dst_bstride_bytes,
               long long dst_ld_bytes, int batches, int rows, int row_bytes, cudaStream_t s) {

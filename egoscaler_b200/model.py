@@ -302,6 +302,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         info_d = ops.point_layout(input_ids, c["point_patch_token"], c["point_start_token"], c["point_end_token"], n)
         info = info_d.cpu()
         pos = torch.full((input_ids.shape[0],), -1, dtype=torch.int32)
+        self.last_splice_all = False
         for b in range(input_ids.shape[0]):
             n_start, n_end, n_patch, first_start, end_ok, consecutive, first_patch = info[b, :7].tolist()
             if n_patch == 0:
@@ -320,6 +321,7 @@ class TrajPointLLMForCausalLM(ParamTree):
                 if not consecutive:
                     raise ValueError("The point patch tokens should be consecutive.")
                 pos[b] = first_patch
+        self.last_splice_all = bool((pos >= 0).all())       # host-side fact the trainer's sparse gradient exchange sizes its buffers by
         return pos.to(self.dev)
 
     @staticmethod

@@ -378,6 +378,27 @@ def embed_splice_bwd(ids, dx, splice_pos, n_point: int, dembed, dfeats, padding_
             B, L, d, int(vocab if vocab is not None else (dembed.shape[0] if dembed is not None else 1 << 62)), _stream())
 
 
+def embed_rows_pack(ids, dx, splice_pos, n_point: int, rmax: int, pad_id: int):
+    """Non-point rows of dx [B*L, d] -> (rows [B*rmax, d] bf16, ids [B*rmax] int64; unused slots carry pad_id)."""
+    ids = ids.contiguous()
+    B, L = ids.shape
+    d = dx.shape[-1]
+    assert dx.is_contiguous()
+    rows = torch.empty(B * rmax, d, device=dx.device, dtype=torch.bfloat16)
+    rid = torch.empty(B * rmax, device=dx.device, dtype=torch.int64)
+    _l.call("esb_embed_rows_pack", ids.data_ptr(), dx.data_ptr(), _p(splice_pos), n_point, rmax, rows.data_ptr(), rid.data_ptr(),
+            pad_id, B, L, d, _stream())
+    return rows, rid
+
+
+def embed_scatter_rows(ids: torch.Tensor, rows: torch.Tensor, dembed: torch.Tensor, pad_id: int):
+    """dembed[id] += sum of rows with that id, in increasing row order (deterministic; ids [R] int64, rows [R, d] bf16)."""
+    _chk(ids, torch.int64, "embed_scatter_rows.ids"); _chk(rows, torch.bfloat16, "embed_scatter_rows.rows"); _chk(dembed, torch.float32, "embed_scatter_rows.dembed")
+    assert ids.is_contiguous() and rows.is_contiguous() and dembed.is_contiguous() and rows.shape[0] == ids.numel()
+    _l.call("esb_embed_scatter_rows", ids.data_ptr(), rows.data_ptr(), dembed.data_ptr(), pad_id, dembed.shape[0], ids.numel(),
+            rows.shape[1], _stream())
+
+
 def copy_rows(src: torch.Tensor, dst: torch.Tensor):
     """dst[b, r, :] = src[b, r, :] for 3-D views whose last dim is contiguous (any batch/row strides)."""
     assert src.dim() == 3 and dst.shape == src.shape and src.stride(2) == 1 and dst.stride(2) == 1 and src.dtype == dst.dtype

@@ -72,6 +72,19 @@ class GradExchange:
         self._pending.append(self.dist.reduce(tensor, dst=self._global(self.owner(unit)), op=self.dist.ReduceOp.SUM,
                                               group=self.pg, async_op=True))
 
+    def all_gather(self, t: torch.Tensor) -> torch.Tensor:
+        """[world, *t.shape] with every rank's ``t`` (blocking; same shape on all ranks).  gloo cannot all-gather device
+        tensors: there the gather is an all-reduce of a zero-padded buffer (single-GPU two-process test path only)."""
+        if self.world == 1:
+            return t.unsqueeze(0)
+        out = torch.zeros((self.world,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+        if self._reduce_is_allreduce and t.is_cuda:
+            out[self.rank].copy_(t)
+            self.dist.all_reduce(out, op=self.dist.ReduceOp.SUM, group=self.pg)
+        else:
+            self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.pg)
+        return out
+
     def broadcast_from_owners(self, units: Sequence["tuple[int, torch.Tensor]"]) -> None:
         if self.world == 1:
             return

@@ -74,6 +74,9 @@ class Trainer:
         self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.last_loss: Optional[torch.Tensor] = None
         self._sync = world_size > 1
+        self.sparse_embed_exchange = True   # (id, row) all-gather + deterministic scatter instead of the dense embed_tokens all-reduce
+        self._exchange_rows = -1
+        self._embed_pending = []
 
     def _sync_initial_state(self):
         """What ``deepspeed.initialize`` does at train.py:119-125: every rank starts from rank 0's parameters and buffers
@@ -98,6 +101,7 @@ class Trainer:
             self.enc_train["pk"].refresh()
 
     def zero_grad(self):
+        self._embed_pending = []
         for g in self.grad.values():
             g.zero_()
         if self.wgrad is not None:
@@ -141,7 +145,8 @@ class Trainer:
         # ---- trunk backward (data gradients through the frozen layers), embedding scatter, projector, encoder
         backward_from_hidden(m, ctx, dh.view(B * L, d), self.grad, self.wgrad,
                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None,
-                             on_ready=self._reduce_async)
+                             on_ready=self._reduce_async,
+                             embed_exchange=self._embed_exchange if (self.world > 1 and self.sparse_embed_exchange) else None)
         self.last_loss = loss
         return loss
 
@@ -149,6 +154,37 @@ class Trainer:
     def _reduce_async(self, names: List[str]):
         if self._sync:
             self.dp.allreduce_async(self.grad[n] for n in names)
+
+    def _embed_exchange(self, tokens: torch.Tensor, dx: torch.Tensor, splice_pos, n_point: int):
+        """embed_tokens gradient of a data-parallel step WITHOUT the dense [V, d] fp32 all-reduce (528 MB at full size, issued
+        after the last backward kernel and therefore fully exposed): at most B * (L - n_point) rows are non-zero per rank, so
+        the ranks all-gather (token id, bf16 gradient row) pairs - 12 MB per rank - and every rank adds ALL of them into its
+        dense fp32 gradient with the deterministic scatter (esb_embed_scatter_rows): same summands in the same order on every
+        rank, hence bit-identical replicas.  Micro-batches run with ``sync=False`` only stash their pairs; the exchange of the
+        whole group happens on the synchronising micro-batch.  Assumes the collate_fn shapes (B, L) and the number of
+        micro-batches are equal on all ranks (dataset.py:150-194 pads to fixed lengths; checked once)."""
+        cfg = self.model.cfg
+        B, L = tokens.shape
+        all_spliced = splice_pos is not None and bool(self.model.last_splice_all)
+        rmax = L - n_point if all_spliced else L
+        self._embed_pending.append(ops.embed_rows_pack(tokens, dx, splice_pos, n_point, rmax, cfg.pad_token_id))
+        if not self._sync:
+            return
+        rows = torch.cat([r for r, _ in self._embed_pending]) if len(self._embed_pending) > 1 else self._embed_pending[0][0]
+        ids = torch.cat([i for _, i in self._embed_pending]) if len(self._embed_pending) > 1 else self._embed_pending[0][1]
+        self._embed_pending = []
+        if self._exchange_rows != rows.shape[0]:                    # first step / shape change: agree before a fixed-size gather
+            n = torch.tensor([rows.shape[0]], device=dx.device, dtype=torch.int64)
+            alln = self.dp.all_gather(n)
+            if not bool((alln == n).all()):
+                raise RuntimeError("sparse embedding-gradient exchange needs equal batch shapes and micro-batch counts on all "
+                                   f"ranks, got row counts {alln.flatten().tolist()} (set Trainer.sparse_embed_exchange = False)")
+            self._exchange_rows = rows.shape[0]
+        all_rows = self.dp.all_gather(rows).view(-1, rows.shape[1])
+        all_ids = self.dp.all_gather(ids).view(-1)
+        step = 1 << 16                                              # rows per deterministic scatter launch
+        for lo in range(0, all_ids.numel(), step):
+            ops.embed_scatter_rows(all_ids[lo:lo + step], all_rows[lo:lo + step], self.grad["model.embed_tokens.weight"], cfg.pad_token_id)
 
     def _reduce_layer_async(self, li: int):
         """ZeRO-1 gradient exchange of one LLM layer, started as soon as its backward has been queued: every unit is

@@ -173,6 +173,15 @@ int esb_embed_splice_fwd(const int64_t* ids, const void* embed, const void* feat
  * nn.Embedding(padding_idx) does). */
 int esb_embed_splice_bwd(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, float* dembed,
                          void* dfeats, int64_t padding_idx, int B, int L, int d, int64_t vocab_size, void* stream);
+/* Sparse exchange of the embed_tokens gradient between data-parallel ranks (replaces the dense [V,d] all-reduce DeepSpeed
+ * performs at train.py:183-184): esb_embed_rows_pack compacts the non-point rows of dx [B,L,d] into rows_out [B*rmax, d] bf16 with
+ * their token ids (ids_out [B*rmax]; unused slots = pad_id; rmax = L - n_point when every sample carries a point block, else L);
+ * after an all-gather, esb_embed_scatter_rows adds the rows of every id into dembed [V,d] fp32 in increasing row order - a
+ * deterministic reduction, so every rank ends with bit-identical gradients.  R <= 65536 rows per call. */
+int esb_embed_rows_pack(const int64_t* ids, const void* dx, const int32_t* splice_pos, int n_point, int rmax, void* rows_out,
+                        int64_t* ids_out, int64_t pad_id, int B, int L, int d, void* stream);
+int esb_embed_scatter_rows(const int64_t* ids, const void* rows, float* dembed, int64_t pad_id, int64_t vocab_size, int R, int d,
+                           void* stream);
 /* Batched strided row copy (logits slice train.py:174-175, hidden-row gathers); all byte strides multiples of 16. */
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream);

@@ -377,3 +377,49 @@ def test_group_maxpool_bwd_and_droppath():
     ref = x.float().view(B, L, d) + sc[:, None, None] * y.float().view(B, L, d)
     close(out.view(B, L, d), ref, 1e-2)
     close(ops.scale_rows_add(y, sc, L).view(B, L, d), sc[:, None, None] * y.float().view(B, L, d), 1e-2)
+
+
+def test_embed_rows_pack_and_deterministic_scatter():
+    """The sparse embedding-gradient exchange (trainer._embed_exchange): pack == the non-point rows in order; the deterministic
+    scatter == the atomicAdd scatter of esb_embed_splice_bwd up to fp32 summation order, is bit-reproducible, and skips pad /
+    out-of-range ids."""
+    B, L, d, Np, V = 3, 40, 64, 7, 500
+    g = torch.Generator(device="cuda").manual_seed(3)
+    ids = torch.randint(1, 30, (B, L), device="cuda", generator=g)             # few distinct ids: many duplicates
+    ids[:, -5:] = 0                                                              # pad tail
+    ids[1, 3] = V + 5                                                            # out of range: ignored
+    dx = rnd(B * L, d, seed=4)
+    pos = torch.tensor([2, 10, 5], device="cuda", dtype=torch.int32)
+    rows, rid = ops.embed_rows_pack(ids, dx, pos, Np, L - Np, 0)
+    for b in range(B):
+        keep = [l for l in range(L) if not (int(pos[b]) <= l < int(pos[b]) + Np)]
+        assert torch.equal(rows.view(B, L - Np, d)[b], dx.view(B, L, d)[b, keep])
+        assert torch.equal(rid.view(B, L - Np)[b], ids[b, keep])
+    ref = torch.zeros(V, d, device="cuda")
+    ops.embed_splice_bwd(ids, dx, pos, Np, ref, torch.empty(B, Np, d, device="cuda", dtype=torch.bfloat16), 0, vocab=V)
+    out1 = torch.zeros(V, d, device="cuda")
+    ops.embed_scatter_rows(rid, rows, out1, 0)
+    out2 = torch.zeros(V, d, device="cuda")
+    ops.embed_scatter_rows(rid, rows, out2, 0)
+    assert torch.equal(out1, out2)
+    torch.testing.assert_close(out1, ref, atol=1e-4, rtol=1e-5)
+    assert float(out1[0].abs().max()) == 0.0
+    exp = torch.zeros(V, d, device="cuda", dtype=torch.float64)
+    ok = (rid > 0) & (rid < V)
+    exp.index_add_(0, rid[ok], rows[ok].double())
+    torch.testing.assert_close(out1.double(), exp, atol=1e-4, rtol=1e-5)
+    # mixed batch (one sample without a point block): rmax = L, unused slots carry pad
+    pos2 = torch.tensor([2, -1, 5], device="cuda", dtype=torch.int32)
+    rows2, rid2 = ops.embed_rows_pack(ids, dx, pos2, Np, L, 0)
+    assert torch.equal(rows2.view(B, L, d)[1], dx.view(B, L, d)[1]) and torch.equal(rid2.view(B, L)[1], ids[1])
+    assert bool((rid2.view(B, L)[0, L - Np:] == 0).all()) and float(rows2.view(B, L, d)[0, L - Np:].abs().max()) == 0.0
+    # accumulate on top of existing content, and many rows (several bitmask words)
+    R = 5000
+    ridb = torch.randint(0, 64, (R,), device="cuda", generator=g)
+    rowsb = rnd(R, d, seed=6)
+    acc = torch.ones(V, d, device="cuda")
+    ops.embed_scatter_rows(ridb, rowsb, acc, 0)
+    expb = torch.ones(V, d, device="cuda", dtype=torch.float64)
+    okb = ridb > 0
+    expb.index_add_(0, ridb[okb], rowsb[okb].double())
+    torch.testing.assert_close(acc.double(), expb, atol=2e-3, rtol=1e-5)
