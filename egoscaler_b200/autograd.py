@@ -126,8 +126,8 @@ class TrajVLMFunction(torch.autograd.Function):
         dl = torch.zeros(B * L, model.v_pad, device=dev, dtype=torch.bfloat16)
         dl.view(B, L, model.v_pad)[:, :, :V].copy_(dlogits)
         dl2 = dl[:, :V]
-        ops.gemm(ops.transpose(dl2), ops.transpose(ctx.hn), out=grad["lm_head.weight"], accumulate=True)
-        dhn = ops.gemm(dl2, model.lm_head_T())
+        ops.gemm_tn(dl2, ctx.hn, out=grad["lm_head.weight"], accumulate=True)
+        dhn = ops.gemm_nn(dl2, model.lm_head.weight.detach()) if ops.gemm_nn_enabled else ops.gemm(dl2, model.lm_head_T())
         dh = ops.rmsnorm_bwd(dhn, ctx.h, model.model.norm.weight.detach(), ctx.rstd, dw=grad["model.norm.weight"])
         del dl, dl2, dhn
         backward_from_hidden(model, tctx, dh, grad, wgrad)

@@ -63,15 +63,19 @@ int esb_gemm_swiglu_bf16(const void* A, int64_t lda, const void* Wgu, int64_t ld
                          int64_t ld_gu, int M, int f, int K, void* stream) {
     return gemm_swiglu_bf16(A, lda, Wgu, ldw, act, ld_act, gu, ld_gu, M, f, K, ST(stream));
 }
-int esb_gemm_dswiglu_bf16(const void* dOut, int64_t lda, const void* WdownT, int64_t ldb, const void* gu, int64_t ld_gu,
+int esb_gemm_dswiglu_bf16(const void* dOut, int64_t lda, const void* Wd, int64_t ldb, int trans_b, const void* gu, int64_t ld_gu,
                           void* dgu, int64_t ld_dgu, int M, int f, int K, void* stream) {
-    return gemm_dswiglu_bf16(dOut, lda, WdownT, ldb, gu, ld_gu, dgu, ld_dgu, M, f, K, ST(stream));
+    return gemm_dswiglu_bf16(dOut, lda, Wd, ldb, trans_b, gu, ld_gu, dgu, ld_dgu, M, f, K, ST(stream));
 }
 int esb_gemm_rope_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                        const void* cos_tab, const void* sin_tab, int L, int pos0, int rope_cols, int head_dim, void* stream) {
     return gemm_rope_bf16(A, lda, W, ldw, C, ldc, M, N, K, cos_tab, sin_tab, L, pos0, rope_cols, head_dim, ST(stream));
 }
 
+int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t ldb, int trans_b, void* C, int64_t ldc, int M,
+                    int N, int Kc, int out_fp32, int accumulate, float alpha, void* stream) {
+    return gemm_t_bf16(A, lda, trans_a, B, ldb, trans_b, C, ldc, M, N, Kc, out_fp32, accumulate, alpha, ST(stream));
+}
 int64_t esb_gemm_skinny_workspace_bytes(int M, int N, int K) { return gemm_skinny_workspace_bytes(M, N, K); }
 int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                          const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,

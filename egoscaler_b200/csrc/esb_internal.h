@@ -56,11 +56,13 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
 
 int gemm_swiglu_bf16(const void* A, long long lda, const void* Wgu, long long ldw, void* act, long long ld_act, void* gu,
                      long long ld_gu, int M, int f, int K, cudaStream_t stream);
-int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long long ldb, const void* gu, long long ld_gu, void* dgu,
-                      long long ld_dgu, int M, int f, int K, cudaStream_t stream);
+int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long long ldb, int trans_b, const void* gu, long long ld_gu,
+                      void* dgu, long long ld_dgu, int M, int f, int K, cudaStream_t stream);
 int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
                    const void* cos_tab, const void* sin_tab, int L, int pos0, int rope_cols, int head_dim, cudaStream_t stream);
 
+int gemm_t_bf16(const void* A, long long lda, int trans_a, const void* B, long long ldb, int trans_b, void* C, long long ldc, int M,
+                int N, int Kc, int out_fp32, int accumulate, float alpha, cudaStream_t stream);
 long long gemm_skinny_workspace_bytes(int M, int N, int K);
 int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
                      const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,

@@ -132,11 +132,19 @@ ESB_DEVICE void load_row32_bf16(const __nv_bfloat16* rp, uint32_t* packed, int n
     }
 }
 
-template <int BN, int EPI>
+// TA / TB = true: that operand is stored with the CONTRACTION index outermost (A [Kc, M] / B [Kc, N] row-major) instead of
+// innermost.  TA & TB: C = A^T . B, the weight-gradient contraction dW = dY^T . X on the activations exactly as they sit in HBM;
+// TB only: C = A . B with B = a weight [in = Kc, out = N]... i.e. the data-gradient dX = dY . W on the state_dict layout - no
+// transposed copies either way.  Such an operand is staged as [64 contraction rows x 64 columns] TMA boxes (128-byte rows, 128B
+// swizzle) = an MN-major UMMA operand: the 64-wide column chunks of a tile lie 8 KB apart (LBO), 16 contraction rows (one MMA)
+// are 2 KB apart.
+template <int BN, int EPI, bool TA = false, bool TB = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const GemmParams p) {
     static_assert(EPI == EPI_PLAIN || BN == 256, "fused epilogues are built on the 128x256 tile");
+    static_assert(!TA || EPI == EPI_PLAIN, "a transposed A operand comes with the plain epilogue only");
+    static_assert(!TB || EPI == EPI_PLAIN || EPI == EPI_DSWIGLU, "a transposed B operand: plain or dSwiGLU epilogue");
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;      // output columns per tile
     using S = GemmSmem<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -192,8 +200,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                     uint8_t* sa = tiles + stage * S::STAGE_BYTES;
                     uint8_t* sb = sa + S::A_BYTES;
                     mbar_arrive_expect_tx(&full_bar[stage], S::STAGE_BYTES);
-                    tma_load_2d_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
-                    if constexpr (EPI == EPI_SWIGLU) {
+                    if constexpr (TA) {
+#pragma unroll
+                        for (int i = 0; i < BM / 64; ++i)
+                            tma_load_2d_hint(sa + i * 8192, &tma_a, &full_bar[stage], m0 + i * 64, kb * BK, p.a_policy);
+                    } else {
+                        tma_load_2d_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
+                    }
+                    if constexpr (TB) {
+#pragma unroll
+                        for (int i = 0; i < BN / 64; ++i)
+                            tma_load_2d_hint(sb + i * 8192, &tma_b, &full_bar[stage], n0 + i * 64, kb * BK, p.b_policy);
+                    } else if constexpr (EPI == EPI_SWIGLU) {
                         // rows [n0, n0+128) of the gate half and the SAME rows of the up half (box = 128 rows): accumulator
                         // columns [0,128) = gate, [128,256) = up of output columns n0..n0+127.  A gate box that runs past f
                         // reads up rows (never stored: columns >= f are masked); an up box past 2f is zero-filled.
@@ -209,7 +227,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     } else if (warp == 1) {
         if (lane == 0) {
             // ===================== MMA issuer
-            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN) | (TA ? (1u << 15) : 0u) | (TB ? (1u << 16) : 0u);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -223,13 +241,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                     tc_fence_after();
                     const uint32_t sa = smem_u32(tiles + stage * S::STAGE_BYTES);
                     const uint32_t sb = sa + S::A_BYTES;
-                    const uint64_t da = umma_desc_kmajor_sw128(sa);
-                    const uint64_t db = umma_desc_kmajor_sw128(sb);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
-                        // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
-                        umma_bf16_ss(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k), idesc,
-                                     (kb | k) != 0 ? 1u : 0u);
+                        // K-major operand: advance 16 bf16 = 32 B inside the 128 B swizzle row (+2 in the addr >> 4 field);
+                        // MN-major operand: 16 contraction rows = 2 KB further down the box
+                        const uint64_t da = TA ? umma_desc_mnmajor_sw128(sa + k * 2048, 8192)
+                                               : umma_desc_kmajor_sw128(sa) + static_cast<uint64_t>(2 * k);
+                        const uint64_t db = TB ? umma_desc_mnmajor_sw128(sb + k * 2048, 8192)
+                                               : umma_desc_kmajor_sw128(sb) + static_cast<uint64_t>(2 * k);
+                        umma_bf16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);       // smem slot reusable once these MMAs retire
                     if (++stage == S::STAGES) { stage = 0; phase ^= 1u; }
@@ -516,13 +536,13 @@ int make_tma_3d_bf16(CUtensorMap* map, const void* ptr, long long cols, long lon
     return ESB_OK;
 }
 
-template <int BN, int EPI = EPI_PLAIN>
+template <int BN, int EPI = EPI_PLAIN, bool TA = false, bool TB = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
     using S = GemmSmem<BN>;
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
         if (e != cudaSuccess) {
             set_last_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e));
             return ESB_ERR_CUDA;
@@ -558,7 +578,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     p.b_policy = ((hints & 1) && p.raster_mode == 1 && persist_fits) ? kEvictLast : kEvictNormal;
     p.c_stream = ((hints & 2) && !p.out_fp32 && c_bytes >= 96.0 * (1 << 20)) ? 1 : 0;
     const int grid = tiles < sms ? tiles : sms;
-    gemm_bf16_tcgen05_kernel<BN, EPI><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
+    gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
     return check_launch("gemm_bf16_tcgen05");
 }
 
@@ -648,9 +668,10 @@ int gemm_swiglu_bf16(const void* A, long long lda, const void* Wgu, long long ld
     return launch_gemm<256, EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());
 }
 
-// dgu [M, 2f] = dSwiGLU(gu, dOut . WdownT^T) with WdownT [f, K=d] (contraction-major copy of down_proj)
-int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long long ldb, const void* gu, long long ld_gu, void* dgu,
-                      long long ld_dgu, int M, int f, int K, cudaStream_t stream) {
+// dgu [M, 2f] = dSwiGLU(gu, dOut . Wdown) with the weight given either as WdownT [f, K=d] (contraction-major copy, trans_b = 0)
+// or as down_proj itself [K=d, f] (state_dict layout, trans_b = 1: MN-major B operand)
+int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long long ldb, int trans_b, const void* gu, long long ld_gu,
+                      void* dgu, long long ld_dgu, int M, int f, int K, cudaStream_t stream) {
     if (M <= 0 || f <= 0) return ESB_OK;
     GemmParams p;
     int rc = fused_common(p, dOut, lda, WdownT, ldb, M, f, K, "gemm_dswiglu_bf16");
@@ -659,9 +680,10 @@ int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long 
     CUtensorMap ta, tb;
     rc = make_tma_2d_bf16(&ta, dOut, M, K, lda, BM);
     if (rc) return rc;
-    rc = make_tma_2d_bf16(&tb, WdownT, f, K, ldb, 256);
+    rc = trans_b ? make_tma_2d_bf16(&tb, WdownT, K, f, ldb, 64) : make_tma_2d_bf16(&tb, WdownT, f, K, ldb, 256);
     if (rc) return rc;
     p.aux = static_cast<const __nv_bfloat16*>(gu); p.ld_aux = ld_gu; p.C2 = dgu; p.ldc2 = ld_dgu; p.f = f;
+    if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, device_sm_count());
     return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
 }
 
@@ -684,6 +706,39 @@ int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, v
     p.C = C; p.ldc = ldc; p.cos_tab = static_cast<const __nv_bfloat16*>(cos_tab); p.sin_tab = static_cast<const __nv_bfloat16*>(sin_tab);
     p.rope_L = L; p.rope_pos0 = pos0; p.rope_cols = rope_cols;
     return launch_gemm<256, EPI_ROPE>(ta, tb, p, stream, device_sm_count());
+}
+
+// C[M,N] (+)= alpha * op(A) . op(B): trans_a = 1: A is [Kc, M] row-major (else [M, Kc]); trans_b = 1: B is [Kc, N] row-major
+// (else [N, Kc], the state_dict layout the plain entry point takes).  trans_a = trans_b = 0 is gemm_bf16 itself.
+template <bool TA, bool TB>
+static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int M, int N, cudaStream_t stream) {
+    const int sms = device_sm_count();
+    const long long t256 = static_cast<long long>((M + BM - 1) / BM) * ((N + 255) / 256);
+    if (N > 128 && t256 >= sms / 2) return launch_gemm<256, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);
+    if (N > 64) return launch_gemm<128, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);
+    return launch_gemm<64, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);
+}
+int gemm_t_bf16(const void* A, long long lda, int trans_a, const void* B, long long ldb, int trans_b, void* C, long long ldc, int M,
+                int N, int Kc, int out_fp32, int accumulate, float alpha, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return ESB_OK;
+    if (!trans_a && !trans_b)
+        return gemm_bf16(A, lda, B, ldb, C, ldc, M, N, Kc, nullptr, nullptr, 0, 0, out_fp32, accumulate, alpha, 0, stream);
+    GemmParams p;
+    int rc = fused_common(p, A, lda, B, ldb, M, N, Kc, "gemm_t_bf16");
+    if (rc) return rc;
+    if (!C || (accumulate && !out_fp32)) { set_last_error("gemm_t_bf16: C is null or accumulate without fp32 output"); return ESB_ERR_INVALID_ARG; }
+    CUtensorMap ta, tb;
+    rc = trans_a ? make_tma_2d_bf16(&ta, A, Kc, M, lda, 64)     // rows = contraction index, box = 64 columns x 64 rows
+                 : make_tma_2d_bf16(&ta, A, M, Kc, lda, BM);
+    if (rc) return rc;
+    p.C = C; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
+    if (trans_b) {
+        rc = make_tma_2d_bf16(&tb, B, Kc, N, ldb, 64);
+        if (rc) return rc;
+        return trans_a ? launch_t<true, true>(ta, tb, p, M, N, stream) : launch_t<false, true>(ta, tb, p, M, N, stream);
+    }
+    set_last_error("gemm_t_bf16: trans_a without trans_b is not built (no call site)");
+    return ESB_ERR_UNSUPPORTED;
 }
 
 }  // namespace esb

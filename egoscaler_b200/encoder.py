@@ -151,7 +151,7 @@ def projector_backward(pp: PackedProjector, saved: list, dout: torch.Tensor, gra
                        grads_b: List[torch.Tensor], need_input_grad: bool = False) -> Optional[torch.Tensor]:
     """dout [R, d] bf16.  Accumulates fp32 dW / db into ``grads_w`` / ``grads_b``.  The gradient w.r.t. the encoder
     output is only computed (and returned) when the encoder trains (--unfreeze_pc_encoder)."""
-    wT = pp.transposed()
+    wT = None if ops.gemm_nn_enabled else pp.transposed()
     n = len(pp.w)
     dz = dout
     for i in reversed(range(n)):
@@ -160,7 +160,7 @@ def projector_backward(pp: PackedProjector, saved: list, dout: torch.Tensor, gra
             dz = ops.gelu_bwd(z, dz)
         ops.colsum(dz, grads_b[i])
         # dW[N,K] = dz^T [N,R] . x [R,K]  ->  A = dz^T (rows N, contraction R), B = x^T (rows K, contraction R)
-        ops.gemm(ops.transpose(dz), ops.transpose(x), out=grads_w[i], accumulate=True)
-        if i > 0 or need_input_grad:
-            dz = ops.gemm(dz, wT[i])          # dx[R,K] = dz[R,N] . W[N,K] ; wT is [K,N] (contraction-major)
+        ops.gemm_tn(dz, x, out=grads_w[i], accumulate=True)
+        if i > 0 or need_input_grad:          # dx[R,K] = dz[R,N] . W[N,K]
+            dz = ops.gemm_nn(dz, pp.w[i].detach()) if wT is None else ops.gemm(dz, wT[i])
     return dz if need_input_grad else None

@@ -169,7 +169,7 @@ def _wgrad(dz: torch.Tensor, x: torch.Tensor, gw: torch.Tensor, gb: Optional[tor
     """Linear / Conv1d(k=1) parameter gradients, fp32-accumulated: gW[N,K] += dz^T . x ; gb[N] += column sums of dz."""
     if gb is not None:
         ops.colsum(dz, gb)
-    ops.gemm(ops.transpose(dz), ops.transpose(x), out=gw, accumulate=True)
+    ops.gemm_tn(dz, x, out=gw, accumulate=True)
 
 
 def _wgrad_padded(dz: torch.Tensor, xpad: torch.Tensor, gw: torch.Tensor, gb: torch.Tensor):
@@ -193,7 +193,6 @@ def train_backward(pk: TrainPointEncoder, sv: dict, dout: torch.Tensor, grads: D
     gr2 = lambda n: grads[PRE + n].view(grads[PRE + n].shape[0], -1)          # conv [out, in, 1] -> [out, in]
     scales = sv["scales"]
     dx = ops.layernorm_bwd(dout, sv["x_final"], pk.norm_g, dgamma=gr("norm.weight"), dbeta=gr("norm.bias"))
-    pos2_wT = ops.transpose(pk.pos2_w)
     for j in reversed(range(len(pk.blocks))):
         blk, s = pk.blocks[j], sv["blocks"][j]
         b = f"blocks.blocks.{j}."
@@ -201,19 +200,19 @@ def train_backward(pk: TrainPointEncoder, sv: dict, dout: torch.Tensor, grads: D
         # ---- MLP branch: x = x1 + s_m * fc2(gelu(fc1(LN2(x1))))
         dbr2 = ops.scale_rows_add(dx, scales[j, 1], Np) if drop else dx
         _wgrad(dbr2, s["hmid"], gr(b + "mlp.fc2.weight"), gr(b + "mlp.fc2.bias"))
-        dh = ops.gemm(dbr2, ops.transpose(blk["fc2_w"]))
+        dh = ops.gemm_nn(dbr2, blk["fc2_w"])
         dz = ops.gelu_bwd(s["z"], dh)
         _wgrad(dz, s["y2"], gr(b + "mlp.fc1.weight"), gr(b + "mlp.fc1.bias"))
-        dy2 = ops.gemm(dz, ops.transpose(blk["fc1_w"]))
+        dy2 = ops.gemm_nn(dz, blk["fc1_w"])
         dx1 = ops.layernorm_bwd(dy2, s["x1"], blk["n2_g"], dgamma=gr(b + "norm2.weight"), dbeta=gr(b + "norm2.bias"), dres=dx)
         # ---- attention branch: x1 = xin + s_a * proj(attn(LN1(xin)))
         dbr = ops.scale_rows_add(dx1, scales[j, 0], Np) if drop else dx1
         o2 = s["o"].view(B * Np, T)
         _wgrad(dbr, o2, gr(b + "attn.proj.weight"), gr(b + "attn.proj.bias"))
-        do = ops.gemm(dbr, ops.transpose(blk["proj_w"]))
+        do = ops.gemm_nn(dbr, blk["proj_w"])
         dqkv = ops.attention_bwd(s["qkv"], s["o"], s["lse"], do.view(B, Np, T), causal=False).view(B * Np, 3 * T)
         _wgrad(dqkv, s["y"], gr(b + "attn.qkv.weight"), None)
-        dy = ops.gemm(dqkv, ops.transpose(blk["qkv_w"]))
+        dy = ops.gemm_nn(dqkv, blk["qkv_w"])
         dxin = ops.layernorm_bwd(dy, s["xin"], blk["n1_g"], dgamma=gr(b + "norm1.weight"), dbeta=gr(b + "norm1.bias"), dres=dx1)
         # ---- xin = x + pos: the same gradient flows to the previous block and (summed over blocks) to pos.  The pos path is
         # linear in its output gradient, so each block's share is pushed through it right away (no fp32 staging buffer).
@@ -223,7 +222,7 @@ def train_backward(pk: TrainPointEncoder, sv: dict, dout: torch.Tensor, grads: D
         ops.copy_rows(d3[:, 1:, :], dpe)
         dpe2 = dpe.view(B * G, T)
         _wgrad(dpe2, sv["gpe"], gr("pos_embed.2.weight"), gr("pos_embed.2.bias"))
-        dzpe = ops.gelu_bwd(sv["zpe"], ops.gemm(dpe2, pos2_wT))
+        dzpe = ops.gelu_bwd(sv["zpe"], ops.gemm_nn(dpe2, pk.pos2_w))
         _wgrad_padded(dzpe, sv["cpad"], gr("pos_embed.0.weight"), gr("pos_embed.0.bias"))
         dx = dxin
         sv["blocks"][j] = None
@@ -234,18 +233,18 @@ def train_backward(pk: TrainPointEncoder, sv: dict, dout: torch.Tensor, grads: D
     ops.copy_rows(d3[:, 1:, :], dt)
     dt2 = dt.view(B * G, T)
     _wgrad(dt2, sv["tok"], gr("reduce_dim.weight"), gr("reduce_dim.bias"))
-    dtok = ops.gemm(dt2, ops.transpose(pk.red_w))
+    dtok = ops.gemm_nn(dt2, pk.red_w)
     # ---- mini-PointNet backward (dvae.py:207-221)
     df2 = ops.group_maxpool_bwd(sv["f2"], K, dpool=dtok)
     y3 = sv["bn3"][1]
     _wgrad(df2, y3, gr2("encoder.second_conv.3.weight"), gr("encoder.second_conv.3.bias"))
-    dy3 = ops.gemm(df2, ops.transpose(pk.c4_w))
+    dy3 = ops.gemm_nn(df2, pk.c4_w)
     dz3 = _bn_train_bwd(dy3, pk.bn["bn3"], sv["bn3"], gr("encoder.second_conv.1.weight"), gr("encoder.second_conv.1.bias"))
     _wgrad(dz3, sv["cat"], gr2("encoder.second_conv.0.weight"), gr("encoder.second_conv.0.bias"))
-    dcat = ops.gemm(dz3, ops.transpose(pk.c3_w))
+    dcat = ops.gemm_nn(dz3, pk.c3_w)
     df1 = ops.group_maxpool_bwd(sv["f1"], K, dcat=dcat)
     y1 = sv["bn1"][1]
     _wgrad(df1, y1, gr2("encoder.first_conv.3.weight"), gr("encoder.first_conv.3.bias"))
-    dy1 = ops.gemm(df1, ops.transpose(pk.c2_w))
+    dy1 = ops.gemm_nn(df1, pk.c2_w)
     dz1 = _bn_train_bwd(dy1, pk.bn["bn1"], sv["bn1"], gr("encoder.first_conv.1.weight"), gr("encoder.first_conv.1.bias"))
     _wgrad_padded(dz1, sv["nb"], gr2("encoder.first_conv.0.weight"), gr("encoder.first_conv.0.bias"))

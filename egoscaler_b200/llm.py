@@ -217,34 +217,41 @@ class LlamaTrunk:
         gradients flow.  ``wgrad`` (fp32 accumulators per layer) enables the --unfreeze_language_model path."""
         c = self.cfg
         d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
+        # Trainable trunk (--unfreeze_language_model): the weights change every step, so the data gradients read them in their
+        # [out, in] layout through the NN GEMM instead of maintaining 13.5 GB of contraction-major copies (and re-transposing
+        # them after every optimizer step); the weight gradients dY^T . X read the token-major activations through the TN GEMM.
+        nn_dgrad = wgrad is not None and ops.gemm_nn_enabled
         for li in reversed(range(len(self.layers))):
             w, s = self.layers[li], saved[li]
-            w.ensure_transposed()
+            if not nn_dgrad:
+                w.ensure_transposed()
             if ops.fuse_dswiglu and dout.shape[0] > ops.SKINNY_MAX_M:
-                dgu = ops.gemm_dswiglu(dout, w.wdownT, s.gu)                      # [T, 2f]: d(act) GEMM + dSwiGLU, one launch
+                # [T, 2f]: d(act) GEMM + dSwiGLU, one launch
+                dgu = ops.gemm_dswiglu(dout, w.wdown, s.gu, w_is_down_proj=True) if nn_dgrad else ops.gemm_dswiglu(dout, w.wdownT, s.gu)
             else:
-                da = ops.gemm(dout, w.wdownT)                                     # [T, f]
+                da = ops.gemm_nn(dout, w.wdown) if nn_dgrad else ops.gemm(dout, w.wdownT)     # [T, f]
                 dgu = ops.silu_mul_bwd(s.gu, da)                                  # [T, 2f]
-            dhn = ops.gemm(dgu, w.wguT)                                           # [T, d]
+            dhn = ops.gemm_nn(dgu, w.wgu) if nn_dgrad else ops.gemm(dgu, w.wguT)   # [T, d]
             if wgrad is not None:
                 hn = ops.rmsnorm(s.h, w.ln2, c.rms_norm_eps)
                 a = ops.silu_mul(s.gu)
-                ops.gemm(ops.transpose(dout), ops.transpose(a), out=wgrad["wdown"][li], accumulate=True)
-                ops.gemm(ops.transpose(dgu), ops.transpose(hn), out=wgrad["wgu"][li], accumulate=True)
+                ops.gemm_tn(dout, a, out=wgrad["wdown"][li], accumulate=True)
+                ops.gemm_tn(dgu, hn, out=wgrad["wgu"][li], accumulate=True)
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout, dw=wgrad["ln2"][li])
             else:
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout)
-            do = ops.gemm(dh, w.woT)                                              # [T, d]
+            do = ops.gemm_nn(dh, w.wo) if nn_dgrad else ops.gemm(dh, w.woT)       # [T, d]
             fused_bwd = ops.fuse_rope_bwd and hd == 128
             dqkv = ops.attention_bwd(s.qkv.view(B, L, 3, H, hd), s.o.view(B, L, d), s.lse, do.view(B, L, d), causal=True,
                                      kmask=kmask, rope=(self.cos, self.sin) if fused_bwd else None)      # [T, 3d]
             if not fused_bwd:
                 ops.rope_(dqkv.view(B * L, 3 * d), L, 2 * H, hd, self.cos, self.sin, 0, inverse=True)
-            dxn = ops.gemm(dqkv.view(B * L, 3 * d), w.wqkvT)
+            dqkv2 = dqkv.view(B * L, 3 * d)
+            dxn = ops.gemm_nn(dqkv2, w.wqkv) if nn_dgrad else ops.gemm(dqkv2, w.wqkvT)
             if wgrad is not None:
                 xn = ops.rmsnorm(s.x, w.ln1, c.rms_norm_eps)
-                ops.gemm(ops.transpose(dh), ops.transpose(s.o), out=wgrad["wo"][li], accumulate=True)
-                ops.gemm(ops.transpose(dqkv.view(B * L, 3 * d)), ops.transpose(xn), out=wgrad["wqkv"][li], accumulate=True)
+                ops.gemm_tn(dh, s.o, out=wgrad["wo"][li], accumulate=True)
+                ops.gemm_tn(dqkv2, xn, out=wgrad["wqkv"][li], accumulate=True)
                 dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh, dw=wgrad["ln1"][li])
             else:
                 dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh)

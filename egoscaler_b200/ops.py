@@ -191,17 +191,19 @@ def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):
     return act, gu
 
 
-def gemm_dswiglu(dout: torch.Tensor, wdownT: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
-    """dout [M,d], wdownT [f,d] (down_proj^T), gu [M,2f] -> dgu [M,2f] = dSwiGLU(gu, dout . down_proj)."""
-    _chk(dout, torch.bfloat16, "gemm_dswiglu.dout"); _chk(wdownT, torch.bfloat16, "gemm_dswiglu.wdownT"); _chk(gu, torch.bfloat16, "gemm_dswiglu.gu")
+def gemm_dswiglu(dout: torch.Tensor, wd: torch.Tensor, gu: torch.Tensor, w_is_down_proj: bool = False) -> torch.Tensor:
+    """dout [M,d], gu [M,2f] -> dgu [M,2f] = dSwiGLU(gu, dout . down_proj).  ``wd`` = down_proj^T [f,d], or with
+    ``w_is_down_proj`` the parameter itself [d,f] (no contraction-major copy needed)."""
+    _chk(dout, torch.bfloat16, "gemm_dswiglu.dout"); _chk(wd, torch.bfloat16, "gemm_dswiglu.wd"); _chk(gu, torch.bfloat16, "gemm_dswiglu.gu")
     M, K = dout.shape
-    f = wdownT.shape[0]
-    assert wdownT.shape[1] == K and gu.shape == (M, 2 * f) and gu.stride(1) == 1 and dout.stride(1) == 1 and wdownT.stride(1) == 1
+    f = wd.shape[1] if w_is_down_proj else wd.shape[0]
+    assert wd.shape == ((K, f) if w_is_down_proj else (f, K)) and gu.shape == (M, 2 * f)
+    assert gu.stride(1) == 1 and dout.stride(1) == 1 and wd.stride(1) == 1
     dgu = torch.empty(M, 2 * f, device=dout.device, dtype=torch.bfloat16)
     if gemm_timer is not None:
         gemm_timer.before(M, f, K)
-    _l.call("esb_gemm_dswiglu_bf16", dout.data_ptr(), dout.stride(0), wdownT.data_ptr(), wdownT.stride(0), gu.data_ptr(), gu.stride(0),
-            dgu.data_ptr(), dgu.stride(0), M, f, K, _stream())
+    _l.call("esb_gemm_dswiglu_bf16", dout.data_ptr(), dout.stride(0), wd.data_ptr(), wd.stride(0), 1 if w_is_down_proj else 0,
+            gu.data_ptr(), gu.stride(0), dgu.data_ptr(), dgu.stride(0), M, f, K, _stream())
     if gemm_timer is not None:
         gemm_timer.after()
     return dgu
@@ -221,6 +223,44 @@ def gemm_rope(a: torch.Tensor, w: torch.Tensor, cos_tab, sin_tab, L: int, pos0: 
     if gemm_timer is not None:
         gemm_timer.after()
     return out
+
+
+gemm_tn_enabled = True    # weight gradients dY^T . X through the TN tcgen05 GEMM (no transposed activation copies)
+gemm_nn_enabled = True    # data gradients dY . W on the [out, in] weight itself (no contraction-major weight copies)
+
+
+def _gemm_t(a, trans_a, b, trans_b, M, N, Kc, out, out_dtype, accumulate, alpha):
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=out_dtype)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    if gemm_timer is not None:
+        gemm_timer.before(M, N, Kc)
+    _l.call("esb_gemm_t_bf16", a.data_ptr(), a.stride(0), 1 if trans_a else 0, b.data_ptr(), b.stride(0), 1 if trans_b else 0,
+            out.data_ptr(), out.stride(0), M, N, Kc, 1 if out.dtype == torch.float32 else 0, 1 if accumulate else 0, float(alpha), _stream())
+    if gemm_timer is not None:
+        gemm_timer.after()
+    return out
+
+
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.float32,
+            accumulate: bool = False, alpha: float = 1.0) -> torch.Tensor:
+    """``alpha * a.T @ b`` for row-major a [T, M], b [T, N] (bf16; row strides multiples of 8): dW = dY^T . X."""
+    _chk(a, torch.bfloat16, "gemm_tn.a"); _chk(b, torch.bfloat16, "gemm_tn.b")
+    assert a.dim() == 2 and b.dim() == 2 and a.shape[0] == b.shape[0] and a.stride(1) == 1 and b.stride(1) == 1
+    if not gemm_tn_enabled:
+        return gemm(transpose(a), transpose(b), out=out, out_dtype=out_dtype, accumulate=accumulate, alpha=alpha)
+    return _gemm_t(a, True, b, True, a.shape[1], b.shape[1], a.shape[0], out, out_dtype, accumulate, alpha)
+
+
+def gemm_nn(a: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16,
+            wT: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``a @ w`` for a [M, Kc], w [Kc, N] row-major (a weight in its [out, in] state_dict layout): dX = dY . W.
+    ``wT`` = an existing [N, Kc] copy of w to use when the NN kernel is switched off."""
+    _chk(a, torch.bfloat16, "gemm_nn.a"); _chk(w, torch.bfloat16, "gemm_nn.w")
+    assert a.dim() == 2 and w.dim() == 2 and a.shape[1] == w.shape[0] and a.stride(1) == 1 and w.stride(1) == 1
+    if not gemm_nn_enabled:
+        return gemm(a, wT if wT is not None else transpose(w), out=out, out_dtype=out_dtype)
+    return _gemm_t(a, False, w, True, a.shape[0], w.shape[1], a.shape[1], out, out_dtype, False, 1.0)
 
 
 # ------------------------------------------------------------------------------------------------ trajectory tokens

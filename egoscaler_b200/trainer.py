@@ -136,8 +136,8 @@ class Trainer:
         targets = tokens[:, P:].contiguous().view(-1)
         loss = ops.cross_entropy(logits, V, targets, cfg.pad_token_id, write_grad=True)      # logits <- dlogits
         # ---- head backward
-        ops.gemm(ops.transpose(logits), ops.transpose(hn), out=self.grad["lm_head.weight"], accumulate=True)
-        dhn = ops.gemm(logits, m.lm_head_T())
+        ops.gemm_tn(logits, hn, out=self.grad["lm_head.weight"], accumulate=True)             # dW = dlogits^T . hn
+        dhn = ops.gemm_nn(logits, m.lm_head.weight.detach()) if ops.gemm_nn_enabled else ops.gemm(logits, m.lm_head_T())
         dhs = ops.rmsnorm_bwd(dhn, hs2, norm_w, rstd, dw=self.grad["model.norm.weight"])
         self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
         dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)

@@ -66,16 +66,25 @@ int esb_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, void* 
  * esb_gemm_swiglu_bf16 : HF LlamaMLP (modeling_llama.py:171-184) gate|up projection + act_fn(gate) * up in one launch.
  *     Wgu = [gate_proj ; up_proj] packed [2f, K]; act [M, f] = silu(A.Wg^T) * (A.Wu^T); gu [M, 2f] (gate | up, kept for the
  *     backward) is written when non-NULL.  Bit-identical to esb_gemm_bf16 + esb_silu_mul_fwd.
- * esb_gemm_dswiglu_bf16: backward of the same: dgu [M, 2f] = dSwiGLU(gu, dOut . WdownT^T), WdownT [f, K] the contraction-major
- *     copy of down_proj; d(act) is never written.  Bit-identical to esb_gemm_bf16 + esb_silu_mul_bwd.
+ * esb_gemm_dswiglu_bf16: backward of the same: dgu [M, 2f] = dSwiGLU(gu, dOut . down_proj); the weight is passed either as
+ *     Wd = down_proj^T [f, K] (trans_b = 0) or as down_proj itself [K, f] (trans_b = 1); d(act) is never written.
+ *     Bit-identical to esb_gemm_bf16 + esb_silu_mul_bwd.
  * esb_gemm_rope_bf16   : the packed q|k|v projection + apply_rotary_pos_emb (modeling_llama.py:138-168) on the heads (128
  *     columns each) that start below rope_cols, position pos0 + (row % L).  Bit-identical to esb_gemm_bf16 + esb_rope. */
 int esb_gemm_swiglu_bf16(const void* A, int64_t lda, const void* Wgu, int64_t ldw, void* act, int64_t ld_act, void* gu,
                          int64_t ld_gu, int M, int f, int K, void* stream);
-int esb_gemm_dswiglu_bf16(const void* dOut, int64_t lda, const void* WdownT, int64_t ldb, const void* gu, int64_t ld_gu,
+int esb_gemm_dswiglu_bf16(const void* dOut, int64_t lda, const void* Wd, int64_t ldb, int trans_b, const void* gu, int64_t ld_gu,
                           void* dgu, int64_t ld_dgu, int M, int f, int K, void* stream);
 int esb_gemm_rope_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                        const void* cos_tab, const void* sin_tab, int L, int pos0, int rope_cols, int head_dim, void* stream);
+
+/* C[M,N] (+)= alpha * op(A) . op(B) for the two contractions of a Linear's backward (autograd of the nn.Linear call sites
+ * above; train.py:183), read from the tensors exactly as they sit in HBM - MN-major tcgen05 operands, no transposed copies:
+ *   trans_a = 1, trans_b = 1: A [Kc, M], B [Kc, N] row-major  -> weight gradient dW[out,in] = dY[T,out]^T . X[T,in]
+ *   trans_a = 0, trans_b = 1: A [M, Kc], B [Kc, N] row-major  -> data gradient   dX[T,in]  = dY[T,out] . W[out,in]
+ * (trans_a = trans_b = 0 is esb_gemm_bf16 without epilogue.)  C bf16 (out_fp32=0) or fp32 (out_fp32=1; accumulate=1 adds). */
+int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t ldb, int trans_b, void* C, int64_t ldc, int M,
+                    int N, int Kc, int out_fp32, int accumulate, float alpha, void* stream);
 
 /* Weight-streaming variant for the cached single-token decode step (M = sequences per GPU <= 64):
  * C[M,N] = X[M,K] . W[N,K]^T + residual[M,N], bf16 in/out, fp32 accumulation, split-K over the SMs with a

@@ -257,3 +257,48 @@ def test_attention_bwd_fused_inverse_rope_equals_two_launches(B, L, H):
     ops.rope_(ref.view(B * L, 3 * d), L, 2 * H, hd, cos, sin, 0, inverse=True)
     got = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask, rope=(cos, sin))
     assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("T,M,N", [(1392, 256, 768), (1216, 32262, 256), (300, 688, 256), (77, 40, 24), (5568, 4096, 11008), (1026, 384, 1152)])
+def test_gemm_tn_weight_gradient_form(T, M, N):
+    """dW[M,N] = A^T . B with A [T,M], B [T,N] row-major (MN-major tcgen05 operands) vs fp32 torch and vs the transpose + NT path;
+    fp32 accumulate-into-C, strided A (the logits buffer has a padded leading dimension)."""
+    a_buf = _rnd(T, M + 8, seed=21)
+    a = a_buf[:, :M]
+    b = _rnd(T, N, seed=22)
+    ref = a.float().t() @ b.float()
+    got = ops.gemm_tn(a, b)
+    assert got.dtype == torch.float32
+    assert (got - ref).abs().max() <= 2e-3 * ref.abs().max() + 1e-3
+    old = ops.gemm_tn_enabled
+    ops.gemm_tn_enabled = False
+    try:
+        via_nt = ops.gemm_tn(a, b)
+    finally:
+        ops.gemm_tn_enabled = old
+    assert (got - via_nt).abs().max() <= 1e-4 * ref.abs().max() + 1e-4         # same products, same fp32 accumulation order per k-block
+    acc = torch.ones(M, N, device="cuda")
+    ops.gemm_tn(a, b, out=acc, accumulate=True)
+    assert (acc - 1.0 - ref).abs().max() <= 2e-3 * ref.abs().max() + 1e-3
+
+
+@pytest.mark.parametrize("M,Kc,N", [(1392, 768, 256), (1216, 32262, 256), (300, 256, 688), (77, 24, 40), (5568, 11008, 4096), (5568, 4096, 4096)])
+def test_gemm_nn_data_gradient_form(M, Kc, N):
+    """dX[M,N] = A . W with A [M,Kc] and W [Kc,N] = a weight in its [out, in] state_dict layout (MN-major B operand) vs fp32 torch
+    and vs the NT GEMM on a transposed copy (bit-identical: same products, same accumulation order)."""
+    a_buf = _rnd(M, Kc + 8, seed=23)
+    a = a_buf[:, :Kc]
+    w = _rnd(Kc, N, seed=24, scale=Kc ** -0.5)
+    got = ops.gemm_nn(a, w)
+    ref = a.float() @ w.float()
+    assert (got.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
+    assert torch.equal(got, ops.gemm(a, w.t().contiguous()))
+
+
+def test_gemm_dswiglu_on_the_down_proj_parameter_itself():
+    M, f, K = 1392, 688, 256
+    dout = _rnd(M, K, seed=3)
+    wd = _rnd(K, f, seed=4, scale=K ** -0.5)                              # down_proj.weight [d, f]
+    gu = _rnd(M, 2 * f, seed=5)
+    ref = ops.silu_mul_bwd(gu, ops.gemm(dout, wd.t().contiguous()))
+    assert torch.equal(ops.gemm_dswiglu(dout, wd, gu, w_is_down_proj=True), ref)
