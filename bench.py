@@ -472,8 +472,9 @@ def traj_tokens_bench(torch, dev, peaks, with_cpu=True):
         x[:256] = edges
         x[256:262] = special
         xs.append(x[torch.randperm(n, device=dev, generator=g)].contiguous())
+    n6 = n // 6 * 6                                                        # de-quantisation works on whole 6-DoF poses
     ids = [ops.traj_quantize(x, 256, 32006) for x in xs]
-    outs = [ops.traj_dequantize(i.view(-1, 6)[: n // 6], 256, 32006) for i in ids]        # warm-up + outputs for the check
+    outs = [ops.traj_dequantize(i[:n6].view(-1, 6), 256, 32006) for i in ids]             # warm-up + outputs for the check
     reps = 30
 
     def time(fn):
@@ -494,7 +495,7 @@ def traj_tokens_bench(torch, dev, peaks, with_cpu=True):
     ms_q, ms_d = time(lq), time(ld)
     hbm = float(peaks.get("hbm_gbs", 6400.0))
     gq = 12.0 * n / (ms_q * 1e-3) / 1e9
-    gd = 12.0 * (n // 6 * 6) / (ms_d * 1e-3) / 1e9
+    gd = 12.0 * n6 / (ms_d * 1e-3) / 1e9
     out = {"values": n, "bytes_per_value": 12,
            "quantize": {"us": round(ms_q * 1e3, 2), "achieved": round(gq, 1), "peak": hbm, "unit": "GB/s", "frac": round(gq / hbm, 4)},
            "dequantize": {"us": round(ms_d * 1e3, 2), "achieved": round(gd, 1), "peak": hbm, "unit": "GB/s", "frac": round(gd / hbm, 4)},
@@ -509,8 +510,7 @@ def traj_tokens_bench(torch, dev, peaks, with_cpu=True):
         t2 = time_mod.time()
         ok = bool(np.array_equal(q + 32006, ids[0].cpu().numpy()))
         valid = (q >= 0)
-        ok_d = bool(np.array_equal(dq.reshape(-1)[: n // 6 * 6][valid[: n // 6 * 6]],
-                                   outs[0].cpu().numpy().reshape(-1)[valid[: n // 6 * 6]]))
+        ok_d = bool(np.array_equal(dq.reshape(-1)[:n6][valid[:n6]], outs[0].cpu().numpy().reshape(-1)[valid[:n6]]))
         out["cpu_baseline"] = {"kind": "port", "cores": 1, "sample": "the same 2^24 values, NumPy np.digitize / table lookup (oracle/traj_tokenizer.py)",
                                "quantize_gbs": round(12.0 * n / (t1 - t0) / 1e9, 3), "dequantize_gbs": round(12.0 * n / (t2 - t1) / 1e9, 3)}
         out["bit_exact_vs_cpu"] = ok and ok_d
@@ -588,7 +588,7 @@ def gpu_eager_baseline(torch, cfg, args, dev, B, steps=5, warmup=3):
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / steps
         res = {"value": round(B / (ms * 1e-3), 3), "unit": UNIT, "ms_per_step": round(ms, 2), "steps": steps, "warmup": warmup,
-               "per_gpu_batch": B, "loss": round(float(loss), 4),
+               "per_gpu_batch": B, "loss": round(float(loss.detach()), 4),
                "what": "stock eager PyTorch on this GPU: oracle module on cuda, bf16 trunk, autocast(bf16), SDPA with the HF 4-D mask, "
                        f"torch.optim.AdamW; torch {torch.__version__}"}
     finally:

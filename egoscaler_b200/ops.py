@@ -168,10 +168,16 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
 
 # Fused GEMM epilogues of the training / prefill step (llm.py switches on them).  Each one is bit-identical to the pair of
 # launches it replaces (tests/test_gemm_gpu.py), so they can be toggled for A/B timing without touching parity.
-fuse_swiglu = True        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
-fuse_dswiglu = True       # d(act) GEMM + dSwiGLU              (esb_gemm_dswiglu_bf16)
-fuse_rope = True          # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
-fuse_rope_bwd = True      # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope; head_dim 128 only)
+def _env_flag(name: str, default: bool) -> bool:
+    import os
+    v = os.environ.get(name)
+    return default if v is None else v not in ("0", "false", "False", "")
+
+
+fuse_swiglu = _env_flag("ESB_FUSE_SWIGLU", True)        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
+fuse_dswiglu = _env_flag("ESB_FUSE_DSWIGLU", True)      # d(act) GEMM + dSwiGLU              (esb_gemm_dswiglu_bf16)
+fuse_rope = _env_flag("ESB_FUSE_ROPE", True)            # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
+fuse_rope_bwd = _env_flag("ESB_FUSE_ROPE_BWD", True)    # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope)
 
 
 def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):

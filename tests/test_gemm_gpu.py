@@ -263,7 +263,7 @@ def test_attention_bwd_fused_inverse_rope_equals_two_launches(B, L, H):
 def test_gemm_tn_weight_gradient_form(T, M, N):
     """dW[M,N] = A^T . B with A [T,M], B [T,N] row-major (MN-major tcgen05 operands) vs fp32 torch and vs the transpose + NT path;
     fp32 accumulate-into-C, strided A (the logits buffer has a padded leading dimension)."""
-    a_buf = _rnd(T, M + 8, seed=21)
+    a_buf = _rnd(T, (M + 7) // 8 * 8 + 8, seed=21)                           # padded leading dimension (multiple of 8)
     a = a_buf[:, :M]
     b = _rnd(T, N, seed=22)
     ref = a.float().t() @ b.float()
@@ -286,7 +286,7 @@ def test_gemm_tn_weight_gradient_form(T, M, N):
 def test_gemm_nn_data_gradient_form(M, Kc, N):
     """dX[M,N] = A . W with A [M,Kc] and W [Kc,N] = a weight in its [out, in] state_dict layout (MN-major B operand) vs fp32 torch
     and vs the NT GEMM on a transposed copy (same products and k-block order: equal up to rare rounding flips)."""
-    a_buf = _rnd(M, Kc + 8, seed=23)
+    a_buf = _rnd(M, (Kc + 7) // 8 * 8 + 8, seed=23)
     a = a_buf[:, :Kc]
     w = _rnd(Kc, N, seed=24, scale=Kc ** -0.5)
     got = ops.gemm_nn(a, w)

@@ -41,7 +41,7 @@ def test_hd128_forward_and_every_llm_gradient_vs_reference():
     bt = synth.make_batch(cfg, 2, seed=1)
     start = torch.from_numpy(gv["fps_start"])
     m.eval()
-    L = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], fps_start=start).logits.float().cpu()
+    L = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], fps_start=start).logits.detach().float().cpu()
     sub = L[:, gv["logit_rows"]][:, :, gv["logit_cols"]].numpy()
     assert np.abs(sub - gv["logits_sub"]).max() <= 2e-2 * np.abs(gv["logits_sub"]).max()
     m.train()
@@ -82,7 +82,7 @@ def test_trained_logits_and_loss_vs_reference(trained):
     m, g, bt = trained
     start = torch.from_numpy(g["fps_start"])
     m.eval()
-    L = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], fps_start=start).logits.float().cpu()
+    L = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], fps_start=start).logits.detach().float().cpu()
     sub = L[:, g["logit_rows"]][:, :, g["logit_cols"]].numpy()
     assert np.abs(sub - g["logits_sub"]).max() <= 2e-2 * np.abs(g["logits_sub"]).max()
     P = int(g["prompt_len"])

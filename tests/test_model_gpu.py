@@ -80,7 +80,7 @@ def test_point_encoder_and_projector(model, batch, gm):
 def test_forward_logits(model, batch, gm):
     out = model(input_ids=batch["tokens"], attention_mask=batch["attention_masks"], point_clouds=batch["pcrgbs"],
                 return_dict=True, fps_start=torch.from_numpy(gm["fps_start"]))
-    L = out.logits.float().cpu()
+    L = out.logits.detach().float().cpu()
     assert L.shape == (2, 696, 32262)
     sub = L[:, gm["logit_rows"]][:, :, gm["logit_cols"]].numpy()
     ref = gm["logits_sub"]

@@ -90,7 +90,7 @@ def test_base_encoder_forward_grads_and_decode():
     ref = gv["point_proj_sub"]
     assert np.abs(got - ref).max() / np.abs(ref).max() < 3e-2
     out = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], return_dict=True, fps_start=start)
-    L = out.logits.float().cpu()
+    L = out.logits.detach().float().cpu()
     sub = L[:, gv["logit_rows"]][:, :, gv["logit_cols"]].numpy()
     assert np.abs(sub - gv["logits_sub"]).max() <= 2e-2 * np.abs(gv["logits_sub"]).max()
     m.train()
@@ -200,7 +200,7 @@ def test_use_max_pool_branch_matches_oracle():
     ref_loss = train_loss(ref, bt["tokens"], P, 0)
     ref_loss.backward()
     out = m(input_ids=bt["tokens"], attention_mask=bt["attention_masks"], point_clouds=bt["pcrgbs"], return_dict=True, fps_start=start)
-    L = out.logits.float().cpu()
+    L = out.logits.detach().float().cpu()
     assert L.shape == ref.shape
     assert float((L - ref.detach()).abs().max()) <= 2e-2 * float(ref.detach().abs().max())
     m.train()
