@@ -132,6 +132,203 @@ ESB_DEVICE void load_row32_bf16(const __nv_bfloat16* rp, uint32_t* packed, int n
     }
 }
 
+// One accumulator tile: TMEM -> registers -> (epilogue arithmetic) -> global.  Called by the four epilogue warps with
+// t_addr = TMEM address of this warp's lane quarter of the accumulator stage, row = the global row this thread owns.
+template <int BN, int EPI>
+ESB_DEVICE void epilogue_tile(const GemmParams& p, const uint32_t t_addr, const int row, const bool row_ok, const int n0) {
+    const bool vec_ok_bf16 = (!p.out_fp32) && ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    const bool vec_ok_f32 = (p.out_fp32) && ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    const bool res_vec_ok = p.res && ((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.res) & 15) == 0);
+    if constexpr (EPI == EPI_SWIGLU) {
+        // act = bf16(bf16(silu(g)) * u) exactly like silu_mul_fwd_kernel on the bf16-rounded projections
+        __nv_bfloat16* act = reinterpret_cast<__nv_bfloat16*>(p.C);
+        __nv_bfloat16* gu = reinterpret_cast<__nv_bfloat16*>(p.C2);
+        const bool v_act = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(act) & 15) == 0);
+        const bool v_gu = gu && ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= p.f) break;
+            uint32_t rg[32], ru[32];
+            tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), rg);
+            tmem_ld_32x32(t_addr + static_cast<uint32_t>(128 + c * 32), ru);
+            tmem_ld_wait();
+            const int ncols = min(32, p.f - col0);
+            uint32_t pg[16], pu[16], pa[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                pg[j] = pack_bf16x2(__uint_as_float(rg[2 * j]), __uint_as_float(rg[2 * j + 1]));
+                pu[j] = pack_bf16x2(__uint_as_float(ru[2 * j]), __uint_as_float(ru[2 * j + 1]));
+                const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
+                pa[j] = pack_bf16x2(bf16_round(silu(gv.x)) * uv.x, bf16_round(silu(gv.y)) * uv.y);
+            }
+            if (row_ok) {
+                store_row32_bf16(act + static_cast<long long>(row) * p.ldc + col0, pa, ncols, v_act, 0);
+                if (gu) {
+                    store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + col0, pg, ncols, v_gu, p.c_stream);
+                    store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + p.f + col0, pu, ncols, v_gu, p.c_stream);
+                }
+            }
+        }
+    } else if constexpr (EPI == EPI_DSWIGLU) {
+        // d(gate|up) from d(act) (this tile, rounded to bf16 like the materialised tensor was) and the saved gate|up:
+        // the arithmetic of silu_mul_bwd_kernel
+        const __nv_bfloat16* gu = p.aux;
+        __nv_bfloat16* dgu = reinterpret_cast<__nv_bfloat16*>(p.C2);
+        const bool v_in = ((p.ld_aux & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
+        const bool v_out = ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(dgu) & 15) == 0);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= p.N) break;
+            uint32_t r[32];
+            tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
+            tmem_ld_wait();
+            const int ncols = min(32, p.N - col0);
+            if (row_ok) {
+                uint32_t pg[16], pu[16], og[16], ou[16];
+                load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + col0, pg, ncols, v_in);
+                load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + p.f + col0, pu, ncols, v_in);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
+                    const float2 dv = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])));
+                    const float s0 = 1.0f / (1.0f + __expf(-gv.x)), s1 = 1.0f / (1.0f + __expf(-gv.y));
+                    og[j] = pack_bf16x2(dv.x * uv.x * s0 * (1.0f + gv.x * (1.0f - s0)), dv.y * uv.y * s1 * (1.0f + gv.y * (1.0f - s1)));
+                    ou[j] = pack_bf16x2(dv.x * gv.x * s0, dv.y * gv.y * s1);
+                }
+                store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + col0, og, ncols, v_out, p.c_stream);
+                store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + p.f + col0, ou, ncols, v_out, p.c_stream);
+            }
+        }
+    } else if constexpr (EPI == EPI_ROPE) {
+        // two heads of 128 columns per tile; column j pairs with j + 64 (rotate_half)
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C);
+        const bool v_out = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+        const int pos = p.rope_pos0 + (row_ok ? row % p.rope_L : 0);
+        const __nv_bfloat16* cp_ = p.cos_tab + static_cast<long long>(pos) * 64;
+        const __nv_bfloat16* sp_ = p.sin_tab + static_cast<long long>(pos) * 64;
+#pragma unroll 1
+        for (int hc = 0; hc < 4; ++hc) {                     // (head in tile, 32-column chunk of the first half)
+            const int h = hc >> 1, c = hc & 1;
+            const int head0 = n0 + h * 128;
+            if (head0 >= p.N) break;
+            uint32_t lo[32], hi[32];
+            tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + c * 32), lo);
+            tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + 64 + c * 32), hi);
+            tmem_ld_wait();
+            uint32_t o1[16], o2[16];
+            const bool rot = head0 < p.rope_cols;
+            uint32_t cw[16], sw[16];
+            if (rot && row_ok) {
+                load_row32_bf16(cp_ + c * 32, cw, 32, true);
+                load_row32_bf16(sp_ + c * 32, sw, 32, true);
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                o1[j] = pack_bf16x2(__uint_as_float(lo[2 * j]), __uint_as_float(lo[2 * j + 1]));
+                o2[j] = pack_bf16x2(__uint_as_float(hi[2 * j]), __uint_as_float(hi[2 * j + 1]));
+                if (rot && row_ok) {
+                    const float2 x1 = unpack_bf16x2(o1[j]), x2 = unpack_bf16x2(o2[j]);
+                    const float2 cc = unpack_bf16x2(cw[j]), ss = unpack_bf16x2(sw[j]);
+                    o1[j] = pack_bf16x2(bf16_round(x1.x * cc.x) - bf16_round(x2.x * ss.x), bf16_round(x1.y * cc.y) - bf16_round(x2.y * ss.y));
+                    o2[j] = pack_bf16x2(bf16_round(x2.x * cc.x) + bf16_round(x1.x * ss.x), bf16_round(x2.y * cc.y) + bf16_round(x1.y * ss.y));
+                }
+            }
+            if (row_ok) {
+                __nv_bfloat16* rp = out + static_cast<long long>(row) * p.ldc + head0 + c * 32;
+                store_row32_bf16(rp, o1, 32, v_out, 0);
+                store_row32_bf16(rp + 64, o2, 32, v_out, 0);
+            }
+        }
+    } else {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;                    // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+        const int ncols = min(32, p.N - col0);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+        if (p.bias) {
+            if (ncols == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
+            }
+        }
+        if (p.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        } else if (p.act == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+        if (row_ok) {
+            if (p.res) {
+                const __nv_bfloat16* rp = p.res + static_cast<long long>(row) * p.ldr + col0;
+                if (res_vec_ok && ncols == 32) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + g);
+                        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
+                                     d = unpack_bf16x2(u.w);
+                        v[g * 8 + 0] += a.x; v[g * 8 + 1] += a.y; v[g * 8 + 2] += b.x; v[g * 8 + 3] += b.y;
+                        v[g * 8 + 4] += cc.x; v[g * 8 + 5] += cc.y; v[g * 8 + 6] += d.x; v[g * 8 + 7] += d.y;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) v[j] += __bfloat162float(rp[j]);
+                }
+            }
+            if (!p.out_fp32) {
+                __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+                if (vec_ok_bf16 && ncols == 32) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint4 u;
+                        u.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+                        u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+                        u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+                        u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+                        if (p.c_stream) __stcs(reinterpret_cast<uint4*>(cp) + g, u);
+                        else reinterpret_cast<uint4*>(cp)[g] = u;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) cp[j] = __float2bfloat16_rn(v[j]);
+                }
+            } else {
+                float* cp = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+                if (vec_ok_f32 && ncols == 32) {
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        float4 u = make_float4(v[g * 4 + 0], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+                        if (p.accumulate) {
+                            const float4 o = reinterpret_cast<float4*>(cp)[g];
+                            u.x += o.x; u.y += o.y; u.z += o.z; u.w += o.w;
+                        }
+                        reinterpret_cast<float4*>(cp)[g] = u;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) cp[j] = p.accumulate ? cp[j] + v[j] : v[j];
+                }
+            }
+        }
+    }
+    }   // EPI_PLAIN
+}
+
 // TA / TB = true: that operand is stored with the CONTRACTION index outermost (A [Kc, M] / B [Kc, N] row-major) instead of
 // innermost.  TA & TB: C = A^T . B, the weight-gradient contraction dW = dY^T . X on the activations exactly as they sit in HBM;
 // TB only: C = A . B with B = a weight [in = Kc, out = N]... i.e. the data-gradient dX = dY . W on the state_dict layout - no
@@ -264,9 +461,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         const int q = warp & 3;                            // TMEM lane quarter this warp may access
         int acc = 0;
         uint32_t acc_phase = 0;
-        const bool vec_ok_bf16 = (!p.out_fp32) && ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-        const bool vec_ok_f32 = (p.out_fp32) && ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-        const bool res_vec_ok = p.res && ((p.ldr & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.res) & 15) == 0);
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             int tm, tn;
             tile_coords(p, t, tm, tn);
@@ -276,194 +470,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < p.M;
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
-            if constexpr (EPI == EPI_SWIGLU) {
-                // act = bf16(bf16(silu(g)) * u) exactly like silu_mul_fwd_kernel on the bf16-rounded projections
-                __nv_bfloat16* act = reinterpret_cast<__nv_bfloat16*>(p.C);
-                __nv_bfloat16* gu = reinterpret_cast<__nv_bfloat16*>(p.C2);
-                const bool v_act = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(act) & 15) == 0);
-                const bool v_gu = gu && ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    const int col0 = n0 + c * 32;
-                    if (col0 >= p.f) break;
-                    uint32_t rg[32], ru[32];
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), rg);
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(128 + c * 32), ru);
-                    tmem_ld_wait();
-                    const int ncols = min(32, p.f - col0);
-                    uint32_t pg[16], pu[16], pa[16];
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        pg[j] = pack_bf16x2(__uint_as_float(rg[2 * j]), __uint_as_float(rg[2 * j + 1]));
-                        pu[j] = pack_bf16x2(__uint_as_float(ru[2 * j]), __uint_as_float(ru[2 * j + 1]));
-                        const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
-                        pa[j] = pack_bf16x2(bf16_round(silu(gv.x)) * uv.x, bf16_round(silu(gv.y)) * uv.y);
-                    }
-                    if (row_ok) {
-                        store_row32_bf16(act + static_cast<long long>(row) * p.ldc + col0, pa, ncols, v_act, 0);
-                        if (gu) {
-                            store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + col0, pg, ncols, v_gu, p.c_stream);
-                            store_row32_bf16(gu + static_cast<long long>(row) * p.ldc2 + p.f + col0, pu, ncols, v_gu, p.c_stream);
-                        }
-                    }
-                }
-            } else if constexpr (EPI == EPI_DSWIGLU) {
-                // d(gate|up) from d(act) (this tile, rounded to bf16 like the materialised tensor was) and the saved gate|up:
-                // the arithmetic of silu_mul_bwd_kernel
-                const __nv_bfloat16* gu = p.aux;
-                __nv_bfloat16* dgu = reinterpret_cast<__nv_bfloat16*>(p.C2);
-                const bool v_in = ((p.ld_aux & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
-                const bool v_out = ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(dgu) & 15) == 0);
-#pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    const int col0 = n0 + c * 32;
-                    if (col0 >= p.N) break;
-                    uint32_t r[32];
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
-                    tmem_ld_wait();
-                    const int ncols = min(32, p.N - col0);
-                    if (row_ok) {
-                        uint32_t pg[16], pu[16], og[16], ou[16];
-                        load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + col0, pg, ncols, v_in);
-                        load_row32_bf16(gu + static_cast<long long>(row) * p.ld_aux + p.f + col0, pu, ncols, v_in);
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const float2 gv = unpack_bf16x2(pg[j]), uv = unpack_bf16x2(pu[j]);
-                            const float2 dv = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])));
-                            const float s0 = 1.0f / (1.0f + __expf(-gv.x)), s1 = 1.0f / (1.0f + __expf(-gv.y));
-                            og[j] = pack_bf16x2(dv.x * uv.x * s0 * (1.0f + gv.x * (1.0f - s0)), dv.y * uv.y * s1 * (1.0f + gv.y * (1.0f - s1)));
-                            ou[j] = pack_bf16x2(dv.x * gv.x * s0, dv.y * gv.y * s1);
-                        }
-                        store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + col0, og, ncols, v_out, p.c_stream);
-                        store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + p.f + col0, ou, ncols, v_out, p.c_stream);
-                    }
-                }
-            } else if constexpr (EPI == EPI_ROPE) {
-                // two heads of 128 columns per tile; column j pairs with j + 64 (rotate_half)
-                __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C);
-                const bool v_out = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-                const int pos = p.rope_pos0 + (row_ok ? row % p.rope_L : 0);
-                const __nv_bfloat16* cp_ = p.cos_tab + static_cast<long long>(pos) * 64;
-                const __nv_bfloat16* sp_ = p.sin_tab + static_cast<long long>(pos) * 64;
-#pragma unroll 1
-                for (int hc = 0; hc < 4; ++hc) {                     // (head in tile, 32-column chunk of the first half)
-                    const int h = hc >> 1, c = hc & 1;
-                    const int head0 = n0 + h * 128;
-                    if (head0 >= p.N) break;
-                    uint32_t lo[32], hi[32];
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + c * 32), lo);
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 128 + 64 + c * 32), hi);
-                    tmem_ld_wait();
-                    uint32_t o1[16], o2[16];
-                    const bool rot = head0 < p.rope_cols;
-                    uint32_t cw[16], sw[16];
-                    if (rot && row_ok) {
-                        load_row32_bf16(cp_ + c * 32, cw, 32, true);
-                        load_row32_bf16(sp_ + c * 32, sw, 32, true);
-                    }
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        o1[j] = pack_bf16x2(__uint_as_float(lo[2 * j]), __uint_as_float(lo[2 * j + 1]));
-                        o2[j] = pack_bf16x2(__uint_as_float(hi[2 * j]), __uint_as_float(hi[2 * j + 1]));
-                        if (rot && row_ok) {
-                            const float2 x1 = unpack_bf16x2(o1[j]), x2 = unpack_bf16x2(o2[j]);
-                            const float2 cc = unpack_bf16x2(cw[j]), ss = unpack_bf16x2(sw[j]);
-                            o1[j] = pack_bf16x2(bf16_round(x1.x * cc.x) - bf16_round(x2.x * ss.x), bf16_round(x1.y * cc.y) - bf16_round(x2.y * ss.y));
-                            o2[j] = pack_bf16x2(bf16_round(x2.x * cc.x) + bf16_round(x1.x * ss.x), bf16_round(x2.y * cc.y) + bf16_round(x1.y * ss.y));
-                        }
-                    }
-                    if (row_ok) {
-                        __nv_bfloat16* rp = out + static_cast<long long>(row) * p.ldc + head0 + c * 32;
-                        store_row32_bf16(rp, o1, 32, v_out, 0);
-                        store_row32_bf16(rp + 64, o2, 32, v_out, 0);
-                    }
-                }
-            } else {
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                const int col0 = n0 + c * 32;
-                if (col0 >= p.N) break;                    // warp-uniform
-                uint32_t r[32];
-                tmem_ld_32x32(t_addr + static_cast<uint32_t>(c * 32), r);
-                tmem_ld_wait();
-                const int ncols = min(32, p.N - col0);
-                float v[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-                if (p.bias) {
-                    if (ncols == 32) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col0 + j);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
-                    }
-                }
-                if (p.act == 1) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-                } else if (p.act == 2) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-                }
-                if (row_ok) {
-                    if (p.res) {
-                        const __nv_bfloat16* rp = p.res + static_cast<long long>(row) * p.ldr + col0;
-                        if (res_vec_ok && ncols == 32) {
-#pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + g);
-                                const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
-                                             d = unpack_bf16x2(u.w);
-                                v[g * 8 + 0] += a.x; v[g * 8 + 1] += a.y; v[g * 8 + 2] += b.x; v[g * 8 + 3] += b.y;
-                                v[g * 8 + 4] += cc.x; v[g * 8 + 5] += cc.y; v[g * 8 + 6] += d.x; v[g * 8 + 7] += d.y;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < ncols) v[j] += __bfloat162float(rp[j]);
-                        }
-                    }
-                    if (!p.out_fp32) {
-                        __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
-                        if (vec_ok_bf16 && ncols == 32) {
-#pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                uint4 u;
-                                u.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
-                                u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
-                                u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
-                                u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-                                if (p.c_stream) __stcs(reinterpret_cast<uint4*>(cp) + g, u);
-                                else reinterpret_cast<uint4*>(cp)[g] = u;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < ncols) cp[j] = __float2bfloat16_rn(v[j]);
-                        }
-                    } else {
-                        float* cp = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
-                        if (vec_ok_f32 && ncols == 32) {
-#pragma unroll
-                            for (int g = 0; g < 8; ++g) {
-                                float4 u = make_float4(v[g * 4 + 0], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
-                                if (p.accumulate) {
-                                    const float4 o = reinterpret_cast<float4*>(cp)[g];
-                                    u.x += o.x; u.y += o.y; u.z += o.z; u.w += o.w;
-                                }
-                                reinterpret_cast<float4*>(cp)[g] = u;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < ncols) cp[j] = p.accumulate ? cp[j] + v[j] : v[j];
-                        }
-                    }
-                }
-            }
-            }   // EPI_PLAIN
+            epilogue_tile<BN, EPI>(p, t_addr, row, row_ok, n0);
             tc_fence_before();
             mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
@@ -478,6 +485,152 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         tmem_dealloc(tmem_base, 2 * BN);
     }
 }
+
+// ============================================================================================ CTA-pair GEMM (cta_group::2)
+// Two CTAs of a cluster (the two SMs of a TPC) compute one 256 x 256 tile: each CTA stages ITS 128 rows of A and ITS 128 of the
+// 256 weight rows (32 KB per stage instead of 48 KB -> 6 stages), the leader CTA issues tcgen05.mma.cta_group::2 (M = 256), which
+// reads A from both CTAs and gives every SM the B half it does not hold through the pair's shared-memory path: half the B
+// traffic from L2 and half the shared-memory operand bytes per flop of the single-CTA kernel (the step is
+// power-capped, so bytes per flop are the lever).  Accumulators: 128 lanes x 256 columns in EACH CTA's TMEM, two stages.
+//   full[s]   (leader)  : count 2 = leader's arrive.expect_tx(64 KB) + the peer's remote arrive; both CTAs' TMA credit it
+//   empty[s]  (both)    : tcgen05.commit multicast to both CTAs once the MMAs reading stage s retired
+//   tfull[a]  (both)    : tcgen05.commit multicast - accumulator stage a complete
+//   tempty[a] (leader)  : count 256 = the epilogue threads of both CTAs (the peer arrives remotely)
+constexpr int P2_STAGES = 6;
+constexpr int P2_STAGE_BYTES = 2 * 128 * BK * 2;
+constexpr int P2_SMEM = P2_STAGES * P2_STAGE_BYTES + 1024 + 1024;
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+    constexpr int BN = 256;
+    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* tiles = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P2_STAGES * P2_STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + P2_STAGES;
+    uint64_t* tmem_full = bars + 2 * P2_STAGES;
+    uint64_t* tmem_empty = bars + 2 * P2_STAGES + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * P2_STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = static_cast<int>(blockIdx.x >> 1), npairs = static_cast<int>(gridDim.x >> 1);
+    const int num_kb = (p.K + BK - 1) / BK;
+    const int num_tiles = p.tiles_m * p.tiles_n;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < P2_STAGES; ++i) {
+            mbar_init(&full_bar[i], 2);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 256);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc_2cta(tmem_slot, 2 * BN);
+        tmem_relinquish_2cta();
+    }
+    tc_fence_before();
+    cluster_sync_all();                                    // barrier inits + TMEM allocation visible to both CTAs
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===================== TMA producer (both CTAs): own 128 rows of A, own 128 weight rows
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t leader_full0 = mapa_shared(smem_u32(&full_bar[0]), 0);
+            for (int t = pair; t < num_tiles; t += npairs) {
+                int tm, tn;
+                tile_coords(p, t, tm, tn);
+                const int m0 = tm * 256 + static_cast<int>(rank) * 128;
+                const int nb = (EPI == EPI_SWIGLU) ? (tn * 128 + (rank ? p.f : 0)) : (tn * 256 + static_cast<int>(rank) * 128);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    uint8_t* sa = tiles + stage * P2_STAGE_BYTES;
+                    uint8_t* sb = sa + 128 * BK * 2;
+                    if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * P2_STAGE_BYTES);
+                    tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
+                    tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], kb * BK, nb, p.b_policy);
+                    if (rank != 0) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
+                    if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // ===================== MMA issuer (leader CTA only)
+            constexpr uint32_t idesc = umma_idesc_bf16(256, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = pair; t < num_tiles; t += npairs) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(tiles + stage * P2_STAGE_BYTES);
+                    const uint32_t sb = sa + 128 * BK * 2;
+                    const uint64_t da = umma_desc_kmajor_sw128(sa);
+                    const uint64_t db = umma_desc_kmajor_sw128(sb);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_bf16_ss_2cta(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k), idesc,
+                                          (kb | k) != 0 ? 1u : 0u);
+                    umma_commit_2cta(&empty_bar[stage], 3);          // both CTAs may refill stage `stage`
+                    if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit_2cta(&tmem_full[acc], 3);                // accumulator complete in both CTAs -> epilogues
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1u;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue (both CTAs): own 128 rows of the tile
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        const uint32_t leader_tempty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
+        for (int t = pair; t < num_tiles; t += npairs) {
+            int tm, tn;
+            tile_coords(p, t, tm, tn);
+            const int m0 = tm * 256 + static_cast<int>(rank) * 128, n0 = tn * BN_OUT;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const bool row_ok = row < p.M;
+            const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+            epilogue_tile<BN, EPI>(p, t_addr, row, row_ok, n0);
+            tc_fence_before();
+            mbar_arrive_cluster(leader_tempty0 + static_cast<uint32_t>(acc) * 8u);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1u;
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();                                    // nobody frees TMEM / exits while the partner still works
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_2cta(tmem_base, 2 * BN);
+    }
+}
+
 
 // ----------------------------------------------------------------------------- host side
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -536,29 +689,17 @@ int make_tma_3d_bf16(CUtensorMap* map, const void* ptr, long long cols, long lon
     return ESB_OK;
 }
 
-template <int BN, int EPI = EPI_PLAIN, bool TA = false, bool TB = false>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
-    using S = GemmSmem<BN>;
-    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-        if (e != cudaSuccess) {
-            set_last_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e));
-            return ESB_ERR_CUDA;
-        }
-        attr_set = true;
-    }
-    p.tiles_m = (p.M + BM - 1) / BM;
-    p.tiles_n = (p.N + BN_OUT - 1) / BN_OUT;
-    const int tiles = p.tiles_m * p.tiles_n;
-    // ---- tile walk: modelled DRAM bytes = persisting operand once + streamed operand once per group + C
+// Tile grid + walk order + L2 policies of one launch (tile = bm rows x bn_out output columns, B panel = bn weight rows).
+// Modelled DRAM bytes = persisting operand once + streamed operand once per group + C.
+static void choose_walk(GemmParams& p, int bm, int bn, int bn_out, int c_mult) {
+    p.tiles_m = (p.M + bm - 1) / bm;
+    p.tiles_n = (p.N + bn_out - 1) / bn_out;
     static const int hints = [] { const char* e = getenv("ESB_GEMM_L2_HINTS"); return e ? atoi(e) : 7; }();
     static const double budget_mb = [] { const char* e = getenv("ESB_GEMM_L2_BUDGET_MB"); return e ? atof(e) : 48.0; }();
     const double budget = budget_mb * (1 << 20);              // bytes of one operand group kept L2-resident (126 MB L2, two halves)
-    const double a_panel = 2.0 * BM * p.K, b_panel = 2.0 * BN * p.K;
+    const double a_panel = 2.0 * bm * p.K, b_panel = 2.0 * bn * p.K;
     const double a_bytes = a_panel * p.tiles_m, b_bytes = b_panel * p.tiles_n;
-    const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2) * ((EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
+    const double c_bytes = static_cast<double>(p.M) * p.N * (p.out_fp32 ? 4 : 2) * c_mult;
     int gm = static_cast<int>(budget / a_panel);
     gm = gm < 1 ? 1 : (gm > p.tiles_m ? p.tiles_m : gm);
     const int groups_m = (p.tiles_m + gm - 1) / gm;
@@ -577,9 +718,51 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     p.a_policy = ((hints & 1) && p.raster_mode == 0 && persist_fits) ? kEvictLast : kEvictNormal;
     p.b_policy = ((hints & 1) && p.raster_mode == 1 && persist_fits) ? kEvictLast : kEvictNormal;
     p.c_stream = ((hints & 2) && !p.out_fp32 && c_bytes >= 96.0 * (1 << 20)) ? 1 : 0;
+}
+
+template <int BN, int EPI = EPI_PLAIN, bool TA = false, bool TB = false>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
+    using S = GemmSmem<BN>;
+    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        if (e != cudaSuccess) {
+            set_last_error("cudaFuncSetAttribute(gemm<%d>): %s", BN, cudaGetErrorString(e));
+            return ESB_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    choose_walk(p, BM, BN, BN_OUT, (EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
+    const int tiles = p.tiles_m * p.tiles_n;
     const int grid = tiles < sms ? tiles : sms;
     gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
     return check_launch("gemm_bf16_tcgen05");
+}
+
+// CTA-pair variant (gemm2_bf16_tcgen05_kernel): opt-in through esb_set_gemm_2cta / ESB_GEMM_2CTA
+static int g_gemm_2cta = [] { const char* e = getenv("ESB_GEMM_2CTA"); return e ? atoi(e) : 0; }();
+int set_gemm_2cta(int on) { const int old = g_gemm_2cta; g_gemm_2cta = on ? 1 : 0; return old; }
+static bool use_2cta(int M, int N, int K) { return g_gemm_2cta && M >= 1024 && N >= 512 && K >= 256; }
+
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
+    constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : 256;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm2_bf16_tcgen05_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, P2_SMEM);
+        if (e != cudaSuccess) {
+            set_last_error("cudaFuncSetAttribute(gemm2): %s", cudaGetErrorString(e));
+            return ESB_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    choose_walk(p, 256, 256, BN_OUT, (EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
+    const int tiles = p.tiles_m * p.tiles_n;
+    int pairs = sms / 2;
+    if (tiles < pairs) pairs = tiles;
+    gemm2_bf16_tcgen05_kernel<EPI><<<2 * pairs, GEMM_THREADS, P2_SMEM, stream>>>(ta, tb, p);
+    return check_launch("gemm2_bf16_tcgen05");
 }
 
 int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* C, long long ldc, int M, int N, int K,
@@ -613,10 +796,11 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
             }
         }
     }
+    const bool pair = force_bn == 0 && use_2cta(M, N, K);
     CUtensorMap ta, tb;
     int rc = make_tma_2d_bf16(&ta, A, M, K, lda, BM);
     if (rc) return rc;
-    rc = make_tma_2d_bf16(&tb, B, N, K, ldb, bn);
+    rc = make_tma_2d_bf16(&tb, B, N, K, ldb, pair ? 128 : bn);
     if (rc) return rc;
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.bias = bias;
@@ -626,6 +810,7 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
     p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;      // set by launch_gemm
     p.C2 = nullptr; p.ldc2 = 0; p.aux = nullptr; p.ld_aux = 0; p.f = 0; p.cos_tab = p.sin_tab = nullptr;
     p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0;
+    if (pair) return launch_gemm2<EPI_PLAIN>(ta, tb, p, stream, sms);
     switch (bn) {
         case 256: return launch_gemm<256>(ta, tb, p, stream, sms);
         case 128: return launch_gemm<128>(ta, tb, p, stream, sms);
@@ -665,6 +850,7 @@ int gemm_swiglu_bf16(const void* A, long long lda, const void* Wgu, long long ld
     rc = make_tma_2d_bf16(&tb, Wgu, 2LL * f, K, ldw, 128);
     if (rc) return rc;
     p.C = act; p.ldc = ld_act; p.C2 = gu; p.ldc2 = ld_gu; p.f = f;
+    if (use_2cta(M, f, K)) return launch_gemm2<EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());      // same 128-row boxes
     return launch_gemm<256, EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());
 }
 
@@ -680,9 +866,11 @@ int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long 
     CUtensorMap ta, tb;
     rc = make_tma_2d_bf16(&ta, dOut, M, K, lda, BM);
     if (rc) return rc;
-    rc = trans_b ? make_tma_2d_bf16(&tb, WdownT, K, f, ldb, 64) : make_tma_2d_bf16(&tb, WdownT, f, K, ldb, 256);
+    const bool pair = !trans_b && use_2cta(M, f, K);
+    rc = trans_b ? make_tma_2d_bf16(&tb, WdownT, K, f, ldb, 64) : make_tma_2d_bf16(&tb, WdownT, f, K, ldb, pair ? 128 : 256);
     if (rc) return rc;
     p.aux = static_cast<const __nv_bfloat16*>(gu); p.ld_aux = ld_gu; p.C2 = dgu; p.ldc2 = ld_dgu; p.f = f;
+    if (pair) return launch_gemm2<EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
     if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, device_sm_count());
     return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
 }
@@ -701,10 +889,12 @@ int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, v
     CUtensorMap ta, tb;
     rc = make_tma_2d_bf16(&ta, A, M, K, lda, BM);
     if (rc) return rc;
-    rc = make_tma_2d_bf16(&tb, W, N, K, ldw, 256);
+    const bool pair = use_2cta(M, N, K);
+    rc = make_tma_2d_bf16(&tb, W, N, K, ldw, pair ? 128 : 256);
     if (rc) return rc;
     p.C = C; p.ldc = ldc; p.cos_tab = static_cast<const __nv_bfloat16*>(cos_tab); p.sin_tab = static_cast<const __nv_bfloat16*>(sin_tab);
     p.rope_L = L; p.rope_pos0 = pos0; p.rope_cols = rope_cols;
+    if (pair) return launch_gemm2<EPI_ROPE>(ta, tb, p, stream, device_sm_count());
     return launch_gemm<256, EPI_ROPE>(ta, tb, p, stream, device_sm_count());
 }
 

@@ -180,6 +180,11 @@ fuse_rope = _env_flag("ESB_FUSE_ROPE", True)            # q|k|v GEMM + rotary em
 fuse_rope_bwd = _env_flag("ESB_FUSE_ROPE_BWD", True)    # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope)
 
 
+def set_gemm_2cta(on: bool) -> bool:
+    """Large GEMMs through the CTA-pair (cta_group::2, 256 x 256 tile) kernel; returns the previous setting."""
+    return bool(_l.lib().raw("esb_set_gemm_2cta")(1 if on else 0))
+
+
 def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):
     """a [M,K], wgu [2f,K] = [gate ; up] -> (act [M,f], gu [M,2f] or None)."""
     _chk(a, torch.bfloat16, "gemm_swiglu.a"); _chk(wgu, torch.bfloat16, "gemm_swiglu.wgu")

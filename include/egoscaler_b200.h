@@ -86,6 +86,11 @@ int esb_gemm_rope_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, v
 int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t ldb, int trans_b, void* C, int64_t ldc, int M,
                     int N, int Kc, int out_fp32, int accumulate, float alpha, void* stream);
 
+/* Route the large NT GEMMs (M >= 1024, N >= 512; plain and fused epilogues) through the CTA-pair kernel: clusters of two CTAs,
+ * tcgen05.mma.cta_group::2 on 256 x 256 tiles, each SM stages half of the weight tile.  Returns the previous setting.  Default:
+ * environment variable ESB_GEMM_2CTA (0). */
+int esb_set_gemm_2cta(int on);
+
 /* Weight-streaming variant for the cached single-token decode step (M = sequences per GPU <= 64):
  * C[M,N] = X[M,K] . W[N,K]^T + residual[M,N], bf16 in/out, fp32 accumulation, split-K over the SMs with a
  * deterministic in-kernel reduction.  Same Linear call sites as esb_gemm_bf16, reached through generate()

@@ -305,3 +305,22 @@ def test_gemm_dswiglu_on_the_down_proj_parameter_itself():
     ref = ops.silu_mul_bwd(gu, ops.gemm(dout, wd.t().contiguous()))
     got = ops.gemm_dswiglu(dout, wd, gu, w_is_down_proj=True)
     assert (got.float() - ref.float()).abs().max() <= 8e-3 * ref.float().abs().max() and (got != ref).float().mean() < 1e-2
+
+
+def test_cta_pair_gemm_matches_single_cta_kernel():
+    """tcgen05.mma.cta_group::2 kernel (clusters of two CTAs, 256 x 256 tile, esb_set_gemm_2cta) == the single-CTA kernel bit for
+    bit on plain / residual / fp32 / SwiGLU / dSwiGLU / RoPE epilogues.  Runs in a subprocess with a timeout: a mistake in the
+    cross-CTA mbarrier protocol would hang, and a hang must fail this test, not the box."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "gemm2_check.py")], capture_output=True, text=True, timeout=240)
+    except subprocess.TimeoutExpired:
+        pytest.fail("CTA-pair GEMM check timed out (hang in the two-CTA pipeline)")
+    assert r.returncode == 0, r.stderr[-2000:]
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["ok"], {k: v for k, v in res["checks"].items() if not v}
+    assert len(res["checks"]) >= 12
