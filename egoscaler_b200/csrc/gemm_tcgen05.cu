@@ -64,6 +64,7 @@ struct GemmParams {
     const __nv_bfloat16* cos_tab;
     const __nv_bfloat16* sin_tab;
     int rope_L, rope_pos0, rope_cols;
+    int dbg;                  // CTA-pair kernel experiments (ESB_GEMM2_DBG): bit 0 full barrier without the peer's arrive, bit 1 spin on test_wait
 };
 enum : int { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_DSWIGLU = 2, EPI_ROPE = 3 };
 
@@ -177,33 +178,41 @@ ESB_DEVICE void epilogue_tile(const GemmParams& p, const uint32_t t_addr, const 
         __nv_bfloat16* dgu = reinterpret_cast<__nv_bfloat16*>(p.C2);
         const bool v_in = ((p.ld_aux & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(gu) & 15) == 0);
         const bool v_out = ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(dgu) & 15) == 0);
-        // The gate|up rows of a warp lie 2f elements apart (32 different DRAM pages per load instruction), so the loads are
-        // software-pipelined two 32-column chunks ahead of the arithmetic (three rotating register buffers; the first
-        // measurement of the un-pipelined epilogue ran the whole GEMM at 810 TF/s, slower than GEMM + silu_mul_bwd).
-        constexpr int NCH = BN / 32, AHEAD = 2;
-        uint32_t pg[AHEAD + 1][16], pu[AHEAD + 1][16];
+        // The gate|up rows of a warp lie 2f elements apart (32 different lines per load instruction) and the L1 next to 194 KB
+        // of shared memory is tiny, so every thread reads WHOLE 128-byte lines (64 columns of gate and of up per group) exactly
+        // once and the next group's loads are in flight while this group's arithmetic runs (two register buffers).  History:
+        // per-32-column loads without prefetch ran the GEMM at 810 TF/s; prefetching half lines two chunks ahead thrashed the L1
+        // (404 TF/s).
+        constexpr int NGRP = BN / 64;
+        uint32_t bg[2][32], bu[2][32];
         const __nv_bfloat16* grow = gu + static_cast<long long>(row_ok ? row : 0) * p.ld_aux;
-#pragma unroll
-        for (int c = 0; c < NCH + AHEAD; ++c) {
-            if (c < NCH) {
-                const int col0 = n0 + c * 32;
-                if (row_ok && col0 < p.N) {
-                    const int ncols = min(32, p.N - col0);
-                    load_row32_bf16(grow + col0, pg[c % (AHEAD + 1)], ncols, v_in);
-                    load_row32_bf16(grow + p.f + col0, pu[c % (AHEAD + 1)], ncols, v_in);
+        auto issue = [&](int g, uint32_t* pg_, uint32_t* pu_) {
+            const int col0 = n0 + g * 64;
+            if (row_ok && col0 < p.N) {
+                const int n64 = min(64, p.N - col0);
+                load_row32_bf16(grow + col0, pg_, min(32, n64), v_in);
+                load_row32_bf16(grow + p.f + col0, pu_, min(32, n64), v_in);
+                if (n64 > 32) {
+                    load_row32_bf16(grow + col0 + 32, pg_ + 16, n64 - 32, v_in);
+                    load_row32_bf16(grow + p.f + col0 + 32, pu_ + 16, n64 - 32, v_in);
                 }
             }
-            if (c >= AHEAD) {
-                const int cc = c - AHEAD;
-                const int col0 = n0 + cc * 32;
+        };
+        issue(0, bg[0], bu[0]);
+#pragma unroll
+        for (int g = 0; g < NGRP; ++g) {
+            if (g + 1 < NGRP) issue(g + 1, bg[(g + 1) & 1], bu[(g + 1) & 1]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int col0 = n0 + g * 64 + h * 32;
                 if (col0 < p.N) {                                        // warp-uniform
                     uint32_t r[32];
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(cc * 32), r);
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(g * 64 + h * 32), r);
                     tmem_ld_wait();
                     const int ncols = min(32, p.N - col0);
                     if (row_ok) {
-                        const uint32_t* qg = pg[cc % (AHEAD + 1)];
-                        const uint32_t* qu = pu[cc % (AHEAD + 1)];
+                        const uint32_t* qg = bg[g & 1] + h * 16;
+                        const uint32_t* qu = bu[g & 1] + h * 16;
                         uint32_t og[16], ou[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
@@ -514,6 +523,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 //   empty[s]  (both)    : tcgen05.commit multicast to both CTAs once the MMAs reading stage s retired
 //   tfull[a]  (both)    : tcgen05.commit multicast - accumulator stage a complete
 //   tempty[a] (leader)  : count 256 = the epilogue threads of both CTAs (the peer arrives remotely)
+ESB_DEVICE void mbar_wait_dbg(int spin, uint64_t* bar, uint32_t parity) {
+    if (!spin) { mbar_wait(bar, parity); return; }
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    }
+}
 constexpr int P2_STAGES = 6;
 constexpr int P2_STAGE_BYTES = 2 * 128 * BK * 2;
 constexpr int P2_SMEM = P2_STAGES * P2_STAGE_BYTES + 1024 + 1024;
@@ -546,7 +564,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < P2_STAGES; ++i) {
-            mbar_init(&full_bar[i], 2);
+            mbar_init(&full_bar[i], (p.dbg & 1) ? 1 : 2);
             mbar_init(&empty_bar[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
@@ -576,13 +594,13 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
                 const int m0 = tm * 256 + static_cast<int>(rank) * 128;
                 const int nb = (EPI == EPI_SWIGLU) ? (tn * 128 + (rank ? p.f : 0)) : (tn * 256 + static_cast<int>(rank) * 128);
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    mbar_wait_dbg(p.dbg & 2, &empty_bar[stage], phase ^ 1u);
                     uint8_t* sa = tiles + stage * P2_STAGE_BYTES;
                     uint8_t* sb = sa + 128 * BK * 2;
                     if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * P2_STAGE_BYTES);
                     tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
                     tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], kb * BK, nb, p.b_policy);
-                    if (rank != 0) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
+                    if (rank != 0 && !(p.dbg & 1)) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
                     if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -596,11 +614,11 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
             int acc = 0;
             uint32_t acc_phase = 0;
             for (int t = pair; t < num_tiles; t += npairs) {
-                mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+                mbar_wait_dbg(p.dbg & 2, &tmem_empty[acc], acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
+                    mbar_wait_dbg(p.dbg & 2, &full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(tiles + stage * P2_STAGE_BYTES);
                     const uint32_t sb = sa + 128 * BK * 2;
@@ -628,7 +646,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
             int tm, tn;
             tile_coords(p, t, tm, tn);
             const int m0 = tm * 256 + static_cast<int>(rank) * 128, n0 = tn * BN_OUT;
-            mbar_wait(&tmem_full[acc], acc_phase);
+            mbar_wait_dbg(p.dbg & 2, &tmem_full[acc], acc_phase);
             tc_fence_after();
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < p.M;
@@ -776,6 +794,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams
         attr_set = true;
     }
     choose_walk(p, 256, 256, BN_OUT, (EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
+    { const char* e = getenv("ESB_GEMM2_DBG"); p.dbg = e ? atoi(e) : 0; }
     const int tiles = p.tiles_m * p.tiles_n;
     int pairs = sms / 2;
     if (tiles < pairs) pairs = tiles;
@@ -827,7 +846,7 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
     p.tiles_m = p.tiles_n = 0;
     p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;      // set by launch_gemm
     p.C2 = nullptr; p.ldc2 = 0; p.aux = nullptr; p.ld_aux = 0; p.f = 0; p.cos_tab = p.sin_tab = nullptr;
-    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0;
+    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0; p.dbg = 0;
     if (pair) return launch_gemm2<EPI_PLAIN>(ta, tb, p, stream, sms);
     switch (bn) {
         case 256: return launch_gemm<256>(ta, tb, p, stream, sms);
@@ -850,7 +869,7 @@ static int fused_common(GemmParams& p, const void* A, long long lda, const void*
     p.act = 0; p.out_fp32 = 0; p.accumulate = 0; p.alpha = 1.0f; p.tiles_m = p.tiles_n = 0;
     p.raster_mode = 0; p.group = 1; p.a_policy = p.b_policy = kEvictNormal; p.c_stream = 0;
     p.C2 = nullptr; p.ldc2 = 0; p.aux = nullptr; p.ld_aux = 0; p.f = 0; p.cos_tab = p.sin_tab = nullptr;
-    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0;
+    p.rope_L = 1; p.rope_pos0 = 0; p.rope_cols = 0; p.dbg = 0;
     return ESB_OK;
 }
 

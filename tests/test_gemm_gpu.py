@@ -294,9 +294,10 @@ def test_gemm_nn_data_gradient_form(M, Kc, N):
     got = ops.gemm_nn(a, w)
     ref = a.float() @ w.float()
     assert (got.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
-    nt = ops.gemm(a, w.t().contiguous())
-    assert (got.float() - nt.float()).abs().max() <= 8e-3 * ref.abs().max()        # at most a bf16 rounding flip apart
-    assert (got != nt).float().mean() < 1e-2
+    if Kc % 8 == 0:                                                          # the NT kernel needs a 16-byte-aligned row pitch
+        nt = ops.gemm(a, w.t().contiguous())
+        assert (got.float() - nt.float()).abs().max() <= 8e-3 * ref.abs().max()    # at most a bf16 rounding flip apart
+        assert (got != nt).float().mean() < 1e-2
 
 
 def test_gemm_dswiglu_on_the_down_proj_parameter_itself():
