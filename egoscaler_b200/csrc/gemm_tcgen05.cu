@@ -64,7 +64,7 @@ struct GemmParams {
     const __nv_bfloat16* cos_tab;
     const __nv_bfloat16* sin_tab;
     int rope_L, rope_pos0, rope_cols;
-    int dbg;                  // CTA-pair kernel experiments (ESB_GEMM2_DBG): bit 0 full barrier without the peer's arrive, bit 1 spin on test_wait
+    int dbg;                  // CTA-pair kernel experiments (ESB_GEMM2_DBG): bit 0 peer also arrives on full[s], bit 1 spin on test_wait, bit 2 per-thread tempty arrives
 };
 enum : int { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_DSWIGLU = 2, EPI_ROPE = 3 };
 
@@ -519,10 +519,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 // reads A from both CTAs and gives every SM the B half it does not hold through the pair's shared-memory path: half the B
 // traffic from L2 and half the shared-memory operand bytes per flop of the single-CTA kernel (the step is
 // power-capped, so bytes per flop are the lever).  Accumulators: 128 lanes x 256 columns in EACH CTA's TMEM, two stages.
-//   full[s]   (leader)  : count 2 = leader's arrive.expect_tx(64 KB) + the peer's remote arrive; both CTAs' TMA credit it
+//   full[s]   (leader)  : count 1 = the leader's arrive.expect_tx(64 KB); both CTAs' TMA credit their bytes to it.  (A second,
+//                         remote arrive by the peer per stage - DeepGEMM's form - measured 640 TF/s instead of 1250: the phase
+//                         cannot complete before the leader's own arrive anyway, and the peer never runs a stage ahead because
+//                         it waits for the multicast empty[s] first.)
 //   empty[s]  (both)    : tcgen05.commit multicast to both CTAs once the MMAs reading stage s retired
 //   tfull[a]  (both)    : tcgen05.commit multicast - accumulator stage a complete
-//   tempty[a] (leader)  : count 256 = the epilogue threads of both CTAs (the peer arrives remotely)
+//   tempty[a] (leader)  : count 8 = one elected lane of each epilogue warp of both CTAs (the peer's four arrive remotely)
 ESB_DEVICE void mbar_wait_dbg(int spin, uint64_t* bar, uint32_t parity) {
     if (!spin) { mbar_wait(bar, parity); return; }
     uint32_t done = 0;
@@ -564,12 +567,12 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < P2_STAGES; ++i) {
-            mbar_init(&full_bar[i], (p.dbg & 1) ? 1 : 2);
+            mbar_init(&full_bar[i], (p.dbg & 1) ? 2 : 1);
             mbar_init(&empty_bar[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 256);
+            mbar_init(&tmem_empty[i], (p.dbg & 4) ? 256 : 8);
         }
         fence_barrier_init();
     }
@@ -600,7 +603,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
                     if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * P2_STAGE_BYTES);
                     tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
                     tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], kb * BK, nb, p.b_policy);
-                    if (rank != 0 && !(p.dbg & 1)) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
+                    if (rank != 0 && (p.dbg & 1)) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
                     if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -653,7 +656,12 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
             epilogue_tile<BN, EPI>(p, t_addr, row, row_ok, n0);
             tc_fence_before();
-            mbar_arrive_cluster(leader_tempty0 + static_cast<uint32_t>(acc) * 8u);
+            if (p.dbg & 4) {
+                mbar_arrive_cluster(leader_tempty0 + static_cast<uint32_t>(acc) * 8u);
+            } else {                                   // one arrive per warp: a remote mbarrier arrive costs ~100x a local one
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(leader_tempty0 + static_cast<uint32_t>(acc) * 8u);
+            }
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1u;
         }

@@ -175,7 +175,10 @@ def _env_flag(name: str, default: bool) -> bool:
 
 
 fuse_swiglu = _env_flag("ESB_FUSE_SWIGLU", True)        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
-fuse_dswiglu = _env_flag("ESB_FUSE_DSWIGLU", True)      # d(act) GEMM + dSwiGLU              (esb_gemm_dswiglu_bf16)
+# d(act) GEMM + dSwiGLU (esb_gemm_dswiglu_bf16): bit-identical, but OFF - the epilogue has to read gate|up with one row per thread
+# (TMEM lane = row), 32 lines per load instruction; measured 620 / 1003 / 1243 us per layer in three variants against 439-534 us
+# for GEMM + silu_mul_bwd (profiles/r02_fused_bench_*.txt).  Needs the gate|up tile staged through shared memory to pay.
+fuse_dswiglu = _env_flag("ESB_FUSE_DSWIGLU", False)
 fuse_rope = _env_flag("ESB_FUSE_ROPE", True)            # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
 fuse_rope_bwd = _env_flag("ESB_FUSE_ROPE_BWD", True)    # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope)
 
