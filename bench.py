@@ -414,6 +414,10 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
             ref = tr.grad[name]
         ref = ref.double() * ref_scale
         den = float(ref.norm())
+        if name.endswith(".bias") and name[:-5] + ".weight" in tr.grad:
+            # a bias in front of a train-mode BatchNorm has a structurally zero gradient (round-off only): measure it against
+            # the scale of its module's weight gradient instead of against itself
+            den = max(den, 5e-3 * float(tr.grad[name[:-5] + ".weight"].double().norm()) * ref_scale)
         if den == 0.0:
             continue
         rel = float((g.double() - ref).norm()) / den

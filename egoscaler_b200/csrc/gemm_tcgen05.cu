@@ -67,6 +67,7 @@ struct GemmParams {
     int dbg;                  // CTA-pair kernel experiments (ESB_GEMM2_DBG): bit 0 peer also arrives on full[s], bit 1 spin on test_wait, bit 2 per-thread tempty arrives
 };
 enum : int { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_DSWIGLU = 2, EPI_ROPE = 3 };
+static_assert(EPI_DSWIGLU == 2, "GemmSmem keys its staging buffers on this value");
 
 ESB_DEVICE void tile_coords(const GemmParams& p, int t, int& tm, int& tn) {
     if (p.raster_mode == 0) {
@@ -86,14 +87,19 @@ ESB_DEVICE void tile_coords(const GemmParams& p, int t, int& tm, int& tn) {
     }
 }
 
-template <int BN>
+constexpr int EPI_DSWIGLU_ID = 2;
+template <int BN, int EPI = 0>
 struct GemmSmem {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    // the dSwiGLU epilogue stages the saved gate|up tile through shared memory (two buffers of [128 rows x 64 cols] gate + up =
+    // 32 KB each, TMA-loaded by warp 3): one operand stage fewer pays for them
+    static constexpr int STG_BUF_BYTES = 2 * BM * 64 * 2;
+    static constexpr int STG_BYTES = (EPI == EPI_DSWIGLU_ID) ? 2 * STG_BUF_BYTES : 0;
+    static constexpr int STAGES = (EPI == EPI_DSWIGLU_ID) ? 3 : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
     static constexpr int BAR_BYTES = 1024;
-    static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024;   // +1024 alignment slack
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + STG_BYTES + BAR_BYTES + 1024;   // +1024 alignment slack
 };
 
 // bf16 stores of 32 consecutive columns of one row (vector path when aligned and complete)
@@ -356,6 +362,58 @@ ESB_DEVICE void epilogue_tile(const GemmParams& p, const uint32_t t_addr, const 
     }   // EPI_PLAIN
 }
 
+// dSwiGLU epilogue with the gate|up tile staged through shared memory: warp 3 TMA-loads [128 rows x 64 cols] of gate and of up
+// (128B swizzle) two groups ahead; each epilogue thread reads ITS row (128 bytes per stream, 16-byte units XOR-swizzled by row & 7)
+// instead of issuing 32-line global loads.  Arithmetic identical to silu_mul_bwd_kernel / epilogue_tile<EPI_DSWIGLU>.
+template <int BN>
+ESB_DEVICE void epilogue_dswiglu_staged(const GemmParams& p, const uint32_t t_addr, const int row, const bool row_ok, const int n0,
+                                        const int r_in_tile, uint8_t* stg, uint64_t* gu_full, uint64_t* gu_empty, uint32_t& gcount,
+                                        const int lane) {
+    constexpr int STG_BUF = 2 * BM * 64 * 2;
+    __nv_bfloat16* dgu = reinterpret_cast<__nv_bfloat16*>(p.C2);
+    const bool v_out = ((p.ldc2 & 7) == 0) && ((p.f & 7) == 0) && ((reinterpret_cast<uintptr_t>(dgu) & 15) == 0);
+#pragma unroll 1
+    for (int g = 0; g < BN / 64; ++g, ++gcount) {
+        const int buf = static_cast<int>(gcount & 1u);
+        mbar_wait(&gu_full[buf], (gcount >> 1) & 1u);
+        const uint8_t* sg = stg + buf * STG_BUF + r_in_tile * 128;
+        const uint8_t* su = sg + BM * 128;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int col0 = n0 + g * 64 + h * 32;
+            if (col0 < p.N) {                                            // warp-uniform
+                uint32_t r[32];
+                tmem_ld_32x32(t_addr + static_cast<uint32_t>(g * 64 + h * 32), r);
+                tmem_ld_wait();
+                const int ncols = min(32, p.N - col0);
+                uint32_t qg[16], qu[16], og[16], ou[16];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int unit = ((h * 4 + u) ^ (r_in_tile & 7)) << 4;
+                    const uint4 a = *reinterpret_cast<const uint4*>(sg + unit);
+                    const uint4 b = *reinterpret_cast<const uint4*>(su + unit);
+                    qg[u * 4 + 0] = a.x; qg[u * 4 + 1] = a.y; qg[u * 4 + 2] = a.z; qg[u * 4 + 3] = a.w;
+                    qu[u * 4 + 0] = b.x; qu[u * 4 + 1] = b.y; qu[u * 4 + 2] = b.z; qu[u * 4 + 3] = b.w;
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 gv = unpack_bf16x2(qg[j]), uv = unpack_bf16x2(qu[j]);
+                    const float2 dv = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])));
+                    const float s0 = 1.0f / (1.0f + __expf(-gv.x)), s1 = 1.0f / (1.0f + __expf(-gv.y));
+                    og[j] = pack_bf16x2(dv.x * uv.x * s0 * (1.0f + gv.x * (1.0f - s0)), dv.y * uv.y * s1 * (1.0f + gv.y * (1.0f - s1)));
+                    ou[j] = pack_bf16x2(dv.x * gv.x * s0, dv.y * gv.y * s1);
+                }
+                if (row_ok) {
+                    store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + col0, og, ncols, v_out, p.c_stream);
+                    store_row32_bf16(dgu + static_cast<long long>(row) * p.ldc2 + p.f + col0, ou, ncols, v_out, p.c_stream);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&gu_empty[buf]);                      // this warp is done with the staging buffer
+    }
+}
+
 // TA / TB = true: that operand is stored with the CONTRACTION index outermost (A [Kc, M] / B [Kc, N] row-major) instead of
 // innermost.  TA & TB: C = A^T . B, the weight-gradient contraction dW = dY^T . X on the activations exactly as they sit in HBM;
 // TB only: C = A . B with B = a weight [in = Kc, out = N]... i.e. the data-gradient dX = dY . W on the state_dict layout - no
@@ -365,21 +423,24 @@ ESB_DEVICE void epilogue_tile(const GemmParams& p, const uint32_t t_addr, const 
 template <int BN, int EPI, bool TA = false, bool TB = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                         const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tma_c, const GemmParams p) {
     static_assert(EPI == EPI_PLAIN || BN == 256, "fused epilogues are built on the 128x256 tile");
     static_assert(!TA || EPI == EPI_PLAIN, "a transposed A operand comes with the plain epilogue only");
     static_assert(!TB || EPI == EPI_PLAIN || EPI == EPI_DSWIGLU, "a transposed B operand: plain or dSwiGLU epilogue");
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;      // output columns per tile
-    using S = GemmSmem<BN>;
+    using S = GemmSmem<BN, EPI>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* tiles = smem;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::STAGES * S::STAGE_BYTES);
+    uint8_t* stg = smem + S::STAGES * S::STAGE_BYTES;                                  // dSwiGLU gate|up staging (else empty)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stg + S::STG_BYTES);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + S::STAGES;
     uint64_t* tmem_full = bars + 2 * S::STAGES;
     uint64_t* tmem_empty = bars + 2 * S::STAGES + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S::STAGES + 4);
+    uint64_t* gu_full = bars + 2 * S::STAGES + 6;
+    uint64_t* gu_empty = bars + 2 * S::STAGES + 8;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -389,6 +450,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_a);
         tma_prefetch_desc(&tma_b);
+        if constexpr (EPI == EPI_DSWIGLU) tma_prefetch_desc(&tma_c);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < S::STAGES; ++i) {
@@ -398,6 +460,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 128);
+            mbar_init(&gu_full[i], 1);
+            mbar_init(&gu_empty[i], 4);
         }
         fence_barrier_init();
     }
@@ -483,11 +547,32 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                 if (acc == 0) acc_phase ^= 1u;
             }
         }
+    } else if (warp == 3) {
+        if constexpr (EPI == EPI_DSWIGLU) {
+            if (lane == 0) {
+                // ===================== gate|up loader: [128 rows x 64 cols] of gate and of up per group, two groups ahead
+                uint32_t gc = 0;
+                for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                    int tm, tn;
+                    tile_coords(p, t, tm, tn);
+                    const int m0 = tm * BM, n0 = tn * BN;
+                    for (int g = 0; g < BN / 64; ++g, ++gc) {
+                        const int buf = static_cast<int>(gc & 1u);
+                        mbar_wait(&gu_empty[buf], ((gc >> 1) & 1u) ^ 1u);
+                        uint8_t* dst = stg + buf * S::STG_BUF_BYTES;
+                        mbar_arrive_expect_tx(&gu_full[buf], S::STG_BUF_BYTES);
+                        tma_load_2d(dst, &tma_c, &gu_full[buf], n0 + g * 64, m0);
+                        tma_load_2d(dst + BM * 128, &tma_c, &gu_full[buf], p.f + n0 + g * 64, m0);
+                    }
+                }
+            }
+        }
     } else if (warp >= 4) {
         // ===================== epilogue: TMEM -> registers -> global
         const int q = warp & 3;                            // TMEM lane quarter this warp may access
         int acc = 0;
         uint32_t acc_phase = 0;
+        [[maybe_unused]] uint32_t gcount = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             int tm, tn;
             tile_coords(p, t, tm, tn);
@@ -497,7 +582,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < p.M;
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
-            epilogue_tile<BN, EPI>(p, t_addr, row, row_ok, n0);
+            if constexpr (EPI == EPI_DSWIGLU)
+                epilogue_dswiglu_staged<BN>(p, t_addr, row, row_ok, n0, q * 32 + lane, stg, gu_full, gu_empty, gcount, lane);
+            else
+                epilogue_tile<BN, EPI>(p, t_addr, row, row_ok, n0);
             tc_fence_before();
             mbar_arrive(&tmem_empty[acc]);
             acc ^= 1;
@@ -765,8 +853,9 @@ static void choose_walk(GemmParams& p, int bm, int bn, int bn_out, int c_mult) {
 }
 
 template <int BN, int EPI = EPI_PLAIN, bool TA = false, bool TB = false>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
-    using S = GemmSmem<BN>;
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms,
+                       const CUtensorMap* tc = nullptr) {
+    using S = GemmSmem<BN, EPI>;
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
     static bool attr_set = false;
     if (!attr_set) {
@@ -780,7 +869,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
     choose_walk(p, BM, BN, BN_OUT, (EPI == EPI_SWIGLU || EPI == EPI_DSWIGLU) ? 2 : 1);
     const int tiles = p.tiles_m * p.tiles_n;
     const int grid = tiles < sms ? tiles : sms;
-    gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, p);
+    gemm_bf16_tcgen05_kernel<BN, EPI, TA, TB><<<grid, GEMM_THREADS, S::TOTAL, stream>>>(ta, tb, tc ? *tc : ta, p);
     return check_launch("gemm_bf16_tcgen05");
 }
 
@@ -916,8 +1005,15 @@ int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long 
     if (rc) return rc;
     p.aux = static_cast<const __nv_bfloat16*>(gu); p.ld_aux = ld_gu; p.C2 = dgu; p.ldc2 = ld_dgu; p.f = f;
     if (pair) return launch_gemm2<EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
-    if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, device_sm_count());
-    return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
+    if ((ld_gu & 7) || (reinterpret_cast<uintptr_t>(gu) & 15)) {
+        set_last_error("gemm_dswiglu_bf16: gu must be 16-byte aligned with a leading dimension that is a multiple of 8");
+        return ESB_ERR_INVALID_ARG;
+    }
+    CUtensorMap tc;                                            // saved gate|up [M, 2f]: box = 64 columns x 128 rows for the staged epilogue
+    rc = make_tma_2d_bf16(&tc, gu, M, 2LL * f, ld_gu, BM);
+    if (rc) return rc;
+    if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, device_sm_count(), &tc);
+    return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count(), &tc);
 }
 
 // C [M, N] = rope(A . W^T): heads of 128 columns starting below rope_cols are rotated at position pos0 + (row % L)
