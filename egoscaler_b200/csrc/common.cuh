@@ -202,8 +202,11 @@ ESB_DEVICE uint32_t mapa_shared(uint32_t smem_addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
     return r;
 }
+// Remote arrive in CUTLASS' form (ClusterBarrier::arrive(cta_id)): default semantics (.release at CTA scope).  The explicit
+// .release.cluster form makes the arriving thread wait until all its earlier global stores are visible cluster-wide - measured
+// ~5 us per arrive from an epilogue warp, which halved the CTA-pair GEMM when it sat on the per-stage full barrier.
 ESB_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // 2-SM TMA load: data lands in THIS CTA's shared memory, the transaction bytes are credited to the mbarrier at the same offset
 // in the pair's leader CTA (peer bit of the shared::cluster address cleared - CUTLASS Sm100MmaPeerBitMask).
