@@ -405,7 +405,12 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
         ref_scale = float(world)                                          # global mean * world == sum of equal-count shard means
     tr.sparse_embed_exchange = sparse
     worst, worst_name, n_cmp = 0.0, "", 0
+    # conv biases directly in front of a train-mode BatchNorm have a structurally zero gradient (the batch mean removes them):
+    # both sides hold round-off only, so a relative comparison is meaningless (tests/test_variants_gpu.py bounds their size)
+    skipped = [n for n in got if tr.enc_train is not None and n.endswith(("encoder.first_conv.0.bias", "encoder.second_conv.0.bias"))]
     for name, g in got.items():
+        if name in skipped:
+            continue
         if name.startswith("unit"):
             u = int(name[4:name.index(":")])
             k, li, _ = tr.trunk_units[u]
@@ -452,7 +457,7 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
             "max_rel_l2": round(float(wmax[0]), 6), "worst_tensor": worst_all[1], "tensors_compared_rank0": n_cmp,
             "tolerance": 2e-2, "ok": bool(float(wmax[0]) <= 2e-2 and identical),
             "loss_mean_over_ranks": round(float(wsum[1]) / world, 5), "loss_single_gpu_global_batch": round(loss_ref, 5),
-            "equal_token_counts": equal_counts, "weights_bit_identical_after_step": identical,
+            "equal_token_counts": equal_counts, "weights_bit_identical_after_step": identical, "skipped_structurally_zero": skipped,
             "reference": ("per-shard recomputation on one GPU (per-rank BatchNorm statistics, no SyncBN)" if tr.enc_train is not None
                           else "one GPU on the concatenated global batch")}
 
