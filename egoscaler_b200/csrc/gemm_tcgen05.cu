@@ -561,8 +561,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                         mbar_wait(&gu_empty[buf], ((gc >> 1) & 1u) ^ 1u);
                         uint8_t* dst = stg + buf * S::STG_BUF_BYTES;
                         mbar_arrive_expect_tx(&gu_full[buf], S::STG_BUF_BYTES);
-                        tma_load_2d(dst, &tma_c, &gu_full[buf], n0 + g * 64, m0);
-                        tma_load_2d(dst + BM * 128, &tma_c, &gu_full[buf], p.f + n0 + g * 64, m0);
+                        // read once: evict-first, so the 245 MB of gate|up do not push the GEMM operands out of L2 (first ncu
+                        // capture: L2 hit rate 68 % against 86 % for the plain launch, 834 MB of DRAM reads)
+                        tma_load_2d_hint(dst, &tma_c, &gu_full[buf], n0 + g * 64, m0, kEvictFirst);
+                        tma_load_2d_hint(dst + BM * 128, &tma_c, &gu_full[buf], p.f + n0 + g * 64, m0, kEvictFirst);
                     }
                 }
             }
