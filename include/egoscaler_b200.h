@@ -88,7 +88,7 @@ int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int6
 
 /* Route the large NT GEMMs (M >= 1024, N >= 512; plain and fused epilogues) through the CTA-pair kernel: clusters of two CTAs,
  * tcgen05.mma.cta_group::2 on 256 x 256 tiles, each SM stages half of the weight tile.  Returns the previous setting.  Default:
- * environment variable ESB_GEMM_2CTA (0). */
+ * on (environment variable ESB_GEMM_2CTA=0 turns it off). */
 int esb_set_gemm_2cta(int on);
 
 /* Weight-streaming variant for the cached single-token decode step (M = sequences per GPU <= 64):

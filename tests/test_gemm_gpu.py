@@ -310,8 +310,6 @@ def test_gemm_dswiglu_on_the_down_proj_parameter_itself():
     assert (got.float() - ref.float()).abs().max() <= 8e-3 * ref.float().abs().max() and (got != ref).float().mean() < 1e-2
 
 
-@pytest.mark.skipif(os.environ.get("ESB_TEST_2CTA", "0") != "1",
-                    reason="opt-in (ESB_TEST_2CTA=1): the CTA-pair kernel is off by default and is validated through tools/gemm2_check.py")
 def test_cta_pair_gemm_matches_single_cta_kernel():
     """tcgen05.mma.cta_group::2 kernel (clusters of two CTAs, 256 x 256 tile, esb_set_gemm_2cta) == the single-CTA kernel bit for
     bit on plain / residual / fp32 / SwiGLU / dSwiGLU / RoPE epilogues.  Runs in a subprocess with a timeout: a mistake in the
