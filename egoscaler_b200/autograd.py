@@ -37,9 +37,12 @@ class TrainCtx:
     enc_saved: Optional[dict] = None                    # train-mode point encoder activations (--unfreeze_pc_encoder)
 
 
-def forward_hidden_train(model, tokens, attention_masks, pcrgbs, fps_start=None, drop_u=None, train_encoder: bool = True):
+def forward_hidden_train(model, tokens, attention_masks, pcrgbs, fps_start=None, drop_u=None, train_encoder: bool = True,
+                         out_rows=None):
     """Point encoder -> projector -> splice -> N LLaMA layers with everything the backward needs kept.  Returns
-    (hidden [B*L, d] bf16 before the final norm, TrainCtx).  pointllm.py:106-178."""
+    (hidden [B*L, d] bf16 before the final norm, TrainCtx).  pointllm.py:106-178.  ``out_rows = (r0, r1)``: the caller only reads
+    these rows of every sample; the hidden states may then come back as [B*(r1-r0), d] (llm.LlamaTrunk._top_layer_rows) and the
+    gradient handed to ``backward_from_hidden`` must have the same shape."""
     dev = model.dev
     tokens = tokens.to(dev)
     B, L = tokens.shape
@@ -49,7 +52,7 @@ def forward_hidden_train(model, tokens, attention_masks, pcrgbs, fps_start=None,
     if enc_train is not None:
         enc_train["drop_u"] = drop_u                    # injected DropPath uniforms [depth, 2, B] (None: drawn on device)
     h, ctx.splice_pos = model.hidden_states(tokens, attention_masks, pcrgbs, fps_start, None, ctx.saved, ctx.proj_saved,
-                                            enc_train=enc_train)
+                                            enc_train=enc_train, out_rows=out_rows)
     if enc_train is not None:
         ctx.enc_saved = enc_train.pop("saved", None)
     return h, ctx

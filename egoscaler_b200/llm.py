@@ -108,6 +108,7 @@ class LayerSaved:
     h: torch.Tensor
     rstd2: torch.Tensor
     gu: torch.Tensor
+    rows: Optional[tuple] = None       # (r0, r1): o / lse / h / rstd2 / gu cover only these rows of every sample (top layer)
 
 
 class LlamaTrunk:
@@ -120,9 +121,12 @@ class LlamaTrunk:
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], pos0: int = 0,
                 cache: Optional[KVCache] = None, saved: Optional[List[LayerSaved]] = None,
-                pos_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+                pos_dev: Optional[torch.Tensor] = None, out_rows: Optional[tuple] = None) -> torch.Tensor:
         """x [B*L, d] bf16 -> hidden [B*L, d] (before the final norm).  kmask uint8 [B, >= pos0+L] or None.
-        With ``cache``: K/V of these L tokens are written at pos0.. and attention runs over cache[:pos0+L]."""
+        With ``cache``: K/V of these L tokens are written at pos0.. and attention runs over cache[:pos0+L].
+        ``out_rows = (r0, r1)``: the caller reads only rows r0..r1-1 of every sample (the loss rows of train.py:174) - the TOP
+        layer then computes its attention output, o-proj and MLP for those rows only (its K / V still cover all positions) and
+        the result is [B*(r1-r0), d].  Same arithmetic per row; ~1.6 % of a full-size training step."""
         c = self.cfg
         d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
         attn_decode = cache is not None and L == 1 and (pos0 > 0 or pos_dev is not None)
@@ -135,7 +139,11 @@ class LlamaTrunk:
         if decode:
             for w in self.layers:          # decode-layout copies exist before the first kernel of the step is queued, so no
                 w.ensure_tiled(False)      # skinny GEMM is ever launched right behind the kernel that wrote its weights
+        sub_ok = (out_rows is not None and cache is None and not decode and hd == 128 and ops.top_layer_rows_enabled
+                  and 0 <= out_rows[0] < out_rows[1] <= L and (out_rows[1] - out_rows[0]) < L)
         for li, w in enumerate(self.layers):
+            if sub_ok and li == len(self.layers) - 1:
+                return self._top_layer_rows(x, w, B, L, kmask, pos0, saved, out_rows)
             if saved is not None:
                 xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True)
             else:
@@ -184,6 +192,38 @@ class LlamaTrunk:
             x = out
         return x
 
+    def _top_layer_rows(self, x, w: LayerWeights, B: int, L: int, kmask, pos0: int, saved, rows) -> torch.Tensor:
+        """The last decoder layer when only rows r0..r1-1 of every sample are read afterwards: queries, o-proj and MLP on
+        those rows; keys / values (and therefore the q|k|v projection) on all L positions."""
+        c = self.cfg
+        d, H, hd = c.hidden_size, c.num_attention_heads, c.head_dim
+        r0, r1 = rows
+        Tn = r1 - r0
+        keep = saved is not None
+        xn, rstd1 = ops.rmsnorm(x, w.ln1, c.rms_norm_eps, want_rstd=True) if keep else (ops.rmsnorm(x, w.ln1, c.rms_norm_eps), None)
+        if ops.fuse_rope:
+            qkv = ops.gemm_rope(xn, w.wqkv, self.cos, self.sin, L, pos0, 2 * d, hd)
+        else:
+            qkv = ops.gemm(xn, w.wqkv)
+            ops.rope_(qkv, L, 2 * H, hd, self.cos, self.sin, pos0)
+        q4 = qkv.view(B, L, 3, H, hd)
+        r = ops.attention(q4[:, r0:r1, 0], q4[:, :, 1], q4[:, :, 2], causal=True, kmask=kmask, q_pos0=pos0 + r0, want_lse=keep)
+        o, lse = r if keep else (r, None)
+        o = o.view(B * Tn, d)
+        xs = torch.empty(B, Tn, d, device=x.device, dtype=torch.bfloat16)
+        ops.copy_rows(x.view(B, L, d)[:, r0:r1, :], xs)
+        h = ops.gemm(o, w.wo, residual=xs.view(B * Tn, d))
+        hn, rstd2 = ops.rmsnorm(h, w.ln2, c.rms_norm_eps, want_rstd=True) if keep else (ops.rmsnorm(h, w.ln2, c.rms_norm_eps), None)
+        if ops.fuse_swiglu and B * Tn > ops.SKINNY_MAX_M:
+            a, gu = ops.gemm_swiglu(hn, w.wgu, want_gu=keep)
+        else:
+            gu = ops.gemm(hn, w.wgu)
+            a = ops.silu_mul(gu)
+        out = ops.gemm(a, w.wdown, residual=h)
+        if keep:
+            saved.append(LayerSaved(x, rstd1, qkv, o, lse, h, rstd2, gu, rows=(r0, r1)))
+        return out
+
     def _decode_step_folded(self, x: torch.Tensor, B: int, kmask, pos0: int, cache: KVCache, pos_dev) -> torch.Tensor:
         """The cached single-token step with every RMSNorm folded around the Linear that consumes it (7 kernels per layer
         instead of 9):  Linear(norm(x)) = rstd(x) * (x . (W * g)^T) - g lives in the decode-layout weight copy, rstd is applied
@@ -225,6 +265,8 @@ class LlamaTrunk:
             w, s = self.layers[li], saved[li]
             if not nn_dgrad:
                 w.ensure_transposed()
+            rows = s.rows                     # top layer computed on a row range only: dout is [B*(r1-r0), d] until its attention
+            Lq = L if rows is None else rows[1] - rows[0]
             if ops.fuse_dswiglu and dout.shape[0] > ops.SKINNY_MAX_M:
                 # [T, 2f]: d(act) GEMM + dSwiGLU, one launch
                 dgu = ops.gemm_dswiglu(dout, w.wdown, s.gu, w_is_down_proj=True) if nn_dgrad else ops.gemm_dswiglu(dout, w.wdownT, s.gu)
@@ -242,8 +284,8 @@ class LlamaTrunk:
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout)
             do = ops.gemm_nn(dh, w.wo) if nn_dgrad else ops.gemm(dh, w.woT)       # [T, d]
             fused_bwd = ops.fuse_rope_bwd and hd == 128
-            dqkv = ops.attention_bwd(s.qkv.view(B, L, 3, H, hd), s.o.view(B, L, d), s.lse, do.view(B, L, d), causal=True,
-                                     kmask=kmask, rope=(self.cos, self.sin) if fused_bwd else None)      # [T, 3d]
+            dqkv = ops.attention_bwd(s.qkv.view(B, L, 3, H, hd), s.o.view(B, Lq, d), s.lse, do.view(B, Lq, d), causal=True,
+                                     kmask=kmask, rope=(self.cos, self.sin) if fused_bwd else None, q_rows=rows)      # [T, 3d]
             if not fused_bwd:
                 ops.rope_(dqkv.view(B * L, 3 * d), L, 2 * H, hd, self.cos, self.sin, 0, inverse=True)
             dqkv2 = dqkv.view(B * L, 3 * d)
@@ -252,9 +294,16 @@ class LlamaTrunk:
                 xn = ops.rmsnorm(s.x, w.ln1, c.rms_norm_eps)
                 ops.gemm_tn(dh, s.o, out=wgrad["wo"][li], accumulate=True)
                 ops.gemm_tn(dqkv2, xn, out=wgrad["wqkv"][li], accumulate=True)
-                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh, dw=wgrad["ln1"][li])
+            if rows is not None:              # the residual gradient exists on the row range only: scatter it into a full tensor
+                dres = torch.zeros(B, L, d, device=dh.device, dtype=torch.bfloat16)
+                ops.copy_rows(dh.view(B, Lq, d), dres[:, rows[0]:rows[1], :])
+                dres = dres.view(B * L, d)
             else:
-                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dh)
+                dres = dh
+            if wgrad is not None:
+                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dres, dw=wgrad["ln1"][li])
+            else:
+                dout = ops.rmsnorm_bwd(dxn, s.x, w.ln1, s.rstd1, dres=dres)
             saved[li] = None                                                      # free activations as we go
             if on_layer_done is not None:
                 on_layer_done(li)                                                 # e.g. start this layer's gradient reduction

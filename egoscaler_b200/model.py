@@ -331,7 +331,7 @@ class TrajPointLLMForCausalLM(ParamTree):
         return attention_mask.to(dev).to(torch.uint8).contiguous()
 
     def hidden_states(self, input_ids, attention_mask=None, point_clouds=None, fps_start=None, cache: Optional[KVCache] = None,
-                      saved=None, proj_saved=None, splice_pos=None, pos_dev=None, enc_train=None):
+                      saved=None, proj_saved=None, splice_pos=None, pos_dev=None, enc_train=None, out_rows=None):
         """Everything up to (not including) the final norm.  Returns (hidden [B*L, d], splice_pos)."""
         input_ids = input_ids.to(self.dev)
         B, L = input_ids.shape
@@ -343,7 +343,7 @@ class TrajPointLLMForCausalLM(ParamTree):
             feats = self.point_features(point_clouds, fps_start, proj_saved, enc_train)
         x = ops.embed_splice(input_ids, self.model.embed_tokens.weight.detach(), feats, splice_pos if feats is not None else None,
                              self.point_backbone_config["point_token_len"])
-        h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved, pos_dev)
+        h = self.trunk.forward(x, B, L, self._kmask(attention_mask, self.dev), pos0, cache, saved, pos_dev, out_rows=out_rows)
         if cache is not None:
             cache.length = cache.length + L
         return h, splice_pos

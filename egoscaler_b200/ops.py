@@ -180,6 +180,7 @@ fuse_swiglu = _env_flag("ESB_FUSE_SWIGLU", True)        # gate|up GEMM + silu*mu
 # for GEMM + silu_mul_bwd (profiles/r02_fused_bench_*.txt).  Needs the gate|up tile staged through shared memory to pay.
 fuse_dswiglu = _env_flag("ESB_FUSE_DSWIGLU", False)
 fuse_rope = _env_flag("ESB_FUSE_ROPE", True)            # q|k|v GEMM + rotary embedding       (esb_gemm_rope_bf16; head_dim 128 only)
+top_layer_rows_enabled = _env_flag("ESB_TOP_LAYER_ROWS", True)   # training: top decoder layer on the loss rows only (llm._top_layer_rows)
 fuse_rope_bwd = _env_flag("ESB_FUSE_ROPE_BWD", True)    # attention backward + transposed rotary embedding on dq / dk (esb_attn_bwd_rope)
 
 
@@ -626,21 +627,27 @@ def knn_group(pts: torch.Tensor, centers: torch.Tensor, K: int, out_ld: int = 64
 
 
 def attention_bwd(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, dout: torch.Tensor, causal: bool,
-                  kmask: Optional[torch.Tensor] = None, scale: Optional[float] = None, rope=None) -> torch.Tensor:
+                  kmask: Optional[torch.Tensor] = None, scale: Optional[float] = None, rope=None, q_rows=None) -> torch.Tensor:
     """Self-attention backward on a packed projection: qkv [B,L,3,H,hd], o/dout [B,L,H*hd], lse [B,H,L]
     -> dqkv [B,L,3,H,hd] (gradients w.r.t. the post-RoPE q,k and v)."""
     _chk(qkv, torch.bfloat16, "attention_bwd.qkv"); _chk(dout, torch.bfloat16, "attention_bwd.dout")
     B, L, three, H, hd = qkv.shape
     assert three == 3 and qkv.is_contiguous() and o.stride(2) == 1 and dout.stride(2) == 1
-    dqkv = torch.empty_like(qkv)
-    dvec = torch.empty(2 * B * H * ((L + 63) // 64 * 64), device=qkv.device, dtype=torch.float32)   # (lse, D) workspace
+    # q_rows = (r0, r1): only these query rows of every sample took part in the forward (o / lse / dout have r1 - r0 rows); dq of the
+    # other rows is zero, dk / dv cover all L keys
+    r0, r1 = (0, L) if q_rows is None else (int(q_rows[0]), int(q_rows[1]))
+    Lq = r1 - r0
+    assert o.shape[1] == Lq and dout.shape[1] == Lq and lse.shape[2] == Lq
+    dqkv = torch.empty_like(qkv) if q_rows is None else torch.zeros_like(qkv)
+    dvec = torch.empty(2 * B * H * ((Lq + 63) // 64 * 64), device=qkv.device, dtype=torch.float32)   # (lse, D) workspace
     bs, rs = qkv.stride(0), qkv.stride(1)
     es = qkv.element_size()
     d = H * hd
-    args = (qkv.data_ptr(), bs, rs, qkv.data_ptr() + d * es, bs, rs, qkv.data_ptr() + 2 * d * es, bs, rs,
+    qoff = r0 * rs * es
+    args = (qkv.data_ptr() + qoff, bs, rs, qkv.data_ptr() + d * es, bs, rs, qkv.data_ptr() + 2 * d * es, bs, rs,
             o.data_ptr(), o.stride(0), o.stride(1), dout.data_ptr(), dout.stride(0), dout.stride(1), lse.data_ptr(),
-            dvec.data_ptr(), dqkv.data_ptr(), bs, rs, dqkv.data_ptr() + d * es, bs, rs, dqkv.data_ptr() + 2 * d * es, bs, rs,
-            _p(kmask), 0 if kmask is None else kmask.stride(0), B, H, L, L, hd, 1 if causal else 0, 0,
+            dvec.data_ptr(), dqkv.data_ptr() + qoff, bs, rs, dqkv.data_ptr() + d * es, bs, rs, dqkv.data_ptr() + 2 * d * es, bs, rs,
+            _p(kmask), 0 if kmask is None else kmask.stride(0), B, H, Lq, L, hd, 1 if causal else 0, r0,
             float(scale if scale is not None else hd ** -0.5))
     if rope is None:
         _l.call("esb_attn_bwd", *args, _stream())

@@ -119,15 +119,20 @@ class Trainer:
         m, cfg = self.model, self.model.cfg
         self._sync = bool(sync) and self.world > 1
         dev = m.dev
-        h, ctx = forward_hidden_train(m, tokens, attention_masks, pcrgbs, fps_start, drop_u)
+        P = int(prompt_len)
+        h, ctx = forward_hidden_train(m, tokens, attention_masks, pcrgbs, fps_start, drop_u, out_rows=(P - 1, tokens.shape[1] - 1))
         tokens = ctx.tokens
         B, L = ctx.B, ctx.L
-        P, d, V = int(prompt_len), cfg.hidden_size, cfg.vocab_size
+        d, V = cfg.hidden_size, cfg.vocab_size
         Tn = L - P
-        # ---- head: rows P-1 .. L-2 only (train.py:174)
-        hs = torch.empty(B, Tn, d, device=dev, dtype=torch.bfloat16)
-        ops.copy_rows(h.view(B, L, d)[:, P - 1:L - 1, :], hs)
-        hs2 = hs.view(B * Tn, d)
+        # ---- head: rows P-1 .. L-2 only (train.py:174); the trunk may already have returned just those rows
+        rows_only = h.shape[0] == B * Tn and Tn != L
+        if rows_only:
+            hs2 = h
+        else:
+            hs = torch.empty(B, Tn, d, device=dev, dtype=torch.bfloat16)
+            ops.copy_rows(h.view(B, L, d)[:, P - 1:L - 1, :], hs)
+            hs2 = hs.view(B * Tn, d)
         norm_w = m.model.norm.weight.detach()
         hn, rstd = ops.rmsnorm(hs2, norm_w, cfg.rms_norm_eps, want_rstd=True)
         lbuf = torch.empty(B * Tn, m.v_pad, device=dev, dtype=torch.bfloat16)
@@ -140,10 +145,14 @@ class Trainer:
         dhn = ops.gemm_nn(logits, m.lm_head.weight.detach()) if ops.gemm_nn_enabled else ops.gemm(logits, m.lm_head_T())
         dhs = ops.rmsnorm_bwd(dhn, hs2, norm_w, rstd, dw=self.grad["model.norm.weight"])
         self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
-        dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)
-        ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
+        if rows_only:
+            dh = dhs
+        else:
+            dh = torch.zeros(B, L, d, device=dev, dtype=torch.bfloat16)
+            ops.copy_rows(dhs.view(B, Tn, d), dh[:, P - 1:L - 1, :])
+            dh = dh.view(B * L, d)
         # ---- trunk backward (data gradients through the frozen layers), embedding scatter, projector, encoder
-        backward_from_hidden(m, ctx, dh.view(B * L, d), self.grad, self.wgrad,
+        backward_from_hidden(m, ctx, dh, self.grad, self.wgrad,
                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None,
                              on_ready=self._reduce_async,
                              embed_exchange=self._embed_exchange if (self.world > 1 and self.sparse_embed_exchange) else None)

@@ -115,3 +115,41 @@ def test_trained_greedy_decode_emits_the_reference_trajectory(trained, graph):
     for b in range(2):
         assert np.array_equal(raw[b].cpu().numpy(), g[f"greedy_poses_raw/{b}"])
         assert np.array_equal(rt2[b].cpu().numpy(), g[f"greedy_poses_rt2/{b}"])
+
+
+def test_top_layer_on_loss_rows_only_equals_the_full_layer():
+    """llm.LlamaTrunk with ``out_rows``: the top layer computed for the loss rows only must give the same hidden rows and the same
+    input gradient as the full computation (frozen trunk and --unfreeze_language_model weight gradients)."""
+    cfg = TrajVLMConfig.tiny_hd128()
+    m = TrajPointLLMForCausalLM(cfg, "cuda", unfreeze_language_model=True)
+    m.load_state_dict(synth.det_state_dict(m.state_dict(), seed=0, round_bf16=True), strict=True)
+    B, L, d, r0, r1 = 2, 260, cfg.hidden_size, 180, 259
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(B * L, d, device="cuda", generator=g).bfloat16()
+    dsub = torch.randn(B * (r1 - r0), d, device="cuda", generator=g).bfloat16()
+    kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+    kmask[1, 50:58] = 0
+    mk = lambda: {k: [torch.zeros(getattr(lw, k).shape, device="cuda", dtype=torch.float32) for lw in m.trunk.layers]
+                  for k in ("wqkv", "wo", "wgu", "wdown", "ln1", "ln2")}
+    # full computation, gradient only on the row range
+    saved = []
+    h_full = m.trunk.forward(x.clone(), B, L, kmask, saved=saved)
+    dfull = torch.zeros(B, L, d, device="cuda", dtype=torch.bfloat16)
+    dfull[:, r0:r1] = dsub.view(B, r1 - r0, d)
+    wg_full = mk()
+    dx_full = m.trunk.backward(dfull.view(B * L, d), B, L, kmask, saved, wgrad=wg_full)
+    # row-range computation
+    saved = []
+    h_sub = m.trunk.forward(x.clone(), B, L, kmask, saved=saved, out_rows=(r0, r1))
+    assert h_sub.shape == (B * (r1 - r0), d) and saved[-1].rows == (r0, r1)
+    wg_sub = mk()
+    dx_sub = m.trunk.backward(dsub.clone(), B, L, kmask, saved, wgrad=wg_sub)
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+    assert rel(h_sub.view(B, r1 - r0, d), h_full.view(B, L, d)[:, r0:r1]) < 5e-3
+    assert rel(dx_sub, dx_full) < 1e-2
+    for k in wg_full:
+        for a, b in zip(wg_sub[k], wg_full[k]):
+            assert rel(a, b) < 1.5e-2, k
+    # inference form
+    h_inf = m.trunk.forward(x.clone(), B, L, kmask, out_rows=(r0, r1))
+    assert rel(h_inf, h_sub) < 5e-3

@@ -423,3 +423,32 @@ def test_embed_rows_pack_and_deterministic_scatter():
     okb = ridb > 0
     expb.index_add_(0, ridb[okb], rowsb[okb].double())
     torch.testing.assert_close(acc.double(), expb, atol=2e-3, rtol=1e-5)
+
+
+def test_attention_bwd_on_a_query_row_range():
+    """ops.attention_bwd(q_rows=(r0, r1)): only rows r0..r1-1 of every sample were queries (the top decoder layer of a training
+    step reads just the loss rows, llm._top_layer_rows) - dq of the other rows is zero, dk / dv cover all keys.  vs fp32 torch."""
+    B, H, hd, L, r0, r1 = 2, 3, 128, 300, 211, 299
+    d = H * hd
+    qkv = rnd(B, L, 3, H, hd, seed=31)
+    kmask = torch.ones(B, L, device="cuda", dtype=torch.uint8)
+    kmask[0, 100:109] = 0
+    q = qkv[:, r0:r1, 0]
+    o, lse = ops.attention(q, qkv[:, :, 1], qkv[:, :, 2], causal=True, kmask=kmask, q_pos0=r0, want_lse=True)
+    qf = qkv.float().requires_grad_(True)
+    ref_o, ref_lse = _attn_ref(qf[:, r0:r1, 0], qf[:, :, 1], qf[:, :, 2], True, kmask, q_pos0=r0)
+    close(o, ref_o, 1.5e-2)
+    assert (lse - ref_lse).abs().max() < 2e-2
+    do = rnd(B, r1 - r0, d, seed=32)
+    ref_o.backward(do.float())
+    dqkv = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask, q_rows=(r0, r1))
+    for j in range(3):
+        close(dqkv[:, :, j], qf.grad[:, :, j], 2.5e-2)
+    assert float(dqkv[:, :r0, 0].abs().max()) == 0.0 and float(dqkv[:, r1:, 0].abs().max()) == 0.0
+    # with the fused inverse rotary embedding == unfused + rope kernel
+    from egoscaler_b200.llm import rope_tables
+    cos, sin = rope_tables(hd, 10000.0, 512, "cuda")
+    ref = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask, q_rows=(r0, r1))
+    ops.rope_(ref.view(B * L, 3 * d), L, 2 * H, hd, cos, sin, 0, inverse=True)
+    got = ops.attention_bwd(qkv, o, lse, do, causal=True, kmask=kmask, q_rows=(r0, r1), rope=(cos, sin))
+    assert torch.equal(got, ref)
