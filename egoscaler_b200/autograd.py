@@ -60,7 +60,8 @@ def forward_hidden_train(model, tokens, attention_masks, pcrgbs, fps_start=None,
 
 def backward_from_hidden(model, ctx: TrainCtx, dh: torch.Tensor, grad: Dict[str, torch.Tensor],
                          wgrad: Optional[Dict[str, List[torch.Tensor]]] = None, on_layer_done: Optional[Callable] = None,
-                         on_ready: Optional[Callable[[List[str]], None]] = None, embed_exchange: Optional[Callable] = None):
+                         on_ready: Optional[Callable[[List[str]], None]] = None, embed_exchange: Optional[Callable] = None,
+                         wgrad_accumulate: bool = True):
     """dh [B*L, d] bf16 = d loss / d hidden (before the final norm).  Accumulates fp32 gradients into ``grad`` (by parameter
     name: embed_tokens, point_proj.*, point_backbone.* when it trains) and ``wgrad`` (packed LLM-layer units, only with
     --unfreeze_language_model).  ``on_ready(names)`` is called as soon as a group of gradients is final (the trainer starts
@@ -70,7 +71,8 @@ def backward_from_hidden(model, ctx: TrainCtx, dh: torch.Tensor, grad: Dict[str,
     cfg = model.cfg
     B, L, d = ctx.B, ctx.L, cfg.hidden_size
     n_point = model.point_backbone_config["point_token_len"]
-    dx = model.trunk.backward(dh, B, L, ctx.kmask, ctx.saved, wgrad=wgrad, on_layer_done=on_layer_done)
+    dx = model.trunk.backward(dh, B, L, ctx.kmask, ctx.saved, wgrad=wgrad, on_layer_done=on_layer_done,
+                              wgrad_accumulate=wgrad_accumulate)
     has_points = ctx.splice_pos is not None and len(ctx.proj_saved) > 0
     dfeats = torch.empty(B, n_point, d, device=dx.device, dtype=torch.bfloat16) if has_points else None
     ops.embed_splice_bwd(ctx.tokens, dx, ctx.splice_pos if has_points else None, n_point,

@@ -252,9 +252,11 @@ class LlamaTrunk:
 
     # ------------------------------------------------------------------ backward (data gradients; frozen weights)
     def backward(self, dout: torch.Tensor, B: int, L: int, kmask: Optional[torch.Tensor], saved: List[LayerSaved],
-                 wgrad: Optional[Dict[str, List[torch.Tensor]]] = None, on_layer_done=None) -> torch.Tensor:
+                 wgrad: Optional[Dict[str, List[torch.Tensor]]] = None, on_layer_done=None, wgrad_accumulate: bool = True) -> torch.Tensor:
         """dout [B*L, d] bf16 -> dx [B*L, d].  Default recipe freezes the trunk (model_arch.py:33-51): only data
-        gradients flow.  ``wgrad`` (fp32 accumulators per layer) enables the --unfreeze_language_model path."""
+        gradients flow.  ``wgrad`` (fp32 accumulators per layer) enables the --unfreeze_language_model path; with
+        ``wgrad_accumulate=False`` the four weight-gradient GEMMs of a layer OVERWRITE their accumulators (first micro-batch after
+        ``zero_grad``: saves zero-filling and re-reading 27 GB of fp32 per step; the norm-weight gradients always accumulate)."""
         c = self.cfg
         d, H, hd, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.intermediate_size
         # Trainable trunk (--unfreeze_language_model): the weights change every step, so the data gradients read them in their
@@ -277,8 +279,8 @@ class LlamaTrunk:
             if wgrad is not None:
                 hn = ops.rmsnorm(s.h, w.ln2, c.rms_norm_eps)
                 a = ops.silu_mul(s.gu)
-                ops.gemm_tn(dout, a, out=wgrad["wdown"][li], accumulate=True)
-                ops.gemm_tn(dgu, hn, out=wgrad["wgu"][li], accumulate=True)
+                ops.gemm_tn(dout, a, out=wgrad["wdown"][li], accumulate=wgrad_accumulate)
+                ops.gemm_tn(dgu, hn, out=wgrad["wgu"][li], accumulate=wgrad_accumulate)
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout, dw=wgrad["ln2"][li])
             else:
                 dh = ops.rmsnorm_bwd(dhn, s.h, w.ln2, s.rstd2, dres=dout)
@@ -292,8 +294,8 @@ class LlamaTrunk:
             dxn = ops.gemm_nn(dqkv2, w.wqkv) if nn_dgrad else ops.gemm(dqkv2, w.wqkvT)
             if wgrad is not None:
                 xn = ops.rmsnorm(s.x, w.ln1, c.rms_norm_eps)
-                ops.gemm_tn(dh, s.o, out=wgrad["wo"][li], accumulate=True)
-                ops.gemm_tn(dqkv2, xn, out=wgrad["wqkv"][li], accumulate=True)
+                ops.gemm_tn(dh, s.o, out=wgrad["wo"][li], accumulate=wgrad_accumulate)
+                ops.gemm_tn(dqkv2, xn, out=wgrad["wqkv"][li], accumulate=wgrad_accumulate)
             if rows is not None:              # the residual gradient exists on the row range only: scatter it into a full tensor
                 dres = torch.zeros(B, L, d, device=dh.device, dtype=torch.bfloat16)
                 ops.copy_rows(dh.view(B, Lq, d), dres[:, rows[0]:rows[1], :])

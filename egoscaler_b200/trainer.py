@@ -74,6 +74,7 @@ class Trainer:
         self.grad = {n: torch.zeros_like(t) for n, t in self.master.items()}
         self.last_loss: Optional[torch.Tensor] = None
         self._sync = world_size > 1
+        self._wgrad_fresh = False           # True right after zero_grad(): the next backward overwrites the trunk weight gradients
         self.sparse_embed_exchange = True   # (id, row) all-gather + deterministic scatter instead of the dense embed_tokens all-reduce
         self._exchange_rows = -1
         self._embed_pending = []
@@ -102,12 +103,17 @@ class Trainer:
 
     def zero_grad(self):
         self._embed_pending = []
-        for g in self.grad.values():
-            g.zero_()
+        for n, g in self.grad.items():
+            if n != "lm_head.weight":                      # overwritten by the first head backward after this call
+                g.zero_()
+        self._wgrad_fresh = True
         if self.wgrad is not None:
-            for lst in self.wgrad.values():
-                for g in lst:
+            # the four big units of a layer are OVERWRITTEN by the first backward after this call (wgrad_accumulate=False), so only
+            # the norm-weight gradients (atomically accumulated) are cleared: no 27 GB memset + re-read per step
+            for k in ("ln1", "ln2"):
+                for g in self.wgrad[k]:
                     g.zero_()
+            self._wgrad_fresh = True
 
     # ------------------------------------------------------------------ forward + backward
     def forward_backward(self, tokens: torch.Tensor, attention_masks: torch.Tensor, pcrgbs: torch.Tensor, prompt_len: int,
@@ -141,7 +147,7 @@ class Trainer:
         targets = tokens[:, P:].contiguous().view(-1)
         loss = ops.cross_entropy(logits, V, targets, cfg.pad_token_id, write_grad=True)      # logits <- dlogits
         # ---- head backward
-        ops.gemm_tn(logits, hn, out=self.grad["lm_head.weight"], accumulate=True)             # dW = dlogits^T . hn
+        ops.gemm_tn(logits, hn, out=self.grad["lm_head.weight"], accumulate=not self._wgrad_fresh)   # dW = dlogits^T . hn
         dhn = ops.gemm_nn(logits, m.lm_head.weight.detach()) if ops.gemm_nn_enabled else ops.gemm(logits, m.lm_head_T())
         dhs = ops.rmsnorm_bwd(dhn, hs2, norm_w, rstd, dw=self.grad["model.norm.weight"])
         self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
@@ -154,8 +160,9 @@ class Trainer:
         # ---- trunk backward (data gradients through the frozen layers), embedding scatter, projector, encoder
         backward_from_hidden(m, ctx, dh, self.grad, self.wgrad,
                              on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None,
-                             on_ready=self._reduce_async,
+                             on_ready=self._reduce_async, wgrad_accumulate=not self._wgrad_fresh,
                              embed_exchange=self._embed_exchange if (self.world > 1 and self.sparse_embed_exchange) else None)
+        self._wgrad_fresh = False
         self.last_loss = loss
         return loss
 
