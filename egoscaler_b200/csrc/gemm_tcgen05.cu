@@ -629,9 +629,10 @@ constexpr int P2_STAGES = 6;
 constexpr int P2_STAGE_BYTES = 2 * 128 * BK * 2;
 constexpr int P2_SMEM = P2_STAGES * P2_STAGE_BYTES + 1024 + 1024;
 
-template <int EPI>
+template <int EPI, bool TA = false, bool TB = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+    static_assert(!(TA || TB) || EPI == EPI_PLAIN, "transposed operands: plain epilogue");
     constexpr int BN = 256;
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : BN;
     extern __shared__ uint8_t smem_raw[];
@@ -691,8 +692,18 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
                     uint8_t* sa = tiles + stage * P2_STAGE_BYTES;
                     uint8_t* sb = sa + 128 * BK * 2;
                     if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * P2_STAGE_BYTES);
-                    tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
-                    tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], kb * BK, nb, p.b_policy);
+                    if constexpr (TA) {                    // [64 contraction rows x 64 columns] boxes, MN-major operand (see the single-CTA kernel)
+                        tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], m0, kb * BK, p.a_policy);
+                        tma_load_2d_2sm_hint(sa + 8192, &tma_a, &full_bar[stage], m0 + 64, kb * BK, p.a_policy);
+                    } else {
+                        tma_load_2d_2sm_hint(sa, &tma_a, &full_bar[stage], kb * BK, m0, p.a_policy);
+                    }
+                    if constexpr (TB) {
+                        tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], nb, kb * BK, p.b_policy);
+                        tma_load_2d_2sm_hint(sb + 8192, &tma_b, &full_bar[stage], nb + 64, kb * BK, p.b_policy);
+                    } else {
+                        tma_load_2d_2sm_hint(sb, &tma_b, &full_bar[stage], kb * BK, nb, p.b_policy);
+                    }
                     if (rank != 0 && (p.dbg & 1)) mbar_arrive_cluster(leader_full0 + static_cast<uint32_t>(stage) * 8u);
                     if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
                 }
@@ -701,7 +712,7 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {
             // ===================== MMA issuer (leader CTA only)
-            constexpr uint32_t idesc = umma_idesc_bf16(256, BN);
+            constexpr uint32_t idesc = umma_idesc_bf16(256, BN) | (TA ? (1u << 15) : 0u) | (TB ? (1u << 16) : 0u);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -715,12 +726,14 @@ gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __gri
                     tc_fence_after();
                     const uint32_t sa = smem_u32(tiles + stage * P2_STAGE_BYTES);
                     const uint32_t sb = sa + 128 * BK * 2;
-                    const uint64_t da = umma_desc_kmajor_sw128(sa);
-                    const uint64_t db = umma_desc_kmajor_sw128(sb);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k)
-                        umma_bf16_ss_2cta(d_tmem, da + static_cast<uint64_t>(2 * k), db + static_cast<uint64_t>(2 * k), idesc,
-                                          (kb | k) != 0 ? 1u : 0u);
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t da = TA ? umma_desc_mnmajor_sw128(sa + k * 2048, 8192)
+                                               : umma_desc_kmajor_sw128(sa) + static_cast<uint64_t>(2 * k);
+                        const uint64_t db = TB ? umma_desc_mnmajor_sw128(sb + k * 2048, 8192)
+                                               : umma_desc_kmajor_sw128(sb) + static_cast<uint64_t>(2 * k);
+                        umma_bf16_ss_2cta(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
                     umma_commit_2cta(&empty_bar[stage], 3);          // both CTAs may refill stage `stage`
                     if (++stage == P2_STAGES) { stage = 0; phase ^= 1u; }
                 }
@@ -882,12 +895,12 @@ static int g_gemm_2cta = [] { const char* e = getenv("ESB_GEMM_2CTA"); return e 
 int set_gemm_2cta(int on) { const int old = g_gemm_2cta; g_gemm_2cta = on ? 1 : 0; return old; }
 static bool use_2cta(int M, int N, int K) { return g_gemm_2cta && M >= 1024 && N >= 512 && K >= 256; }
 
-template <int EPI>
+template <int EPI, bool TA = false, bool TB = false>
 static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, cudaStream_t stream, int sms) {
     constexpr int BN_OUT = (EPI == EPI_SWIGLU) ? 128 : 256;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm2_bf16_tcgen05_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, P2_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm2_bf16_tcgen05_kernel<EPI, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize, P2_SMEM);
         if (e != cudaSuccess) {
             set_last_error("cudaFuncSetAttribute(gemm2): %s", cudaGetErrorString(e));
             return ESB_ERR_CUDA;
@@ -899,7 +912,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams
     const int tiles = p.tiles_m * p.tiles_n;
     int pairs = sms / 2;
     if (tiles < pairs) pairs = tiles;
-    gemm2_bf16_tcgen05_kernel<EPI><<<2 * pairs, GEMM_THREADS, P2_SMEM, stream>>>(ta, tb, p);
+    gemm2_bf16_tcgen05_kernel<EPI, TA, TB><<<2 * pairs, GEMM_THREADS, P2_SMEM, stream>>>(ta, tb, p);
     return check_launch("gemm2_bf16_tcgen05");
 }
 
@@ -1048,6 +1061,7 @@ int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, v
 template <bool TA, bool TB>
 static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int M, int N, cudaStream_t stream) {
     const int sms = device_sm_count();
+    if (use_2cta(M, N, p.K)) return launch_gemm2<EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);   // same 64 x 64 boxes / 128-row A box
     const long long t256 = static_cast<long long>((M + BM - 1) / BM) * ((N + 255) / 256);
     if (N > 128 && t256 >= sms / 2) return launch_gemm<256, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);
     if (N > 64) return launch_gemm<128, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);

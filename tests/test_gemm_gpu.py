@@ -261,7 +261,7 @@ def test_attention_bwd_fused_inverse_rope_equals_two_launches(B, L, H):
     assert torch.equal(got, ref)
 
 
-@pytest.mark.parametrize("T,M,N", [(1392, 256, 768), (1216, 32262, 256), (300, 688, 256), (77, 40, 24), (5568, 4096, 11008), (1026, 384, 1152)])
+@pytest.mark.parametrize("T,M,N", [(1100, 1100, 640), (1392, 256, 768), (1216, 32262, 256), (300, 688, 256), (77, 40, 24), (5568, 4096, 11008), (1026, 384, 1152)])
 def test_gemm_tn_weight_gradient_form(T, M, N):
     """dW[M,N] = A^T . B with A [T,M], B [T,N] row-major (MN-major tcgen05 operands) vs fp32 torch and vs the transpose + NT path;
     fp32 accumulate-into-C, strided A (the logits buffer has a padded leading dimension)."""
@@ -284,7 +284,7 @@ def test_gemm_tn_weight_gradient_form(T, M, N):
     assert (acc - 1.0 - ref).abs().max() <= 2e-3 * ref.abs().max() + 1e-3
 
 
-@pytest.mark.parametrize("M,Kc,N", [(1392, 768, 256), (1216, 32262, 256), (300, 256, 688), (77, 24, 40), (5568, 11008, 4096), (5568, 4096, 4096)])
+@pytest.mark.parametrize("M,Kc,N", [(1100, 320, 640), (1392, 768, 256), (1216, 32262, 256), (300, 256, 688), (77, 24, 40), (5568, 11008, 4096), (5568, 4096, 4096)])
 def test_gemm_nn_data_gradient_form(M, Kc, N):
     """dX[M,N] = A . W with A [M,Kc] and W [Kc,N] = a weight in its [out, in] state_dict layout (MN-major B operand) vs fp32 torch
     and vs the NT GEMM on a transposed copy (same products and k-block order: equal up to rare rounding flips)."""
