@@ -235,6 +235,13 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                     mbar_wait(&bar_dq[(j - 1) & 1], ((j - 1) >> 1) & 1);
                     load_k(j + 2);
                 }
+                // S / dP of block j+2 go to the tensor pipe as soon as the compute warps have READ buffer st (early in their work
+                // on block j) - not after dS_j is finished: the MMAs then run under the exp / pack / store of block j instead of
+                // after them (the loop is bound by these hand-off latencies, not by MMA throughput)
+                if (j + 2 < nblk) {
+                    mbar_wait(&bar_sfree[st], (j >> 1) & 1);
+                    issue_sdp(j + 2);
+                }
                 mbar_wait(&bar_ds[st], (j >> 1) & 1);    // dS_j is in smem
                 tc_fence_after();
                 const uint32_t ads = smem_u32(sDS + st * OP_BYTES), ak = smem_u32(sK + (j % DQ_K_STAGES) * BLK_BYTES);
@@ -245,10 +252,6 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                     umma_bf16_ss(tmem_base + 256, da, db, idesc_q, (j | ks) != 0 ? 1u : 0u);
                 }
                 umma_commit(&bar_dq[st]);
-                if (j + 2 < nblk) {
-                    mbar_wait(&bar_sfree[st], (j >> 1) & 1);
-                    issue_sdp(j + 2);
-                }
             }
         }
     } else {
@@ -454,6 +457,10 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                     mbar_wait(bar_acc, (jj - 1) & 1);
                     load_q(jj + 2);
                 }
+                if (jj + 2 < nq) {                       // same early issue as in the dQ kernel
+                    mbar_wait(&bar_sfree[st], (jj >> 1) & 1);
+                    issue_s(jj + 2);
+                }
                 mbar_wait(bar_p, jj & 1);                // P^T_jj, dS^T_jj are in smem
                 tc_fence_after();
                 const uint32_t apt = smem_u32(sPT), adst = smem_u32(sDST), aq = smem_u32(sQ + q3 * BLK_BYTES), ado = smem_u32(sDO + q3 * BLK_BYTES);
@@ -470,10 +477,6 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                     umma_bf16_ss(tmem_base + 384, da, db, idesc_a, (jj | ks) != 0 ? 1u : 0u);
                 }
                 umma_commit(bar_acc);
-                if (jj + 2 < nq) {
-                    mbar_wait(&bar_sfree[st], (jj >> 1) & 1);
-                    issue_s(jj + 2);
-                }
             }
         }
     } else {
