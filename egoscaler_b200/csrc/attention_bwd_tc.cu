@@ -130,8 +130,12 @@ ESB_DEVICE void store_operand_half_row(uint8_t* tile, int r, int half, const uin
 }
 
 // ================================================================================================ dQ
-constexpr int DQ_K_STAGES = 3;
-constexpr int DQ_SMEM = 2 * TILE_BYTES + DQ_K_STAGES * BLK_BYTES + 2 * BLK_BYTES + 2 * OP_BYTES + 256 + 1024;
+// K / V rings one stage deeper than the MMA look-ahead (4 / 3): a ring slot is only freed by an MMA that retires one block time
+// before the slot's next use, and with 3 / 2 stages that left the TMA round trip on the critical path (ncu: 36 % of the compute
+// warps' samples waiting for S / dP, tensor pipe 16 % - profiles/r02_attn_bwd_ncu.txt)
+constexpr int DQ_K_STAGES = 4;
+constexpr int DQ_V_STAGES = 3;
+constexpr int DQ_SMEM = 2 * TILE_BYTES + DQ_K_STAGES * BLK_BYTES + DQ_V_STAGES * BLK_BYTES + 2 * OP_BYTES + 256 + 1024;
 // TMEM columns: S[2] at 0/64, dP[2] at 128/192, dQ at 256..383
 
 __global__ void __launch_bounds__(BT_THREADS, 1)
@@ -141,18 +145,18 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
     uint8_t* sDO = sQ + TILE_BYTES;
-    uint8_t* sK = sDO + TILE_BYTES;                      // 3 stages
-    uint8_t* sV = sK + DQ_K_STAGES * BLK_BYTES;          // 2 stages
-    uint8_t* sDS = sV + 2 * BLK_BYTES;                   // 2 buffers
+    uint8_t* sK = sDO + TILE_BYTES;                      // DQ_K_STAGES stages
+    uint8_t* sV = sK + DQ_K_STAGES * BLK_BYTES;          // DQ_V_STAGES stages
+    uint8_t* sDS = sV + DQ_V_STAGES * BLK_BYTES;         // 2 buffers
     uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * OP_BYTES);
     uint64_t* bar_qdo = bars;
-    uint64_t* bar_k = bars + 1;        // [3]
-    uint64_t* bar_v = bars + 4;        // [2]
-    uint64_t* bar_s = bars + 6;        // [2] S_j and dP_j computed
-    uint64_t* bar_sfree = bars + 8;    // [2] all compute threads have read them
-    uint64_t* bar_ds = bars + 10;      // [2] dS_j written
-    uint64_t* bar_dq = bars + 12;      // [2] dQ += dS_j K_j retired
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+    uint64_t* bar_k = bars + 1;        // [4]
+    uint64_t* bar_v = bars + 5;        // [3]
+    uint64_t* bar_s = bars + 8;        // [2] S_j and dP_j computed
+    uint64_t* bar_sfree = bars + 10;   // [2] all compute threads have read them
+    uint64_t* bar_ds = bars + 12;      // [2] dS_j written
+    uint64_t* bar_dq = bars + 14;      // [2] dQ += dS_j K_j retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int qt = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);
@@ -165,8 +169,9 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
     if (tid == 0) {
         mbar_init(bar_qdo, 1);
         for (int i = 0; i < DQ_K_STAGES; ++i) mbar_init(&bar_k[i], 1);
+        for (int i = 0; i < DQ_V_STAGES; ++i) mbar_init(&bar_v[i], 1);
         for (int i = 0; i < 2; ++i) {
-            mbar_init(&bar_v[i], 1); mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32);
+            mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32);
             mbar_init(&bar_ds[i], BT_COMPUTE / 32); mbar_init(&bar_dq[i], 1);
         }
         fence_barrier_init();
@@ -190,17 +195,17 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 tma_load_3d(sK + st * BLK_BYTES + BLK_BYTES / 2, &tk, &bar_k[st], hcol + 64, j * BT_BLK, b);
             };
             auto load_v = [&](int j) {
-                const int st = j & 1;
+                const int st = j % DQ_V_STAGES;
                 mbar_arrive_expect_tx(&bar_v[st], BLK_BYTES);
                 tma_load_3d(sV + st * BLK_BYTES, &tv, &bar_v[st], hcol, j * BT_BLK, b);
                 tma_load_3d(sV + st * BLK_BYTES + BLK_BYTES / 2, &tv, &bar_v[st], hcol + 64, j * BT_BLK, b);
             };
             auto issue_sdp = [&](int j) {             // S_j = Q K_j^T, dP_j = dO V_j^T
-                const int st = j & 1, ks3 = j % DQ_K_STAGES;
+                const int st = j & 1, ks3 = j % DQ_K_STAGES, vs3 = j % DQ_V_STAGES;
                 mbar_wait(&bar_k[ks3], (j / DQ_K_STAGES) & 1);
-                mbar_wait(&bar_v[st], (j >> 1) & 1);
+                mbar_wait(&bar_v[vs3], (j / DQ_V_STAGES) & 1);
                 tc_fence_after();
-                const uint32_t aq = smem_u32(sQ), ado = smem_u32(sDO), ak = smem_u32(sK + ks3 * BLK_BYTES), av = smem_u32(sV + st * BLK_BYTES);
+                const uint32_t aq = smem_u32(sQ), ado = smem_u32(sDO), ak = smem_u32(sK + ks3 * BLK_BYTES), av = smem_u32(sV + vs3 * BLK_BYTES);
 #pragma unroll
                 for (int ks = 0; ks < BT_HD / 16; ++ks) {
                     const uint64_t da = umma_desc_kmajor_sw128(aq + (ks >> 2) * (TILE_BYTES / 2)) + static_cast<uint64_t>(2 * (ks & 3));
@@ -221,19 +226,19 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
             tma_load_3d(sDO, &tdo, bar_qdo, hcol, m0, b);
             tma_load_3d(sDO + TILE_BYTES / 2, &tdo, bar_qdo, hcol + 64, m0, b);
             for (int j = 0; j < min(nblk, DQ_K_STAGES); ++j) load_k(j);
-            for (int j = 0; j < min(nblk, 2); ++j) load_v(j);
+            for (int j = 0; j < min(nblk, DQ_V_STAGES); ++j) load_v(j);
             mbar_wait(bar_qdo, 0);
             issue_sdp(0);
             if (nblk > 1) issue_sdp(1);
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1;
-                if (j + 2 < nblk) {                      // V stage st is free once dP_j has been computed
+                if (j + DQ_V_STAGES < nblk) {            // V stage j % 3 is free once dP_j has been computed
                     mbar_wait(&bar_s[st], (j >> 1) & 1);
-                    load_v(j + 2);
+                    load_v(j + DQ_V_STAGES);
                 }
-                if (j >= 1 && j + 2 < nblk) {            // K stage (j-1)%3 is free once dQ += dS_{j-1} K_{j-1} retired
+                if (j >= 1 && j - 1 + DQ_K_STAGES < nblk) {   // K stage (j-1) % 4 is free once dQ += dS_{j-1} K_{j-1} retired
                     mbar_wait(&bar_dq[(j - 1) & 1], ((j - 1) >> 1) & 1);
-                    load_k(j + 2);
+                    load_k(j - 1 + DQ_K_STAGES);
                 }
                 // S / dP of block j+2 go to the tensor pipe as soon as the compute warps have READ buffer st (early in their work
                 // on block j) - not after dS_j is finished: the MMAs then run under the exp / pack / store of block j instead of
