@@ -368,7 +368,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
 // ================================================================================================ dK / dV
 constexpr int KV_Q_STAGES = 3;
 constexpr int KV_STAT_BYTES = BT_BLK * 8;            // 64 x float2
-constexpr int KV_SMEM = 2 * TILE_BYTES + 2 * KV_Q_STAGES * BLK_BYTES + 2 * OP_BYTES + KV_Q_STAGES * KV_STAT_BYTES + 256 + 1024;
+// P^T / dS^T double-buffered: with one buffer the compute warps of block j+1 stalled until the dV / dK MMAs of block j had retired
+// (ncu: 18 % of their samples on that wait, profiles/r02_attn_bwd_ncu.txt)
+constexpr int KV_SMEM = 2 * TILE_BYTES + 2 * KV_Q_STAGES * BLK_BYTES + 4 * OP_BYTES + KV_Q_STAGES * KV_STAT_BYTES + 256 + 1024;
+static_assert(KV_SMEM <= 232448, "dK/dV kernel shared memory");
 // TMEM columns: S^T[2] at 0/64, dP^T[2] at 128/192, dV at 256..383, dK at 384..511
 
 __global__ void __launch_bounds__(BT_THREADS, 1)
@@ -380,17 +383,17 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
     uint8_t* sV = sK + TILE_BYTES;
     uint8_t* sQ = sV + TILE_BYTES;                       // 3 stages
     uint8_t* sDO = sQ + KV_Q_STAGES * BLK_BYTES;         // 3 stages
-    uint8_t* sPT = sDO + KV_Q_STAGES * BLK_BYTES;
-    uint8_t* sDST = sPT + OP_BYTES;
-    float2* sStat = reinterpret_cast<float2*>(sDST + OP_BYTES);        // 3 x 64
+    uint8_t* sPT = sDO + KV_Q_STAGES * BLK_BYTES;        // 2 buffers
+    uint8_t* sDST = sPT + 2 * OP_BYTES;                  // 2 buffers
+    float2* sStat = reinterpret_cast<float2*>(sDST + 2 * OP_BYTES);    // 3 x 64
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sStat) + KV_Q_STAGES * KV_STAT_BYTES);
     uint64_t* bar_kv = bars;
     uint64_t* bar_q = bars + 1;        // [3] Q_i, dO_i, stats_i landed
     uint64_t* bar_s = bars + 4;        // [2] S^T, dP^T computed
     uint64_t* bar_sfree = bars + 6;    // [2]
-    uint64_t* bar_p = bars + 8;        // P^T, dS^T written
-    uint64_t* bar_acc = bars + 9;      // dV / dK MMAs of the block retired
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+    uint64_t* bar_p = bars + 8;        // [2] P^T, dS^T written (buffer jj & 1)
+    uint64_t* bar_acc = bars + 10;     // [2] dV / dK MMAs of the block retired (buffer jj & 1 reusable)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int h = blockIdx.y, b = blockIdx.z;
@@ -404,8 +407,7 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
         mbar_init(bar_kv, 1);
         for (int i = 0; i < KV_Q_STAGES; ++i) mbar_init(&bar_q[i], 1);
         for (int i = 0; i < 2; ++i) { mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32); }
-        mbar_init(bar_p, BT_COMPUTE / 32);
-        mbar_init(bar_acc, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], BT_COMPUTE / 32); mbar_init(&bar_acc[i], 1); }
         fence_barrier_init();
     }
     if (warp == 8) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -461,16 +463,16 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
             for (int jj = 0; jj < nq; ++jj) {
                 const int st = jj & 1, q3 = jj % KV_Q_STAGES;
                 if (jj >= 1 && jj + 2 < nq) {            // stage (jj-1)%3 is free once the dV/dK MMAs of block jj-1 retired
-                    mbar_wait(bar_acc, (jj - 1) & 1);
+                    mbar_wait(&bar_acc[(jj - 1) & 1], ((jj - 1) >> 1) & 1);
                     load_q(jj + 2);
                 }
                 if (jj + 2 < nq) {                       // same early issue as in the dQ kernel
                     mbar_wait(&bar_sfree[st], (jj >> 1) & 1);
                     issue_s(jj + 2);
                 }
-                mbar_wait(bar_p, jj & 1);                // P^T_jj, dS^T_jj are in smem
+                mbar_wait(&bar_p[st], (jj >> 1) & 1);    // P^T_jj, dS^T_jj are in smem (buffer st)
                 tc_fence_after();
-                const uint32_t apt = smem_u32(sPT), adst = smem_u32(sDST), aq = smem_u32(sQ + q3 * BLK_BYTES), ado = smem_u32(sDO + q3 * BLK_BYTES);
+                const uint32_t apt = smem_u32(sPT + st * OP_BYTES), adst = smem_u32(sDST + st * OP_BYTES), aq = smem_u32(sQ + q3 * BLK_BYTES), ado = smem_u32(sDO + q3 * BLK_BYTES);
 #pragma unroll
                 for (int ks = 0; ks < BT_BLK / 16; ++ks) {
                     const uint64_t da = umma_desc_kmajor_sw128(apt) + static_cast<uint64_t>(2 * ks);
@@ -483,7 +485,7 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                     const uint64_t db = umma_desc_mnmajor_sw128(aq + ks * 2048, BLK_BYTES / 2);
                     umma_bf16_ss(tmem_base + 384, da, db, idesc_a, (jj | ks) != 0 ? 1u : 0u);
                 }
-                umma_commit(bar_acc);
+                umma_commit(&bar_acc[st]);
             }
         }
     } else {
@@ -531,16 +533,16 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                 wp[c >> 1] = pack_bf16x2(p0, p1);
                 wd[c >> 1] = pack_bf16x2(p0 * (__uint_as_float(dpr[c]) - s0.y), p1 * (__uint_as_float(dpr[c + 1]) - s1.y));
             }
-            if (jj >= 1) mbar_wait(bar_acc, (jj - 1) & 1);              // previous dV/dK MMAs no longer read sPT / sDST
-            store_operand_half_row(sPT, r, half, wp);
-            store_operand_half_row(sDST, r, half, wd);
+            if (jj >= 2) mbar_wait(&bar_acc[st], ((jj - 2) >> 1) & 1);  // the dV/dK MMAs of block jj-2 no longer read buffer st
+            store_operand_half_row(sPT + st * OP_BYTES, r, half, wp);
+            store_operand_half_row(sDST + st * OP_BYTES, r, half, wd);
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_p);
+            if (lane == 0) mbar_arrive(&bar_p[st]);
         }
         // ---- epilogue: dV, dK * scale -> bf16
         if (nq > 0) {
-            mbar_wait(bar_acc, (nq - 1) & 1);
+            mbar_wait(&bar_acc[(nq - 1) & 1], ((nq - 1) >> 1) & 1);
             tc_fence_after();
         }
         __nv_bfloat16* gv = p.dv + static_cast<long long>(b) * p.dv_bs + static_cast<long long>(key) * p.dv_rs + static_cast<long long>(h) * BT_HD + half * 64;
