@@ -99,6 +99,15 @@ int esb_gemm_skinny_normed_bf16(const void* X, int64_t ldx, const void* W, int64
                                    scale_src, scale_parts, eps, ssq_out, ST(stream));
 }
 
+int64_t esb_gemm_chain_workspace_bytes(int M, int max_N) { return gemm_chain_workspace_bytes(M, max_N); }
+int esb_gemm_chain_bf16(const void* phases, int n_phases, int M, void* workspace, int64_t workspace_bytes, int flags, void* stream) {
+    return gemm_chain_bf16(static_cast<const esb_chain_phase*>(phases), n_phases, M, workspace, workspace_bytes, flags, ST(stream));
+}
+int64_t esb_retiled_gateup_elems(int f, int K) { return retiled_gateup_elems(f, K); }
+int esb_retile_weight_gateup_bf16(const void* W, int64_t ldw, int f, int K, const void* col_scale, void* out, void* stream) {
+    return retile_weight_gateup_bf16(W, ldw, f, K, col_scale, out, ST(stream));
+}
+
 int esb_traj_quantize(const void* x, int is_f64, int64_t n, int num_bins, int64_t id_offset, int64_t* out, void* stream) {
     return traj_quantize(x, is_f64, n, num_bins, id_offset, reinterpret_cast<long long*>(out), ST(stream));
 }

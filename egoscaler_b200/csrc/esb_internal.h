@@ -74,5 +74,13 @@ int gemm_skinny_normed_bf16(const void* X, long long ldx, const void* W, long lo
 int retile_weight_scaled_bf16(const void* W, long long ldw, int N, int K, const void* col_scale, void* out, cudaStream_t stream);
 long long retiled_weight_elems(int N, int K);
 int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cudaStream_t stream);
+long long retiled_gateup_elems(int f, int K);
+int retile_weight_gateup_bf16(const void* W, long long ldw, int f, int K, const void* col_scale, void* out, cudaStream_t stream);
+long long gemm_chain_workspace_bytes(int M, int max_N);
+}  // namespace esb
+struct esb_chain_phase;      // include/egoscaler_b200.h
+namespace esb {
+int gemm_chain_bf16(const esb_chain_phase* phases, int n_phases, int M, void* workspace, long long workspace_bytes, int flags,
+                    cudaStream_t stream);
 
 }  // namespace esb

@@ -370,8 +370,11 @@ int launch_skinny(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyPara
 namespace {
 // tile (tile, kb) = W[tile*128 .. +128][kb*64 .. +64] (zero beyond N / K), 16 KiB contiguous, stored as the 128-byte-swizzled
 // shared-memory image tcgen05 expects (16-byte chunk c of row r at chunk c ^ (r & 7)), so a 1-D bulk copy stages it.
+// gu_f > 0: W is a packed [2 gu_f, K] gate|up weight and tile t holds gate rows t*64.. (tile rows 0..63) and up rows gu_f + t*64..
+// (tile rows 64..127), so that one accumulator tile carries both factors of 64 SwiGLU outputs (gemm_chain.cu).
 __global__ void retile_weight_kernel(const __nv_bfloat16* __restrict__ W, long long ldw, int N, int K, int num_kb,
-                                     long long total_vec, uint4* __restrict__ out, const __nv_bfloat16* __restrict__ col_scale) {
+                                     long long total_vec, uint4* __restrict__ out, const __nv_bfloat16* __restrict__ col_scale,
+                                     int gu_f) {
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total_vec;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
         const int c8 = static_cast<int>(i & 7);
@@ -379,7 +382,11 @@ __global__ void retile_weight_kernel(const __nv_bfloat16* __restrict__ W, long l
         const long long blk = i >> 10;
         const int kb = static_cast<int>(blk % num_kb);
         const long long tile = blk / num_kb;
-        const long long n = tile * SK_ROWS + r;
+        long long n = tile * SK_ROWS + r;
+        if (gu_f > 0) {
+            const long long col = tile * 64 + (r & 63);
+            n = col < gu_f ? col + (r >= 64 ? gu_f : 0) : N;          // N: out of range -> zero row
+        }
         const int k = kb * SK_BK + c8 * 8;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (n < N && k + 8 <= K) v = __ldg(reinterpret_cast<const uint4*>(W + n * ldw + k));
@@ -416,8 +423,25 @@ int retile_weight_scaled_bf16(const void* W, long long ldw, int N, int K, const 
     const long long total_vec = retiled_weight_elems(N, K) / 8;
     const int grid = device_sm_count() * 8;
     retile_weight_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(W), ldw, N, K, num_kb, total_vec,
-                                                   reinterpret_cast<uint4*>(out), reinterpret_cast<const __nv_bfloat16*>(col_scale));
+                                                   reinterpret_cast<uint4*>(out), reinterpret_cast<const __nv_bfloat16*>(col_scale), 0);
     return check_launch("retile_weight");
+}
+
+long long retiled_gateup_elems(int f, int K) {
+    return static_cast<long long>((f + 63) / 64) * ((K + SK_BK - 1) / SK_BK) * SK_ROWS * SK_BK;
+}
+
+int retile_weight_gateup_bf16(const void* W, long long ldw, int f, int K, const void* col_scale, void* out, cudaStream_t stream) {
+    if (f <= 0 || K <= 0 || !W || !out || (ldw & 7) || (reinterpret_cast<uintptr_t>(W) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) {
+        set_last_error("retile_weight_gateup_bf16: bad arguments (f=%d K=%d ldw=%lld)", f, K, ldw);
+        return ESB_ERR_INVALID_ARG;
+    }
+    const int num_kb = (K + SK_BK - 1) / SK_BK;
+    const long long total_vec = retiled_gateup_elems(f, K) / 8;
+    const int grid = device_sm_count() * 8;
+    retile_weight_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(W), ldw, 2 * f, K, num_kb, total_vec,
+                                                   reinterpret_cast<uint4*>(out), reinterpret_cast<const __nv_bfloat16*>(col_scale), f);
+    return check_launch("retile_weight_gateup");
 }
 
 long long gemm_skinny_workspace_bytes(int M, int N, int K) {

@@ -54,12 +54,25 @@ class LayerWeights:
     tgu: Optional["ops.TiledWeight"] = None
     tdown: Optional["ops.TiledWeight"] = None
     tiled_folded: bool = False          # tqkv / tgu carry ln1 / ln2 folded into their columns (ops.fold_norm_enabled)
+    tgu_il: Optional["ops.TiledWeight"] = None    # gate|up rows interleaved per tile + ln2 folded (ops.gemm_chain SwiGLU phase)
 
     def ensure_tiled(self, folded: bool = False):
-        if self.tqkv is None or self.tiled_folded != folded:
+        if self.tqkv is None or self.tgu is None or self.tiled_folded != folded:
             self.tqkv = ops.retile_weight(self.wqkv, self.ln1 if folded else None)
             self.tgu = ops.retile_weight(self.wgu, self.ln2 if folded else None)
             self.tiled_folded = folded
+        if self.to is None:
+            self.to = ops.retile_weight(self.wo)
+            self.tdown = ops.retile_weight(self.wdown)
+
+    def ensure_chain(self):
+        """decode-layout copies of ``LlamaTrunk._decode_step_chain``: q|k|v with ln1 folded, gate|up interleaved with ln2 folded."""
+        if self.tqkv is None or not self.tiled_folded:
+            self.tqkv = ops.retile_weight(self.wqkv, self.ln1)
+            self.tgu = None                # the plain-layout gate|up copy is not needed by the chain (405 MB per layer)
+            self.tiled_folded = True
+        if self.tgu_il is None:
+            self.tgu_il = ops.retile_weight_gateup(self.wgu, self.ln2)
         if self.to is None:
             self.to = ops.retile_weight(self.wo)
             self.tdown = ops.retile_weight(self.wdown)
@@ -72,7 +85,7 @@ class LayerWeights:
             ops.transpose(self.wo, out=self.woT)
             ops.transpose(self.wgu, out=self.wguT)
             ops.transpose(self.wdown, out=self.wdownT)
-        self.tqkv = self.to = self.tgu = self.tdown = None
+        self.tqkv = self.to = self.tgu = self.tdown = self.tgu_il = None
 
     def ensure_transposed(self):
         if self.wqkvT is None:
@@ -134,6 +147,8 @@ class LlamaTrunk:
         if pos_dev is not None:          # graph-replayed decode step: the position lives in a device counter
             assert attn_decode and pos0 == 0
         self.decode_stat = None
+        if decode and ops.decode_chain_enabled and saved is None:
+            return self._decode_step_chain(x, B, kmask, pos0, cache, pos_dev)
         if decode and ops.fold_norm_enabled and saved is None:
             return self._decode_step_folded(x, B, kmask, pos0, cache, pos_dev)
         if decode:
@@ -248,6 +263,38 @@ class LlamaTrunk:
             x = ops.gemm_skinny(a, w.tdown, residual=h, weights_const=True, ssq_out=ssq[1])
             stat = (ssq[1], nt)
         self.decode_stat = stat
+        return x
+
+    def _decode_step_chain(self, x: torch.Tensor, B: int, kmask, pos0: int, cache: KVCache, pos_dev) -> torch.Tensor:
+        """The cached single-token step with the Linears between two attention calls in ONE persistent launch
+        (ops.gemm_chain, csrc/gemm_chain.cu): per layer  rope + cache write -> attention -> [o-proj + residual -> gate|up + SwiGLU
+        -> down-proj + residual -> next layer's q|k|v], norms folded as in ``_decode_step_folded``.  3 kernels per layer."""
+        c = self.cfg
+        d, H, hd, eps, f = c.hidden_size, c.num_attention_heads, c.head_dim, c.rms_norm_eps, c.intermediate_size
+        for w in self.layers:
+            w.ensure_chain()
+        nt = (d + 127) // 128
+        dev = x.device
+        _, rstd0 = ops.rmsnorm(x, self.layers[0].ln1, eps, want_rstd=True)      # statistics of the embedding rows
+        qkv = ops.gemm_skinny(x, self.layers[0].tqkv, weights_const=True, row_scale=(rstd0, 0), eps=eps)
+        ssq = torch.empty(2, nt, 64, device=dev, dtype=torch.float32)
+        n_layers = len(self.layers)
+        for li, w in enumerate(self.layers):
+            ops.rope_(qkv, 1, 2 * H, hd, self.cos, self.sin, pos0, kcache=cache.k[li], vcache=cache.v[li],
+                      kv_head0=H, kv_heads=H, v_col0=2 * d, cache_len=cache.max_len, pos_ptr=pos_dev)
+            o = ops.attention_decode(qkv, cache.k[li], cache.v[li], H, hd, kmask=kmask, len_ptr=pos_dev, len_static=pos0 + 1)
+            h = torch.empty(B, d, device=dev, dtype=torch.bfloat16)
+            a = torch.empty(B, f, device=dev, dtype=torch.bfloat16)
+            xn = torch.empty(B, d, device=dev, dtype=torch.bfloat16)
+            phases = [ops.ChainPhase(o, w.to, h, residual=x, ssq_out=ssq[0]),
+                      ops.ChainPhase(h, w.tgu_il, a, row_scale=(ssq[0], nt), eps=eps, swiglu=True),
+                      ops.ChainPhase(a, w.tdown, xn, residual=h, ssq_out=ssq[1])]
+            if li + 1 < n_layers:
+                qkv = torch.empty(B, 3 * d, device=dev, dtype=torch.bfloat16)
+                phases.append(ops.ChainPhase(xn, self.layers[li + 1].tqkv, qkv, row_scale=(ssq[1], nt), eps=eps))
+            ops.gemm_chain(phases, weights_const=True)
+            x = xn
+        self.decode_stat = (ssq[1], nt)
         return x
 
     # ------------------------------------------------------------------ backward (data gradients; frozen weights)

@@ -6,6 +6,7 @@ a missing library or a non-CUDA tensor raises.
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional
 
 import torch
@@ -58,10 +59,10 @@ def _skinny_workspace(device) -> torch.Tensor:
 class TiledWeight:
     """A [N,K] bf16 weight re-laid out once into [ceil(N/128)][ceil(K/64)][128][64] tiles (esb_retile_weight_bf16): the
     layout the decode-step GEMM streams at HBM speed (one contiguous 16 KiB read per pipeline stage)."""
-    __slots__ = ("data", "N", "K")
+    __slots__ = ("data", "N", "K", "gateup")
 
-    def __init__(self, data: torch.Tensor, N: int, K: int):
-        self.data, self.N, self.K = data, N, K
+    def __init__(self, data: torch.Tensor, N: int, K: int, gateup: bool = False):
+        self.data, self.N, self.K, self.gateup = data, N, K, gateup
 
 
 def retile_weight(w: torch.Tensor, col_scale: Optional[torch.Tensor] = None) -> TiledWeight:
@@ -78,6 +79,81 @@ def retile_weight(w: torch.Tensor, col_scale: Optional[torch.Tensor] = None) -> 
         assert col_scale.numel() == K and col_scale.is_contiguous()
         _l.call("esb_retile_weight_scaled_bf16", w.data_ptr(), w.stride(0), N, K, col_scale.data_ptr(), out.data_ptr(), _stream())
     return TiledWeight(out, N, K)
+
+
+def retile_weight_gateup(w: torch.Tensor, col_scale: Optional[torch.Tensor] = None) -> TiledWeight:
+    """The packed [2f, K] gate|up weight as tiles of 64 gate rows + the 64 matching up rows (esb_retile_weight_gateup_bf16):
+    the layout whose accumulator tile carries both factors of SwiGLU (``gemm_chain`` with ``swiglu=True``)."""
+    _chk(w, torch.bfloat16, "retile_weight_gateup.w")
+    assert w.dim() == 2 and w.stride(1) == 1 and w.shape[0] % 2 == 0
+    N, K = w.shape
+    n = int(_l.lib().raw("esb_retiled_gateup_elems")(N // 2, K))
+    out = torch.empty(n, device=w.device, dtype=torch.bfloat16)
+    if col_scale is not None:
+        _chk(col_scale, torch.bfloat16, "retile_weight_gateup.col_scale")
+        assert col_scale.numel() == K and col_scale.is_contiguous()
+    _l.call("esb_retile_weight_gateup_bf16", w.data_ptr(), w.stride(0), N // 2, K, _p(col_scale), out.data_ptr(), _stream())
+    return TiledWeight(out, N, K, gateup=True)
+
+
+class _ChainPhaseC(ctypes.Structure):          # esb_chain_phase (include/egoscaler_b200.h)
+    _fields_ = [("X", ctypes.c_void_p), ("ldx", ctypes.c_int64), ("W_tiles", ctypes.c_void_p), ("C", ctypes.c_void_p),
+                ("ldc", ctypes.c_int64), ("residual", ctypes.c_void_p), ("ldr", ctypes.c_int64), ("scale_src", ctypes.c_void_p),
+                ("ssq_out", ctypes.c_void_p), ("N", ctypes.c_int32), ("K", ctypes.c_int32), ("scale_parts", ctypes.c_int32),
+                ("swiglu", ctypes.c_int32), ("eps", ctypes.c_float), ("reserved", ctypes.c_int32)]
+
+
+class ChainPhase:
+    """One Linear of ``gemm_chain``: ``out = rstd * (x @ w.T) + residual`` (``swiglu``: ``out = silu(gate) * up``); arguments as
+    in :func:`gemm_skinny`, ``w`` a :class:`TiledWeight` (``retile_weight_gateup`` for a SwiGLU phase)."""
+    __slots__ = ("x", "w", "out", "residual", "row_scale", "eps", "ssq_out", "swiglu")
+
+    def __init__(self, x, w, out, residual=None, row_scale=None, eps: float = 0.0, ssq_out=None, swiglu: bool = False):
+        self.x, self.w, self.out, self.residual, self.row_scale, self.eps, self.ssq_out, self.swiglu = \
+            x, w, out, residual, row_scale, eps, ssq_out, swiglu
+
+
+_chain_ws = {}
+
+
+def gemm_chain(phases, weights_const: bool = True) -> None:
+    """Up to four dependent skinny Linears in ONE persistent launch (esb_gemm_chain_bf16): phase i+1 may read what phase i
+    wrote.  The decode step runs o-proj -> gate|up + SwiGLU -> down-proj -> next q|k|v through it (llm._decode_step_chain)."""
+    assert 1 <= len(phases) <= 4
+    M = phases[0].x.shape[0]
+    arr = (_ChainPhaseC * len(phases))()
+    max_n = 0
+    for c, ph in zip(arr, phases):
+        _chk(ph.x, torch.bfloat16, "gemm_chain.x")
+        _chk(ph.out, torch.bfloat16, "gemm_chain.out")
+        assert isinstance(ph.w, TiledWeight) and ph.w.K == ph.x.shape[1] and ph.x.shape[0] == M and ph.x.stride(1) == 1
+        assert ph.w.gateup == bool(ph.swiglu) and ph.out.stride(1) == 1
+        assert tuple(ph.out.shape) == (M, ph.w.N // 2 if ph.swiglu else ph.w.N)
+        sc, parts = (None, 0) if ph.row_scale is None else ph.row_scale
+        if sc is not None:
+            _chk(sc, torch.float32, "gemm_chain.row_scale")
+            assert sc.is_contiguous() and sc.numel() >= (M if parts == 0 else parts * 64)
+        if ph.ssq_out is not None:
+            _chk(ph.ssq_out, torch.float32, "gemm_chain.ssq_out")
+            assert ph.ssq_out.is_contiguous() and ph.ssq_out.numel() >= (ph.w.N + 127) // 128 * 64
+        if ph.residual is not None:
+            _chk(ph.residual, torch.bfloat16, "gemm_chain.residual")
+            assert ph.residual.shape == ph.out.shape and ph.residual.stride(1) == 1
+        c.X, c.ldx, c.W_tiles = ph.x.data_ptr(), ph.x.stride(0), ph.w.data.data_ptr()
+        c.C, c.ldc = ph.out.data_ptr(), ph.out.stride(0)
+        c.residual, c.ldr = _p(ph.residual), 0 if ph.residual is None else ph.residual.stride(0)
+        c.scale_src, c.ssq_out = _p(sc), _p(ph.ssq_out)
+        c.N, c.K, c.scale_parts, c.swiglu, c.eps, c.reserved = ph.w.N, ph.w.K, int(parts), int(bool(ph.swiglu)), float(ph.eps), 0
+        max_n = max(max_n, ph.w.N)
+    dev = phases[0].x.device
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    need = int(_l.lib().raw("esb_gemm_chain_workspace_bytes")(64, max(max_n, 65536)))
+    ws = _chain_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, device=dev, dtype=torch.uint8)
+        _chain_ws[key] = ws
+    _l.call("esb_gemm_chain_bf16", ctypes.addressof(arr), len(phases), M, ws.data_ptr(), ws.numel(),
+            2 if (weights_const and pdl_enabled) else 0, _stream())
 
 
 def gemm_skinny(a: torch.Tensor, w, residual: Optional[torch.Tensor] = None,
@@ -174,6 +250,9 @@ def _env_flag(name: str, default: bool) -> bool:
     return default if v is None else v not in ("0", "false", "False", "")
 
 
+# decode step with the Linears between two attention calls as one persistent launch (llm._decode_step_chain, csrc/gemm_chain.cu);
+# norms folded as above, SwiGLU in the gate|up epilogue: 3 kernels per layer instead of 9.  ESB_DECODE_CHAIN=0 restores the plain step.
+decode_chain_enabled = _env_flag("ESB_DECODE_CHAIN", True)
 fuse_swiglu = _env_flag("ESB_FUSE_SWIGLU", True)        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
 # d(act) GEMM + dSwiGLU (esb_gemm_dswiglu_bf16): bit-identical, but OFF - the epilogue has to read gate|up with one row per thread
 # (TMEM lane = row), 32 lines per load instruction; measured 620 / 1003 / 1243 us per layer in three variants against 439-534 us

@@ -123,6 +123,38 @@ int esb_gemm_skinny_normed_bf16(const void* X, int64_t ldx, const void* W, int64
                                 const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,
                                 int w_tiled, const float* scale_src, int scale_parts, float eps, float* ssq_out, void* stream);
 
+/* The Linear layers BETWEEN two attention calls of the cached token step as ONE persistent launch (csrc/gemm_chain.cu):
+ *   o-proj (+residual) -> gate|up (+SwiGLU) -> down-proj (+residual) -> next layer's q|k|v projection (or lm_head),
+ * HF LlamaDecoderLayer.forward / LlamaMLP.forward / lm_head as reached from generate() (model_arch.py:94-108 ->
+ * pointllm.py:255-275, :173-178, :228).  Up to 4 phases; phase i+1 may read what phase i wrote (grid-wide hand-off inside the
+ * kernel), the weight stream runs ahead across the hand-off.  Each phase is an esb_gemm_skinny_normed_bf16 (same meaning of
+ * residual / scale_src / scale_parts / eps / ssq_out, K = the length the mean of squares is taken over) on a TILED weight image;
+ * swiglu != 0: W_tiles is the esb_retile_weight_gateup_bf16 image of the packed [2f, K] gate|up weight (N = 2f) and
+ * C[M, f] = bf16(bf16(silu(gate)) * up) of the bf16-rounded projections (HF LlamaMLP act_fn(gate_proj(x)) * up_proj(x)).
+ * workspace: esb_gemm_chain_workspace_bytes(M, largest N) bytes, first 16 KiB ZERO on first use (left zero), private to this
+ * entry point.  flags bit 1 (value 2): programmatic dependent launch as for esb_gemm_skinny_bf16.  All CTAs of the launch must
+ * be co-resident: do not run it concurrently with other work on the same GPU. */
+typedef struct esb_chain_phase {
+    const void* X;          /* [M, K] bf16 activations */
+    int64_t ldx;
+    const void* W_tiles;
+    void* C;                /* [M, N] bf16 (swiglu: [M, N/2]) */
+    int64_t ldc;
+    const void* residual;   /* NULL or [M, N] bf16 */
+    int64_t ldr;
+    const float* scale_src;
+    float* ssq_out;
+    int32_t N, K, scale_parts, swiglu;
+    float eps;
+    int32_t reserved;
+} esb_chain_phase;
+int64_t esb_gemm_chain_workspace_bytes(int M, int max_N);
+int esb_gemm_chain_bf16(const void* phases, int n_phases, int M, void* workspace, int64_t workspace_bytes, int flags, void* stream);
+/* [2f, K] packed gate|up weight -> [ceil(f/64)][ceil(K/64)][128][64] tiles whose rows 0..63 are gate rows t*64.. and rows 64..127
+ * the up rows f + t*64.. (zero padded); col_scale (NULL or bf16 [K]) folds a norm weight into the columns. */
+int64_t esb_retiled_gateup_elems(int f, int K);
+int esb_retile_weight_gateup_bf16(const void* W, int64_t ldw, int f, int K, const void* col_scale, void* out, void* stream);
+
 /* ------------------------------------------------------------------------------------------------ trajectory tokens
  * utils/utils.py:13-16 discretize_action: out[i] = np.digitize(x[i], np.linspace(-1,1,num_bins)) - 1 + id_offset
  * (bit-exact incl. edge values, NaN -> num_bins-1, x < -1 -> -1).  x: float32 (is_f64=0) or float64. */

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""Times the cached token step of generate() (B=32, P=544) in four variants: {CUDA graph, eager} x {skinny split-K
-GEMMs on tiled weights, general tcgen05 GEMM}.  ms/token = (t(T) - t(1)) / (T - 1)."""
+"""Times the cached token step of generate() (B=32, P=544) in five variants: the persistent Linear chain (gemm_chain.cu), skinny
+split-K GEMMs on tiled weights with / without folded norms / without programmatic launch, and the general tcgen05 GEMM.  ms/token = (t(T) - t(1)) / (T - 1)."""
 import os
 import sys
 
@@ -32,16 +32,20 @@ def run(t_new, graph):
     return e0.elapsed_time(e1)
 
 
-VARIANTS = {"fold_norm": (True, True, True), "plain": (True, True, False), "no_pdl": (True, False, False), "general_gemm": (False, False, False)}
+VARIANTS = {"chain": (True, True, True, True), "fold_norm": (True, True, True, False), "plain": (True, True, False, False),
+            "no_pdl": (True, False, False, False), "general_gemm": (False, False, False, False)}
+if os.environ.get("DECODE_VARIANTS"):
+    VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ["DECODE_VARIANTS"].split(",") or k == "no_pdl"}
 best = {k: (1e9, 1e9) for k in VARIANTS}
 seqs = {}
 
 
-def select(skinny, pdl, fold):
+def select(skinny, pdl, fold, chain):
     ops.SKINNY_MAX_M = 64 if skinny else 0
     ops.skinny_enabled = skinny
     ops.pdl_enabled = pdl
     ops.fold_norm_enabled = fold
+    ops.decode_chain_enabled = chain
 
 
 for rnd in range(4):                                     # round-robin so that a throttling episode hits every variant alike
