@@ -7,8 +7,8 @@
 // Why one launch: with M = 32 tokens every Linear is a weight stream (HBM bound), and as separate launches each of the 129
 // GEMMs of a token step pays pipeline fill, split-K tail and drain (~8 us against 8-28 us of streaming,
 // profiles/r01_decode_launches_v3.txt).  Here the weight stream never stops:
-//   * 2 persistent CTAs per SM; the TMA producer warp of each runs ahead ACROSS phases - weights do not depend on the previous
-//     phase, so while a phase drains (reduction tail, grid-wide hand-off) the ring already holds the next phase's tiles;
+//   * one persistent CTA per SM with a 10-stage ring (200 KiB of weights in flight per SM); its TMA producer warp runs ahead
+//     ACROSS phases - weights do not depend on the previous phase, so while a phase drains (reduction tail, grid-wide hand-off) the ring already holds the next phase's tiles;
 //   * stream-K: each phase's (128-row weight tile x 64-column k-block) units are cut into G equal contiguous ranges, so all CTAs
 //     stream the same number of bytes whatever N and K are; a tile split over several CTAs is summed in fixed order by the last
 //     contributor (fp32 partials through L2, per-tile counters) - deterministic for a given SM count;
@@ -140,7 +140,7 @@ ESB_DEVICE void emit16(const ChainPhase& ph, int M, float (&v)[16], int m0, int 
 }
 
 template <int BT, int STAGES>
-__global__ void __launch_bounds__(CH_THREADS, 2)
+__global__ void __launch_bounds__(CH_THREADS, 1)
 gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainParams p) {
     using S = ChainSmem<BT, STAGES>;
     extern __shared__ uint8_t smem_raw[];
@@ -408,25 +408,33 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
     }
 }
 
+// CTAs of this instantiation the runtime keeps resident per SM (0: the kernel cannot launch).  The phase hand-off needs every CTA
+// of the grid resident, so the grid is sized from this number.  Measured on B200: the occupancy query answers 1 for this kernel
+// whatever its shared-memory / register footprint (80 KB and 124 registers included; the same query on gemm_skinny's <32, 4>
+// kernel also answers 1), hence ONE CTA per SM with a ring deep enough to hold the bytes two CTAs would have had in flight.
+template <int BT, int STAGES>
+int chain_ctas_per_sm() {
+    using S = ChainSmem<BT, STAGES>;
+    static int per_sm = -1;
+    if (per_sm < 0) {
+        auto kernel = gemm_chain_tcgen05_kernel<BT, STAGES>;
+        int n = 0;
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, CH_THREADS, S::TOTAL);
+        if (e != cudaSuccess) {
+            set_last_error("gemm_chain<%d,%d>: %s", BT, STAGES, cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            n = 0;
+        }
+        per_sm = n;
+    }
+    return per_sm;
+}
+
 template <int BT, int STAGES>
 int launch_chain_kernel(const ChainMaps& maps, const ChainParams& p, bool pdl, cudaStream_t stream) {
     using S = ChainSmem<BT, STAGES>;
     auto kernel = gemm_chain_tcgen05_kernel<BT, STAGES>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-        if (e != cudaSuccess) {
-            set_last_error("cudaFuncSetAttribute(gemm_chain<%d>): %s", BT, cudaGetErrorString(e));
-            return ESB_ERR_CUDA;
-        }
-        int per_sm = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, CH_THREADS, S::TOTAL);
-        if (e != cudaSuccess || per_sm < 2) {     // the phase hand-off needs every CTA of the grid resident
-            set_last_error("gemm_chain<%d>: %d CTAs per SM resident, 2 needed (%s)", BT, per_sm, cudaGetErrorString(e));
-            return ESB_ERR_CUDA;
-        }
-        attr_set = true;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p.grid);
     cfg.blockDim = dim3(CH_THREADS);
@@ -445,11 +453,16 @@ int launch_chain_kernel(const ChainMaps& maps, const ChainParams& p, bool pdl, c
     return check_launch("gemm_chain_tcgen05");
 }
 
+constexpr int CH_STAGES_32 = 10;      // 10 x 20 KiB
+constexpr int CH_STAGES_64 = 8;       //  8 x 24 KiB
+
 }  // namespace
+
+int gemm_chain_ctas_per_sm(int M) { return M <= 32 ? chain_ctas_per_sm<32, CH_STAGES_32>() : chain_ctas_per_sm<64, CH_STAGES_64>(); }
 
 long long gemm_chain_workspace_bytes(int M, int max_N) {
     const int bt = M <= 32 ? 32 : 64;
-    const long long slots = (max_N + 63) / 64 + 2 * device_sm_count();
+    const long long slots = (max_N + 63) / 64 + 2 * device_sm_count();      // grid <= 2 CTAs per SM
     return CH_COUNTER_BYTES + slots * bt * CH_ROWS * 4;
 }
 
@@ -461,7 +474,9 @@ int gemm_chain_bf16(const esb_chain_phase* phases, int n_phases, int M, void* wo
         return ESB_ERR_INVALID_ARG;
     }
     const int bt = M <= 32 ? 32 : 64;
-    const int grid = 2 * device_sm_count();
+    const int per_sm = gemm_chain_ctas_per_sm(M);
+    if (per_sm < 1) return ESB_ERR_CUDA;
+    const int grid = device_sm_count() * (per_sm < 2 ? per_sm : 2);
     ChainMaps maps;
     ChainParams p;
     memset(&maps, 0, sizeof(maps));
@@ -506,7 +521,7 @@ int gemm_chain_bf16(const esb_chain_phase* phases, int n_phases, int M, void* wo
     p.grid_ctr = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(workspace) + 12288);
     p.partial = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + CH_COUNTER_BYTES);
     const bool pdl = (flags & 2) != 0;            // caller promises no weight image is written by the kernel launched just before
-    return bt == 32 ? launch_chain_kernel<32, 5>(maps, p, pdl, stream) : launch_chain_kernel<64, 4>(maps, p, pdl, stream);
+    return bt == 32 ? launch_chain_kernel<32, CH_STAGES_32>(maps, p, pdl, stream) : launch_chain_kernel<64, CH_STAGES_64>(maps, p, pdl, stream);
 }
 
 }  // namespace esb
