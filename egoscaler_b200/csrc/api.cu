@@ -101,6 +101,7 @@ int esb_gemm_skinny_normed_bf16(const void* X, int64_t ldx, const void* W, int64
 
 int64_t esb_gemm_chain_workspace_bytes(int M, int max_N) { return gemm_chain_workspace_bytes(M, max_N); }
 int64_t esb_gemm_chain_ctas_per_sm(int M) { return gemm_chain_ctas_per_sm(M); }
+int esb_gemm_chain_debug_buffer(void* buf) { return gemm_chain_debug_buffer(buf); }
 int esb_gemm_chain_bf16(const void* phases, int n_phases, int M, void* workspace, int64_t workspace_bytes, int flags, void* stream) {
     return gemm_chain_bf16(static_cast<const esb_chain_phase*>(phases), n_phases, M, workspace, workspace_bytes, flags, ST(stream));
 }

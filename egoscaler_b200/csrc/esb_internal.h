@@ -78,6 +78,7 @@ long long retiled_gateup_elems(int f, int K);
 int retile_weight_gateup_bf16(const void* W, long long ldw, int f, int K, const void* col_scale, void* out, cudaStream_t stream);
 long long gemm_chain_workspace_bytes(int M, int max_N);
 int gemm_chain_ctas_per_sm(int M);
+int gemm_chain_debug_buffer(void* buf);
 }  // namespace esb
 struct esb_chain_phase;      // include/egoscaler_b200.h
 namespace esb {

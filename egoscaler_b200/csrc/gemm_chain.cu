@@ -21,6 +21,7 @@
 #include "esb_internal.h"
 #include "../../include/egoscaler_b200.h"
 #include <cstring>
+#include <cstdlib>
 
 namespace esb {
 
@@ -46,12 +47,15 @@ struct ChainPhase {
     int N;                       // output columns (SwiGLU: f)
     int n_tiles, num_kb;
     int swiglu;
+    int vec4;                    // C / residual rows allow 8-byte accesses at columns that are multiples of 4
     int total;                   // n_tiles * num_kb
     int g_eff;                   // CTAs that take part in this phase = min(grid, total)
 };
 
 struct ChainParams {
     int M, n_phases, grid;
+    long long* dbg;              // NULL, or [grid][CH_MAX_PHASES][8] globaltimer stamps (esb_gemm_chain_debug_buffer)
+    int pf_dist;                 // weight blocks (16 KiB) requested into L2 ahead of the ring, per CTA
     ChainPhase ph[CH_MAX_PHASES];
     float* partial;              // [n_tiles_max + grid][BT][128] fp32
     int* counters;
@@ -86,6 +90,17 @@ ESB_DEVICE void wait_counter(const int* ctr, int target) {
 // CTA c of g_eff owns units [c * total / g_eff, (c + 1) * total / g_eff); the owner of unit b follows from the same formula
 ESB_DEVICE int range_start(int c, int total, int g) { return static_cast<int>(static_cast<long long>(c) * total / g); }
 ESB_DEVICE int unit_owner(int b, int total, int g) { return static_cast<int>((static_cast<long long>(b + 1) * g - 1) / total); }
+
+ESB_DEVICE long long gtime() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define CH_STAMP(pi, ev) do { if (p.dbg) p.dbg[(static_cast<size_t>(cta) * CH_MAX_PHASES + (pi)) * 8 + (ev)] = gtime(); } while (0)
+
+ESB_DEVICE void l2_prefetch(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 
 // Finish 16 tokens (m0 .. m0+15) of weight row `nl` of `tile`: v[] holds the complete fp32 sums.  Called by all 128 epilogue
 // threads with the same (tile, m0) - it contains named barriers.
@@ -139,6 +154,81 @@ ESB_DEVICE void emit16(const ChainPhase& ph, int M, float (&v)[16], int m0, int 
     }
 }
 
+// Finish up to 4 tokens (mm[0..3]; >= M: none) of a tile whose sums were just rebuilt from the partials: this thread holds the four weight
+// rows 4*lane .. 4*lane+3 of the tile for each token (one warp covers all 128 rows of a token, so a token's sum of squares is a
+// warp reduction).  Shuffles only - warps may call it independently.
+ESB_DEVICE void emit_rows(const ChainPhase& ph, int M, const float4 (&acc)[4], const int (&mm)[4], int tile, int lane, bool scaled,
+                          const float* s_scale) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int m = mm[r];
+        const bool m_ok = m < M;                                   // warp-uniform
+        const float sc = (scaled && m_ok) ? s_scale[m] : 1.0f;
+        float v[4] = {acc[r].x * sc, acc[r].y * sc, acc[r].z * sc, acc[r].w * sc};
+        if (!ph.swiglu) {
+            const int n0 = tile * CH_ROWS + 4 * lane;
+            float sq = 0.0f;
+            if (m_ok && n0 < ph.N) {
+                __nv_bfloat16* cp = ph.C + static_cast<long long>(m) * ph.ldc + n0;
+                if (ph.vec4 && n0 + 3 < ph.N) {
+                    if (ph.res) {
+                        const uint2 ru = __ldcg(reinterpret_cast<const uint2*>(ph.res + static_cast<long long>(m) * ph.ldr + n0));
+                        const float2 r01 = unpack_bf16x2(ru.x), r23 = unpack_bf16x2(ru.y);
+                        v[0] += r01.x; v[1] += r01.y; v[2] += r23.x; v[3] += r23.y;
+                    }
+                    uint2 ou;
+                    ou.x = pack_bf16x2(v[0], v[1]);
+                    ou.y = pack_bf16x2(v[2], v[3]);
+                    *reinterpret_cast<uint2*>(cp) = ou;
+                    const float2 o01 = unpack_bf16x2(ou.x), o23 = unpack_bf16x2(ou.y);
+                    sq = o01.x * o01.x + o01.y * o01.y + o23.x * o23.x + o23.y * o23.y;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        if (n0 + e >= ph.N) break;
+                        float o = v[e];
+                        if (ph.res)
+                            o += __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(ph.res) + static_cast<long long>(m) * ph.ldr + n0 + e)));
+                        const __nv_bfloat16 ob = __float2bfloat16_rn(o);
+                        cp[e] = ob;
+                        const float of = __bfloat162float(ob);
+                        sq += of * of;
+                    }
+                }
+            }
+            if (ph.ssq_out) {
+                sq = warp_sum(sq);
+                if (lane == 0 && m_ok) ph.ssq_out[tile * 64 + m] = sq;
+            }
+        } else {
+            // lanes 0..15 hold gate columns tile*64 + 4*lane .., lane + 16 the matching up columns
+            float u[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                v[e] = bf16_round(v[e]);
+                u[e] = __shfl_xor_sync(0xffffffffu, v[e], 16);
+            }
+            const int col = tile * 64 + 4 * lane;
+            if (m_ok && lane < 16 && col < ph.N) {
+                __nv_bfloat16* cp = ph.C + static_cast<long long>(m) * ph.ldc + col;
+                float a4[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) a4[e] = bf16_round(silu(v[e])) * u[e];
+                if (ph.vec4 && col + 3 < ph.N) {
+                    uint2 ou;
+                    ou.x = pack_bf16x2(a4[0], a4[1]);
+                    ou.y = pack_bf16x2(a4[2], a4[3]);
+                    *reinterpret_cast<uint2*>(cp) = ou;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (col + e < ph.N) cp[e] = __float2bfloat16_rn(a4[e]);
+                }
+            }
+        }
+    }
+}
+
 template <int BT, int STAGES>
 __global__ void __launch_bounds__(CH_THREADS, 1)
 gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainParams p) {
@@ -187,6 +277,8 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
             // ===================== TMA producer.  Weight tiles are requested as soon as a ring stage is free, also across a
             // phase boundary; the activation tile of a stage follows once the phase's input is complete (phase 0: the previous
             // kernel of the stream, griddepcontrol.wait; later phases: every CTA has finished the previous phase).
+            // While this thread waits for a phase's input (~8 us of dependent latencies: reduction tail, counter, fences), the
+            // next pf_dist weight blocks beyond the ring are requested into L2, so that HBM keeps streaming through the hand-off.
             int stage = 0;
             uint32_t phase = 0;
             for (int pi = 0; pi < p.n_phases; ++pi) {
@@ -195,12 +287,16 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                 if (cta < ph.g_eff) { b = range_start(cta, ph.total, ph.g_eff); end = range_start(cta + 1, ph.total, ph.g_eff); }
                 if (b >= end) continue;
                 int tile = b / ph.num_kb, kb = b - tile * ph.num_kb;
+                CH_STAMP(pi, 0);
                 bool ready = false;
                 int n_pend = 0;
                 int pend_stage[STAGES], pend_kb[STAGES];
                 auto flush = [&]() {
+                    for (int i = 0; i < p.pf_dist && b + i < end; ++i)
+                        l2_prefetch(ph.w_tiles + static_cast<size_t>(b + i) * CH_W_BYTES, CH_W_BYTES);
                     if (pi == 0) griddep_wait();
                     else { wait_counter(p.grid_ctr, pi * p.grid); fence_proxy_async_all(); }
+                    CH_STAMP(pi, 1);
                     for (int i = 0; i < n_pend; ++i)
                         tma_load_2d_hint(smem + pend_stage[i] * S::STAGE_BYTES + CH_W_BYTES, &maps.x[pi], &full_bar[pend_stage[i]],
                                          pend_kb[i] * CH_BK, 0, kEvictLast);
@@ -216,6 +312,7 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                                       &full_bar[stage], kEvictFirst);
                     if (ready) tma_load_2d_hint(sw + CH_W_BYTES, &maps.x[pi], &full_bar[stage], kb * CH_BK, 0, kEvictLast);
                     else { pend_stage[n_pend] = stage; pend_kb[n_pend] = kb; ++n_pend; }
+
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                     if (++kb == ph.num_kb) { kb = 0; ++tile; }
                 }
@@ -234,6 +331,7 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                 const ChainPhase& ph = p.ph[pi];
                 int b = 0, end = 0;
                 if (cta < ph.g_eff) { b = range_start(cta, ph.total, ph.g_eff); end = range_start(cta + 1, ph.total, ph.g_eff); }
+                bool first = true;
                 while (b < end) {
                     const int tile = b / ph.num_kb, kb0 = b - tile * ph.num_kb;
                     const int nkb = min(ph.num_kb - kb0, end - b);
@@ -243,6 +341,7 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                     for (int i = 0; i < nkb; ++i) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
+                        if (first) { CH_STAMP(pi, 2); first = false; }
                         const uint32_t sw = smem_u32(smem + stage * S::STAGE_BYTES);
                         const uint64_t da = umma_desc_kmajor_sw128(sw);
                         const uint64_t db = umma_desc_kmajor_sw128(sw + CH_W_BYTES);
@@ -258,6 +357,7 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                     if (acc == 0) acc_phase ^= 1u;
                     b += nkb;
                 }
+                if (!first) CH_STAMP(pi, 3);
             }
         }
     } else {
@@ -274,6 +374,7 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                 if (nl == 0) wait_counter(p.grid_ctr, pi * p.grid);
                 ch_epi_sync();
             }
+            if (nl == 0) CH_STAMP(pi, 4);
             int b = 0, end = 0;
             if (cta < ph.g_eff) { b = range_start(cta, ph.total, ph.g_eff); end = range_start(cta + 1, ph.total, ph.g_eff); }
             const bool scaled = ph.scale_src != nullptr;
@@ -292,6 +393,9 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                 }
                 ch_epi_sync();
             }
+            // split tiles this CTA contributed to: at most its first and its last tile
+            int n_def = 0;
+            int def_tile[2], def_c0[2], def_n[2];
             while (b < end) {
                 const int tile = b / ph.num_kb, kb0 = b - tile * ph.num_kb;
                 const int nkb = min(ph.num_kb - kb0, end - b);
@@ -339,49 +443,14 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                     mbar_arrive(&tmem_empty[acc]);
                     __threadfence();
                     ch_epi_sync();
-                    if (nl == 0) {
-                        const int prev = atomicAdd(&p.counters[tile], 1);
-                        const int last = (prev == n_contrib - 1) ? 1 : 0;
-                        if (last) p.counters[tile] = 0;           // nobody else touches this counter again in this phase
-                        *last_flag = last;
-                    }
-                    ch_epi_sync();
-                    const bool is_last = *last_flag != 0;
-                    ch_epi_sync();                                // last_flag may be rewritten by the next segment
-                    if (!is_last) { acc ^= 1; if (acc == 0) acc_phase ^= 1u; continue; }
-                    __threadfence();
-                    const float* base = p.partial + static_cast<size_t>(tile + c0) * (BT * CH_ROWS) + nl;
-#pragma unroll 1
-                    for (int m0 = 0; m0 < p.M; m0 += 16) {
-                        float v[16];
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] = 0.0f;
-                        int s2 = 0;
-#pragma unroll 1
-                        for (; s2 + 4 <= n_contrib; s2 += 4) {    // fixed order, 4 slices x 16 tokens of loads in flight
-                            float t[4][16];
-#pragma unroll
-                            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                                for (int j = 0; j < 16; ++j)
-                                    t[i][j] = __ldcg(base + (static_cast<size_t>(s2 + i) * BT + m0 + j) * CH_ROWS);
-#pragma unroll
-                            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                                for (int j = 0; j < 16; ++j) v[j] += t[i][j];
-                        }
-#pragma unroll 1
-                        for (; s2 < n_contrib; ++s2) {
-                            float t[16];
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) t[j] = __ldcg(base + (static_cast<size_t>(s2) * BT + m0 + j) * CH_ROWS);
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] += t[j];
-                        }
-                        emit16(ph, p.M, v, m0, tile, nl, q, lane, scaled, s_scale, s_red, s_x);
-                    }
+                    if (nl == 0) atomicAdd(&p.counters[tile], 1);      // arrival; the sums are rebuilt after the last segment (below)
+                    def_tile[n_def] = tile; def_c0[n_def] = c0; def_n[n_def] = n_contrib;
+                    ++n_def;
+                    acc ^= 1;
+                    if (acc == 0) acc_phase ^= 1u;
+                    continue;
                 }
-                if (ph.ssq_out) {                                 // reached only by the thread group that finished the tile
+                if (ph.ssq_out) {                                 // direct path: the tile was finished from TMEM by emit16
                     ch_epi_sync();
                     if (nl < p.M) ph.ssq_out[tile * 64 + nl] = s_red[0][nl] + s_red[1][nl] + s_red[2][nl] + s_red[3][nl];
                     ch_epi_sync();
@@ -389,13 +458,62 @@ gemm_chain_tcgen05_kernel(const __grid_constant__ ChainMaps maps, const __grid_c
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1u;
             }
+            // Every split tile is rebuilt by ALL its contributors, contributor k taking the tokens m = k (mod n): the phase ends
+            // with 148 CTAs each summing a few token rows (16-byte loads, fixed order s = 0..n-1) instead of 32..172 CTAs each
+            // summing a whole tile (8-28 us of dependent L2 round trips at the tail of every phase, tools/chain_trace.py).
+            // counters[tile]: n arrivals, then n completions; the last completion leaves it at zero.
+            for (int di = 0; di < n_def; ++di) {
+                const int tile = def_tile[di], c0 = def_c0[di], n_contrib = def_n[di];
+                if (nl == 0) wait_counter(&p.counters[tile], n_contrib);
+                ch_epi_sync();
+                const float* base = p.partial + static_cast<size_t>(tile + c0) * (BT * CH_ROWS) + 4 * lane;
+                const int my = cta - c0;
+#pragma unroll 1
+                for (int i0 = 4 * q; ; i0 += 16) {                      // warp q: the share's tokens 4q .. 4q+3, 4q+16 .., ...
+                    int mm[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const int m = my + n_contrib * (i0 + r);
+                        mm[r] = m < p.M ? m : p.M;
+                    }
+                    if (mm[0] >= p.M) break;
+                    float4 a4[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) a4[r] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 1
+                    for (int s2 = 0; s2 < n_contrib; s2 += 4) {
+                        float4 t[4][4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int r = 0; r < 4; ++r)
+                                t[i][r] = (s2 + i < n_contrib && mm[r] < p.M)
+                                              ? __ldcg(reinterpret_cast<const float4*>(base + (static_cast<size_t>(s2 + i) * BT + mm[r]) * CH_ROWS))
+                                              : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int r = 0; r < 4; ++r) {
+                                a4[r].x += t[i][r].x; a4[r].y += t[i][r].y; a4[r].z += t[i][r].z; a4[r].w += t[i][r].w;
+                            }
+                    }
+                    emit_rows(ph, p.M, a4, mm, tile, lane, scaled, s_scale);
+                }
+                ch_epi_sync();                                        // all loads of the share are done
+                if (nl == 0) {
+                    const int prev = atomicAdd(&p.counters[tile], 1);
+                    if (prev == 2 * n_contrib - 1) p.counters[tile] = 0;      // every contributor has arrived and finished
+                }
+            }
             // hand-off: everything this CTA wrote in the phase is visible before the counter moves
+            if (nl == 0) CH_STAMP(pi, 5);
             __threadfence();
             fence_proxy_async_all();                              // the next phase reads these rows through TMA (async proxy)
             ch_epi_sync();
             if (nl == 0) {
                 const int prev = atomicAdd(p.grid_ctr, 1);
                 if (prev + 1 == p.n_phases * p.grid) *p.grid_ctr = 0;      // last arrival of the launch: nobody polls any more
+                CH_STAMP(pi, 6);
             }
         }
     }
@@ -458,6 +576,9 @@ constexpr int CH_STAGES_64 = 8;       //  8 x 24 KiB
 
 }  // namespace
 
+static long long* g_chain_dbg = nullptr;
+int gemm_chain_debug_buffer(void* buf) { g_chain_dbg = static_cast<long long*>(buf); return ESB_OK; }
+
 int gemm_chain_ctas_per_sm(int M) { return M <= 32 ? chain_ctas_per_sm<32, CH_STAGES_32>() : chain_ctas_per_sm<64, CH_STAGES_64>(); }
 
 long long gemm_chain_workspace_bytes(int M, int max_N) {
@@ -482,6 +603,15 @@ int gemm_chain_bf16(const esb_chain_phase* phases, int n_phases, int M, void* wo
     memset(&maps, 0, sizeof(maps));
     memset(&p, 0, sizeof(p));
     p.M = M; p.n_phases = n_phases; p.grid = grid;
+    static int pf_dist = -1;
+    if (pf_dist < 0) {
+        const char* e = getenv("ESB_CHAIN_PREFETCH");      // tuning aid; default measured with tools/chain_bench.py
+        pf_dist = e ? atoi(e) : 0;           // measured: 109 / 111 / 112 / 116 us per layer at 0 / 8 / 16 / 32 blocks - off
+        if (pf_dist < 0) pf_dist = 0;
+        if (pf_dist > 256) pf_dist = 256;
+    }
+    p.pf_dist = pf_dist;
+    p.dbg = g_chain_dbg;
     long long max_tiles = 0;
     for (int i = 0; i < n_phases; ++i) {
         const esb_chain_phase& s = phases[i];
@@ -498,6 +628,8 @@ int gemm_chain_bf16(const esb_chain_phase* phases, int n_phases, int M, void* wo
         d.scale_src = s.scale_src; d.ssq_out = s.ssq_out; d.scale_parts = s.scale_parts;
         d.scale_inv_d = 1.0f / static_cast<float>(s.K); d.scale_eps = s.eps;
         d.swiglu = s.swiglu ? 1 : 0;
+        d.vec4 = ((s.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(s.C) & 7) == 0 &&
+                  (!s.residual || ((s.ldr & 3) == 0 && (reinterpret_cast<uintptr_t>(s.residual) & 7) == 0))) ? 1 : 0;
         d.N = s.swiglu ? s.N / 2 : s.N;
         d.n_tiles = s.swiglu ? (d.N + 63) / 64 : (d.N + CH_ROWS - 1) / CH_ROWS;
         d.num_kb = (s.K + CH_BK - 1) / CH_BK;

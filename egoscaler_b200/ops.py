@@ -251,8 +251,11 @@ def _env_flag(name: str, default: bool) -> bool:
 
 
 # decode step with the Linears between two attention calls as one persistent launch (llm._decode_step_chain, csrc/gemm_chain.cu);
-# norms folded as above, SwiGLU in the gate|up epilogue: 3 kernels per layer instead of 9.  ESB_DECODE_CHAIN=0 restores the plain step.
-decode_chain_enabled = _env_flag("ESB_DECODE_CHAIN", True)
+# norms folded as above, SwiGLU in the gate|up epilogue: 3 kernels per layer instead of 9.  OFF (ESB_DECODE_CHAIN=1 enables it):
+# the four Linears of a layer take 109 us in the chain against 108.5 us as four launches (tools/chain_bench.py) and the token step
+# 5.95 against 5.49-5.61 ms (tools/decode_variants.py) - an in-kernel hand-off between dependent phases costs what a kernel
+# boundary with programmatic launch costs: ~6 dependent L2 round trips of ~1.3 us (tools/chain_trace.py).
+decode_chain_enabled = _env_flag("ESB_DECODE_CHAIN", False)
 fuse_swiglu = _env_flag("ESB_FUSE_SWIGLU", True)        # gate|up GEMM + silu*mul            (esb_gemm_swiglu_bf16)
 # d(act) GEMM + dSwiGLU (esb_gemm_dswiglu_bf16): bit-identical, but OFF - the epilogue has to read gate|up with one row per thread
 # (TMEM lane = row), 32 lines per load instruction; measured 620 / 1003 / 1243 us per layer in three variants against 439-534 us

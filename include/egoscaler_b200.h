@@ -149,6 +149,9 @@ typedef struct esb_chain_phase {
     int32_t reserved;
 } esb_chain_phase;
 int64_t esb_gemm_chain_workspace_bytes(int M, int max_N);
+/* diagnostics: buf = NULL (off) or a device buffer of (2 * SM count) * 4 * 8 int64 that later launches fill with %globaltimer
+ * stamps per CTA and phase (tools/chain_trace.py) */
+int esb_gemm_chain_debug_buffer(void* buf);
 int64_t esb_gemm_chain_ctas_per_sm(int M);      /* resident CTAs per SM the grid is sized from; 0 = the kernel cannot run here */
 int esb_gemm_chain_bf16(const void* phases, int n_phases, int M, void* workspace, int64_t workspace_bytes, int flags, void* stream);
 /* [2f, K] packed gate|up weight -> [ceil(f/64)][ceil(K/64)][128][64] tiles whose rows 0..63 are gate rows t*64.. and rows 64..127

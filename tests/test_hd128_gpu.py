@@ -90,13 +90,20 @@ def test_trained_logits_and_loss_vs_reference(trained):
                           bt["tokens"][:, P:].numpy()[bt["tokens"][:, P:].numpy() != 0])       # teacher-forced arg-max = targets
 
 
-@pytest.mark.parametrize("graph", [False, True])
-def test_trained_greedy_decode_emits_the_reference_trajectory(trained, graph):
+@pytest.mark.parametrize("graph,chain", [(False, False), (True, False), (False, True), (True, True)])
+def test_trained_greedy_decode_emits_the_reference_trajectory(trained, graph, chain):
+    """``chain``: the token step with the Linears between two attention calls as one persistent launch (ops.gemm_chain,
+    llm._decode_step_chain) instead of one launch per Linear - same reference trajectory either way."""
     m, g, bt = trained
     ref = g["greedy_ids"]                                              # [2, 135]: 19 x (6 bins + <tsep>) + <te> + </s>
     T = 152
-    out = m.generate(input_ids=bt["prompts"], attention_mask=bt["prompt_masks"], point_clouds=bt["pcrgbs"], max_length=T,
-                     do_sample=False, fps_start=torch.from_numpy(g["fps_start"]), use_cuda_graph=graph)
+    keep = ops.decode_chain_enabled
+    ops.decode_chain_enabled = chain
+    try:
+        out = m.generate(input_ids=bt["prompts"], attention_mask=bt["prompt_masks"], point_clouds=bt["pcrgbs"], max_length=T,
+                         do_sample=False, fps_start=torch.from_numpy(g["fps_start"]), use_cuda_graph=graph)
+    finally:
+        ops.decode_chain_enabled = keep
     P = bt["prompts"].shape[1]
     gen = out.sequences[:, P:].cpu().numpy()
     n = ref.shape[1]
