@@ -84,6 +84,11 @@ int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw,
     return gemm_skinny_bf16(X, ldx, W, ldw, C, ldc, M, N, K, residual, ldr, workspace, workspace_bytes, force_splits,
                             w_tiled, ST(stream));
 }
+int64_t esb_gemm_skinny_static_scratch_bytes(void) { return gemm_skinny_static_scratch_bytes(); }
+int esb_gemm_skinny_static_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
+                                const void* residual, int64_t ldr, int force_splits, int w_tiled, void* stream) {
+    return gemm_skinny_static_bf16(X, ldx, W, ldw, C, ldc, M, N, K, residual, ldr, force_splits, w_tiled, ST(stream));
+}
 int64_t esb_retiled_weight_elems(int N, int K) { return retiled_weight_elems(N, K); }
 int esb_retile_weight_bf16(const void* W, int64_t ldw, int N, int K, void* out, void* stream) {
     return retile_weight_bf16(W, ldw, N, K, out, ST(stream));

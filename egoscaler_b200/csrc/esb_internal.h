@@ -71,6 +71,9 @@ int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw,
 int gemm_skinny_normed_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
                             const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,
                             int w_tiled, const float* scale_src, int scale_parts, float eps, float* ssq_out, cudaStream_t stream);
+long long gemm_skinny_static_scratch_bytes();
+int gemm_skinny_static_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                            const void* residual, long long ldr, int force_splits, int w_tiled, cudaStream_t stream);
 int retile_weight_scaled_bf16(const void* W, long long ldw, int N, int K, const void* col_scale, void* out, cudaStream_t stream);
 long long retiled_weight_elems(int N, int K);
 int retile_weight_bf16(const void* W, long long ldw, int N, int K, void* out, cudaStream_t stream);

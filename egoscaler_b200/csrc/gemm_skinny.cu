@@ -536,4 +536,70 @@ int gemm_skinny_normed_bf16(const void* X, long long ldx, const void* W, long lo
     return bt == 32 ? launch_skinny<32, 4>(tw, tx, p, grid, pdl, stream) : launch_skinny<64, 4>(tw, tx, p, grid, pdl, stream);
 }
 
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// esb_gemm_skinny_static_bf16: the same kernel with its split-K workspace in a file-scope device array instead of a caller
+// buffer - for callers that cannot allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds SK_STATIC_BYTES until exit.
+constexpr long long SK_STATIC_PARTIAL_BYTES = 8ll << 20;
+constexpr long long SK_STATIC_BYTES = SK_COUNTER_BYTES + SK_STATIC_PARTIAL_BYTES;        // 16 KiB counters + 8 MiB fp32 partials
+constexpr int SK_STATIC_MAX_N = 16384, SK_STATIC_MAX_K = 16384;
+constexpr int SK_STATIC_MAX_DEVICES = 64;
+
+}  // namespace esb
+
+// In host code this name is only a handle for cudaGetSymbolAddress - never a device address.
+static __device__ __align__(256) unsigned char g_esb_skinny_scratch[esb::SK_STATIC_BYTES];
+
+namespace esb {
+
+namespace {
+// device address of g_esb_skinny_scratch on the CURRENT device, resolved once per device
+int skinny_static_scratch(void** out) {
+    static void* ptrs[SK_STATIC_MAX_DEVICES] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= SK_STATIC_MAX_DEVICES) {
+        set_last_error("gemm_skinny_static_bf16: cudaGetDevice -> %d (%s)", dev, cudaGetErrorString(e));
+        return ESB_ERR_CUDA;
+    }
+    void* ptr = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (!ptr) {
+        e = cudaGetSymbolAddress(&ptr, g_esb_skinny_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_last_error("gemm_skinny_static_bf16: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return ESB_ERR_CUDA;
+        }
+        __atomic_store_n(&ptrs[dev], ptr, __ATOMIC_RELEASE);      // same value from every thread that races here
+    }
+    *out = ptr;
+    return ESB_OK;
+}
+}  // namespace
+
+long long gemm_skinny_static_scratch_bytes() { return SK_STATIC_BYTES; }
+
+int gemm_skinny_static_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
+                            const void* residual, long long ldr, int force_splits, int w_tiled, cudaStream_t stream) {
+    if (M <= 0 || N <= 0) return ESB_OK;
+    if (M > 64 || N > SK_STATIC_MAX_N || K > SK_STATIC_MAX_K) {
+        set_last_error("gemm_skinny_static_bf16: M=%d N=%d K=%d exceeds the static scratch limits (M <= 64, N <= %d, K <= %d); "
+                       "use esb_gemm_skinny_bf16 with a caller workspace", M, N, K, SK_STATIC_MAX_N, SK_STATIC_MAX_K);
+        return ESB_ERR_UNSUPPORTED;
+    }
+    void* scratch = nullptr;
+    int rc = skinny_static_scratch(&scratch);
+    if (rc) return rc;
+    // the tile counters must start at zero; the kernel leaves them at zero, but an aborted launch would not - clear them every call
+    // (a memset node, no allocation).  The partials need no clearing: every slot is written before it is read.
+    cudaError_t e = cudaMemsetAsync(scratch, 0, SK_COUNTER_BYTES, stream);
+    if (e != cudaSuccess) {
+        set_last_error("gemm_skinny_static_bf16: cudaMemsetAsync: %s", cudaGetErrorString(e));
+        return ESB_ERR_CUDA;
+    }
+    // no programmatic dependent launch (w_tiled bit 1 dropped): the kernel must not start before the memset has finished
+    return gemm_skinny_normed_bf16(X, ldx, W, ldw, C, ldc, M, N, K, residual, ldr, scratch, SK_STATIC_BYTES, force_splits, w_tiled & 1,
+                                   nullptr, 0, 0.0f, nullptr, stream);
+}
+
 }  // namespace esb

@@ -107,6 +107,17 @@ int64_t esb_gemm_skinny_workspace_bytes(int M, int N, int K);
 int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                          const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,
                          int w_tiled, void* stream);
+/* No counterpart in the reference: added for callers that cannot allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  esb_gemm_skinny_bf16 with its split-K
+ * workspace in a file-scope device array of the library (16 KiB of tile counters + 8 MiB of fp32 partials per GPU, held until
+ * exit) instead of a caller buffer; inputs and outputs are still the caller's.  Limits: M <= 64, N <= 16384, K <= 16384 -
+ * larger sizes are rejected with ESB_ERR_UNSUPPORTED (use esb_gemm_skinny_bf16).  Calls no cudaMalloc / cudaFree / allocating
+ * library routine; the counters are cleared by a cudaMemsetAsync on `stream` in every call, and w_tiled bit 1 (programmatic
+ * launch) is ignored.  ALL calls on one GPU share the array: calls that overlap on the GPU (different streams) race - serialise
+ * them.  The first call on a device resolves the array's address (cudaGetSymbolAddress); make it outside graph capture. */
+int64_t esb_gemm_skinny_static_scratch_bytes(void);
+int esb_gemm_skinny_static_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
+                                const void* residual, int64_t ldr, int force_splits, int w_tiled, void* stream);
 int64_t esb_retiled_weight_elems(int N, int K);
 int esb_retile_weight_bf16(const void* W, int64_t ldw, int N, int K, void* out, void* stream);
 /* The decode step with LlamaRMSNorm (HF modeling_llama.py LlamaRMSNorm, called at the three norm sites of
