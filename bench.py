@@ -295,6 +295,56 @@ def run_b200(args):
     timer.flops = timer.flops / gsteps * args.steps
     timer.n = timer.n // gsteps * args.steps
     clocks = sampler.stop()
+    # N > 1: the same step WITHOUT any gradient exchange, timed on every rank by itself - separates a slow GPU of the box
+    # (all ranks wait for it in every collective) from exchange time that the overlap does not hide
+    dp_timeline = None
+    spans = None
+    if world > 1:
+        tr.trace_spans = {}
+        sync_all()
+        for i in range(4):
+            step_resident(i)
+        sync_all()
+        spans = {k: round(sum(a.elapsed_time(b) for a, b in v) / 4, 3) for k, v in tr.trace_spans.items()}
+        tr.trace_spans = None
+    if world > 1 and args.recipe != "unfreeze_lm":
+        def step_local(i):
+            b = dbatches[i % nb]
+            ev = tr._mark("zero_grad")
+            tr.zero_grad()
+            tr._mark_end(ev)
+            ev = tr._mark("forward_backward")
+            loss = tr.forward_backward(b["tokens"], b["attention_masks"], b["pcrgbs"], b["prompts"].shape[1], dstarts[i % nb], None,
+                                       sync=False)
+            tr._mark_end(ev)
+            tr._embed_pending = []
+            ev = tr._mark("optimizer_step")
+            tr.optimizer_step()
+            tr._mark_end(ev)
+            return loss
+        step_local(0)
+        tr.trace_spans = {}
+        sync_all()
+        for i in range(4):
+            step_local(i)
+        sync_all()
+        spans_local = {k: round(sum(a.elapsed_time(b) for a, b in v) / 4, 3) for k, v in tr.trace_spans.items()}
+        tr.trace_spans = None
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(4):
+            step_local(i)
+        e1.record()
+        torch.cuda.synchronize()
+        mine = torch.tensor([e0.elapsed_time(e1) / 4], device=dev)
+        allms = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allms, mine)
+        per_rank = [round(float(t), 2) for t in allms]
+        dp_timeline = {"local_step_ms_per_rank_no_exchange": per_rank, "slowest_rank_ms": max(per_rank), "fastest_rank_ms": min(per_rank),
+                       "step_ms_with_exchange": round(ms_res / args.steps, 2),
+                       "exchange_not_hidden_ms": round(ms_res / args.steps - max(per_rank), 2),
+                       "rank0_ms_per_step_inside": spans, "rank0_ms_per_step_inside_no_exchange": spans_local}
 
     peaks = {}
     try:
@@ -329,6 +379,8 @@ def run_b200(args):
     }
     if dpc is not None:
         line["dp_check"] = dpc
+    if dp_timeline is not None:
+        line["dp_timeline"] = dp_timeline
     tr = None                                                          # frees optimizer state + gradient buffers
     torch.cuda.empty_cache()
     if not args.no_decode:

@@ -77,6 +77,7 @@ int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int6
     return gemm_t_bf16(A, lda, trans_a, B, ldb, trans_b, C, ldc, M, N, Kc, out_fp32, accumulate, alpha, ST(stream));
 }
 int esb_set_gemm_2cta(int on) { return set_gemm_2cta(on); }
+int esb_set_gemm_sm_reserve(int k) { return set_gemm_sm_reserve(k); }
 int64_t esb_gemm_skinny_workspace_bytes(int M, int N, int K) { return gemm_skinny_workspace_bytes(M, N, K); }
 int esb_gemm_skinny_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, int K,
                          const void* residual, int64_t ldr, void* workspace, int64_t workspace_bytes, int force_splits,

@@ -51,6 +51,10 @@ int esb_embed_scatter_rows(const int64_t* ids, const void* rows, float* dembed, 
                            void* stream) {
     return embed_scatter_rows(CLLP(ids), rows, dembed, pad_id, vocab_size, R, d, ST(stream));
 }
+int esb_embed_scatter_sorted(const int64_t* sorted_ids, const int64_t* order, const void* rows, float* dembed, int64_t pad_id,
+                             int64_t vocab_size, int R, int d, void* stream) {
+    return embed_scatter_sorted(CLLP(sorted_ids), CLLP(order), rows, dembed, pad_id, vocab_size, R, d, ST(stream));
+}
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream) {
     return copy_rows(src, src_bstride_bytes, src_ld_bytes, dst, dst_bstride_bytes, dst_ld_bytes, batches, rows, row_bytes, ST(stream));

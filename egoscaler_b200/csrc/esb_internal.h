@@ -64,6 +64,7 @@ int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, v
 int gemm_t_bf16(const void* A, long long lda, int trans_a, const void* B, long long ldb, int trans_b, void* C, long long ldc, int M,
                 int N, int Kc, int out_fp32, int accumulate, float alpha, cudaStream_t stream);
 int set_gemm_2cta(int on);
+int set_gemm_sm_reserve(int k);
 long long gemm_skinny_workspace_bytes(int M, int N, int K);
 int gemm_skinny_bf16(const void* X, long long ldx, const void* W, long long ldw, void* C, long long ldc, int M, int N, int K,
                      const void* residual, long long ldr, void* workspace, long long workspace_bytes, int force_splits,

@@ -59,6 +59,8 @@ int embed_splice_bwd(const long long* ids, const void* dx, const int* splice_pos
 int embed_rows_pack(const long long* ids, const void* dx, const int* splice_pos, int n_point, int rmax, void* rows_out,
                     long long* ids_out, long long pad, int B, int L, int d, cudaStream_t s);
 int embed_scatter_rows(const long long* ids, const void* rows, float* dembed, long long pad, long long vocab, int R, int d, cudaStream_t s);
+int embed_scatter_sorted(const long long* sorted_ids, const long long* order, const void* rows, float* dembed, long long pad,
+                         long long vocab, int R, int d, cudaStream_t s);
 int copy_rows(const void* src, long long src_bstride_bytes, long long src_ld_bytes, void* dst, long long dst_bstride_bytes,
               long long dst_ld_bytes, int batches, int rows, int row_bytes, cudaStream_t s);
 int transpose_bf16(const void* in, long long ld_in, void* out, long long ld_out, int R, int C, cudaStream_t s);

@@ -891,6 +891,19 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams 
 // CTA-pair variant (gemm2_bf16_tcgen05_kernel): ON by default since it measured 1450-1520 TF/s against 1385-1430 for the
 // single-CTA kernel on the four trunk shapes and 143.2-143.8 ms against 147.7-148.8 ms per training step on the same box
 // (profiles/r02_v6_*); esb_set_gemm_2cta(0) / ESB_GEMM_2CTA=0 switch back
+// SMs left out of the persistent grids (esb_set_gemm_sm_reserve): while a gradient all-reduce is in flight NCCL's CTAs need SMs of
+// their own - next to a 1-CTA-per-SM kernel with ~200 KB of shared memory they only get scheduled in the gaps between launches and
+// the collective is still running when the backward ends (bench.py dp_timeline: 3.2 ms of exchange not hidden at N=2).
+static int g_gemm_sm_reserve = 0;
+int set_gemm_sm_reserve(int k) {
+    const int old = g_gemm_sm_reserve;
+    g_gemm_sm_reserve = k < 0 ? 0 : (k > 64 ? 64 : k);
+    return old;
+}
+static int gemm_sm_count() {
+    const int n = device_sm_count() - g_gemm_sm_reserve;
+    return n < 2 ? 2 : n;
+}
 static int g_gemm_2cta = [] { const char* e = getenv("ESB_GEMM_2CTA"); return e ? atoi(e) : 1; }();
 int set_gemm_2cta(int on) { const int old = g_gemm_2cta; g_gemm_2cta = on ? 1 : 0; return old; }
 static bool use_2cta(int M, int N, int K) { return g_gemm_2cta && M >= 1024 && N >= 512 && K >= 256; }
@@ -933,7 +946,7 @@ int gemm_bf16(const void* A, long long lda, const void* B, long long ldb, void* 
         set_last_error("gemm_bf16: accumulate requires fp32 output");
         return ESB_ERR_INVALID_ARG;
     }
-    const int sms = device_sm_count();
+    const int sms = gemm_sm_count();
     int bn = force_bn;
     if (bn == 0) {
         if (N <= 64) bn = 64;
@@ -1001,8 +1014,8 @@ int gemm_swiglu_bf16(const void* A, long long lda, const void* Wgu, long long ld
     rc = make_tma_2d_bf16(&tb, Wgu, 2LL * f, K, ldw, 128);
     if (rc) return rc;
     p.C = act; p.ldc = ld_act; p.C2 = gu; p.ldc2 = ld_gu; p.f = f;
-    if (use_2cta(M, f, K)) return launch_gemm2<EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());      // same 128-row boxes
-    return launch_gemm<256, EPI_SWIGLU>(ta, tb, p, stream, device_sm_count());
+    if (use_2cta(M, f, K)) return launch_gemm2<EPI_SWIGLU>(ta, tb, p, stream, gemm_sm_count());      // same 128-row boxes
+    return launch_gemm<256, EPI_SWIGLU>(ta, tb, p, stream, gemm_sm_count());
 }
 
 // dgu [M, 2f] = dSwiGLU(gu, dOut . Wdown) with the weight given either as WdownT [f, K=d] (contraction-major copy, trans_b = 0)
@@ -1021,7 +1034,7 @@ int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long 
     rc = trans_b ? make_tma_2d_bf16(&tb, WdownT, K, f, ldb, 64) : make_tma_2d_bf16(&tb, WdownT, f, K, ldb, pair ? 128 : 256);
     if (rc) return rc;
     p.aux = static_cast<const __nv_bfloat16*>(gu); p.ld_aux = ld_gu; p.C2 = dgu; p.ldc2 = ld_dgu; p.f = f;
-    if (pair) return launch_gemm2<EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count());
+    if (pair) return launch_gemm2<EPI_DSWIGLU>(ta, tb, p, stream, gemm_sm_count());
     if ((ld_gu & 7) || (reinterpret_cast<uintptr_t>(gu) & 15)) {
         set_last_error("gemm_dswiglu_bf16: gu must be 16-byte aligned with a leading dimension that is a multiple of 8");
         return ESB_ERR_INVALID_ARG;
@@ -1029,8 +1042,8 @@ int gemm_dswiglu_bf16(const void* dOut, long long lda, const void* WdownT, long 
     CUtensorMap tc;                                            // saved gate|up [M, 2f]: box = 64 columns x 128 rows for the staged epilogue
     rc = make_tma_2d_bf16(&tc, gu, M, 2LL * f, ld_gu, BM);
     if (rc) return rc;
-    if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, device_sm_count(), &tc);
-    return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, device_sm_count(), &tc);
+    if (trans_b) return launch_gemm<256, EPI_DSWIGLU, false, true>(ta, tb, p, stream, gemm_sm_count(), &tc);
+    return launch_gemm<256, EPI_DSWIGLU>(ta, tb, p, stream, gemm_sm_count(), &tc);
 }
 
 // C [M, N] = rope(A . W^T): heads of 128 columns starting below rope_cols are rotated at position pos0 + (row % L)
@@ -1052,15 +1065,15 @@ int gemm_rope_bf16(const void* A, long long lda, const void* W, long long ldw, v
     if (rc) return rc;
     p.C = C; p.ldc = ldc; p.cos_tab = static_cast<const __nv_bfloat16*>(cos_tab); p.sin_tab = static_cast<const __nv_bfloat16*>(sin_tab);
     p.rope_L = L; p.rope_pos0 = pos0; p.rope_cols = rope_cols;
-    if (pair) return launch_gemm2<EPI_ROPE>(ta, tb, p, stream, device_sm_count());
-    return launch_gemm<256, EPI_ROPE>(ta, tb, p, stream, device_sm_count());
+    if (pair) return launch_gemm2<EPI_ROPE>(ta, tb, p, stream, gemm_sm_count());
+    return launch_gemm<256, EPI_ROPE>(ta, tb, p, stream, gemm_sm_count());
 }
 
 // C[M,N] (+)= alpha * op(A) . op(B): trans_a = 1: A is [Kc, M] row-major (else [M, Kc]); trans_b = 1: B is [Kc, N] row-major
 // (else [N, Kc], the state_dict layout the plain entry point takes).  trans_a = trans_b = 0 is gemm_bf16 itself.
 template <bool TA, bool TB>
 static int launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int M, int N, cudaStream_t stream) {
-    const int sms = device_sm_count();
+    const int sms = gemm_sm_count();
     if (use_2cta(M, N, p.K)) return launch_gemm2<EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);   // same 64 x 64 boxes / 128-row A box
     const long long t256 = static_cast<long long>((M + BM - 1) / BM) * ((N + 255) / 256);
     if (N > 128 && t256 >= sms / 2) return launch_gemm<256, EPI_PLAIN, TA, TB>(ta, tb, p, stream, sms);

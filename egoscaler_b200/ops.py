@@ -271,6 +271,11 @@ def set_gemm_2cta(on: bool) -> bool:
     return bool(_l.lib().raw("esb_set_gemm_2cta")(1 if on else 0))
 
 
+def set_gemm_sm_reserve(k: int) -> int:
+    """Leave ``k`` SMs out of the persistent GEMM grids (for NCCL while a gradient all-reduce is in flight); returns the previous k."""
+    return int(_l.lib().raw("esb_set_gemm_sm_reserve")(int(k)))
+
+
 def gemm_swiglu(a: torch.Tensor, wgu: torch.Tensor, want_gu: bool = True):
     """a [M,K], wgu [2f,K] = [gate ; up] -> (act [M,f], gu [M,2f] or None)."""
     _chk(a, torch.bfloat16, "gemm_swiglu.a"); _chk(wgu, torch.bfloat16, "gemm_swiglu.wgu")
@@ -534,6 +539,15 @@ def embed_scatter_rows(ids: torch.Tensor, rows: torch.Tensor, dembed: torch.Tens
     assert ids.is_contiguous() and rows.is_contiguous() and dembed.is_contiguous() and rows.shape[0] == ids.numel()
     _l.call("esb_embed_scatter_rows", ids.data_ptr(), rows.data_ptr(), dembed.data_ptr(), pad_id, dembed.shape[0], ids.numel(),
             rows.shape[1], _stream())
+
+
+def embed_scatter_sorted(ids: torch.Tensor, rows: torch.Tensor, dembed: torch.Tensor, pad_id: int):
+    """``embed_scatter_rows`` (same sums, same order) through a stable sort of the ids instead of the O(R^2) scan; any R."""
+    _chk(ids, torch.int64, "embed_scatter_sorted.ids"); _chk(rows, torch.bfloat16, "embed_scatter_sorted.rows"); _chk(dembed, torch.float32, "embed_scatter_sorted.dembed")
+    assert ids.is_contiguous() and rows.is_contiguous() and dembed.is_contiguous() and rows.shape[0] == ids.numel()
+    sorted_ids, order = torch.sort(ids, stable=True)             # index bookkeeping only; the sums run in esb_embed_scatter_sorted
+    _l.call("esb_embed_scatter_sorted", sorted_ids.data_ptr(), order.data_ptr(), rows.data_ptr(), dembed.data_ptr(), pad_id,
+            dembed.shape[0], ids.numel(), rows.shape[1], _stream())
 
 
 def copy_rows(src: torch.Tensor, dst: torch.Tensor):

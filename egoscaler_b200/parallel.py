@@ -37,6 +37,7 @@ class GradExchange:
         self.pg = process_group
         self.rank = 0
         self._pending: List = []
+        self._named: dict = {}                   # name -> pending work (allreduce_async_named / wait_named)
         self._reduce_is_allreduce = False
         if self.world > 1:
             import torch.distributed as dist
@@ -62,6 +63,25 @@ class GradExchange:
             return
         for t in tensors:
             self._pending.append(self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
+    def allreduce_async_named(self, named) -> None:
+        """Like ``allreduce_async`` for (name, tensor) pairs; ``wait_named(name)`` joins one of them, so the optimizer can start on
+        the tensors whose exchange has finished while later ones are still in flight."""
+        if self.world == 1:
+            return
+        for name, t in named:
+            self._named.setdefault(name, []).append(self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
+    def wait_named(self, name: str) -> None:
+        for w in self._named.pop(name, []):
+            w.wait()
+
+    def all_gather_async(self, t: torch.Tensor):
+        """(out [world, *t.shape], work or None): ``all_gather`` without the wait (``work.wait()`` before ``out`` is read)."""
+        if self.world == 1 or (self._reduce_is_allreduce and t.is_cuda):
+            return self.all_gather(t), None
+        out = torch.empty((self.world,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+        return out, self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.pg, async_op=True)
 
     def reduce_to_owner_async(self, unit: int, tensor: torch.Tensor) -> None:
         if self.world == 1:
@@ -96,6 +116,8 @@ class GradExchange:
         for w in self._pending:
             w.wait()
         self._pending = []
+        for name in list(self._named):
+            self.wait_named(name)
 
     @property
     def grad_scale(self) -> float:

@@ -12,6 +12,8 @@ NVLink); the lm_head/norm gradients -- half of the bytes -- are reduced while th
 """
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional
 
 import torch
@@ -151,6 +153,20 @@ class Trainer:
         dhn = ops.gemm_nn(logits, m.lm_head.weight.detach()) if ops.gemm_nn_enabled else ops.gemm(logits, m.lm_head_T())
         dhs = ops.rmsnorm_bwd(dhn, hs2, norm_w, rstd, dw=self.grad["model.norm.weight"])
         self._reduce_async(["lm_head.weight", "model.norm.weight"])       # overlaps with the trunk backward below
+        # NCCL's CTAs need SMs of their own to make progress next to the persistent 1-CTA-per-SM GEMMs: keep a few SMs out of the
+        # GEMM grids while the head gradients (528 MB at full size) are in flight - the first layers of the trunk backward for the
+        # default recipe, the whole backward when every layer's gradients are exchanged (--unfreeze_language_model)
+        reserve = self.nccl_sm_reserve if self._sync else 0
+        if reserve > 0:
+            ops.set_gemm_sm_reserve(reserve)
+        n_layers = cfg.num_hidden_layers
+        release_at = -1 if self.wgrad is not None else n_layers - self.nccl_reserve_layers      # layers run top (n-1) to bottom (0)
+
+        def layer_done(li):
+            if self.wgrad is not None and self._sync:
+                self._reduce_layer_async(li)
+            if reserve > 0 and li == release_at:
+                ops.set_gemm_sm_reserve(0)
         if rows_only:
             dh = dhs
         else:
@@ -159,9 +175,11 @@ class Trainer:
             dh = dh.view(B * L, d)
         # ---- trunk backward (data gradients through the frozen layers), embedding scatter, projector, encoder
         backward_from_hidden(m, ctx, dh, self.grad, self.wgrad,
-                             on_layer_done=self._reduce_layer_async if (self.wgrad is not None and self._sync) else None,
+                             on_layer_done=layer_done if (reserve > 0 or (self.wgrad is not None and self._sync)) else None,
                              on_ready=self._reduce_async, wgrad_accumulate=not self._wgrad_fresh,
                              embed_exchange=self._embed_exchange if (self.world > 1 and self.sparse_embed_exchange) else None)
+        if reserve > 0:
+            ops.set_gemm_sm_reserve(0)
         self._wgrad_fresh = False
         self.last_loss = loss
         return loss
@@ -169,7 +187,7 @@ class Trainer:
     # ------------------------------------------------------------------ data parallel (parallel.GradExchange)
     def _reduce_async(self, names: List[str]):
         if self._sync:
-            self.dp.allreduce_async(self.grad[n] for n in names)
+            self.dp.allreduce_async_named((n, self.grad[n]) for n in names)
 
     def _embed_exchange(self, tokens: torch.Tensor, dx: torch.Tensor, splice_pos, n_point: int):
         """embed_tokens gradient of a data-parallel step WITHOUT the dense [V, d] fp32 all-reduce (528 MB at full size, issued
@@ -196,11 +214,22 @@ class Trainer:
                 raise RuntimeError("sparse embedding-gradient exchange needs equal batch shapes and micro-batch counts on all "
                                    f"ranks, got row counts {alln.flatten().tolist()} (set Trainer.sparse_embed_exchange = False)")
             self._exchange_rows = rows.shape[0]
-        all_rows = self.dp.all_gather(rows).view(-1, rows.shape[1])
-        all_ids = self.dp.all_gather(ids).view(-1)
-        step = 1 << 16                                              # rows per deterministic scatter launch
-        for lo in range(0, all_ids.numel(), step):
-            ops.embed_scatter_rows(all_ids[lo:lo + step], all_rows[lo:lo + step], self.grad["model.embed_tokens.weight"], cfg.pad_token_id)
+        # the gathers run behind the projector / encoder backward and the AdamW of the other tensors; the scatter waits for them
+        # right before the embedding's own optimizer step (_finish_embed_exchange)
+        self._embed_inflight = (self.dp.all_gather_async(rows), self.dp.all_gather_async(ids), rows.shape[1])
+
+    def _finish_embed_exchange(self):
+        if self._embed_inflight is None:
+            return
+        (all_rows, w_rows), (all_ids, w_ids), d = self._embed_inflight
+        self._embed_inflight = None
+        ev = self._mark("embed_exchange")
+        for w in (w_rows, w_ids):
+            if w is not None:
+                w.wait()
+        all_rows, all_ids = all_rows.view(-1, d), all_ids.view(-1)
+        ops.embed_scatter_sorted(all_ids, all_rows, self.grad["model.embed_tokens.weight"], self.model.cfg.pad_token_id)
+        self._mark_end(ev)
 
     def _reduce_layer_async(self, li: int):
         """ZeRO-1 gradient exchange of one LLM layer, started as soon as its backward has been queued: every unit is
@@ -210,20 +239,56 @@ class Trainer:
                 self.dp.reduce_to_owner_async(u, self.wgrad[k][li])
 
     def _wait_reduce(self):
+        """All gradients of this step are final in ``self.grad`` / ``self.wgrad`` once the current stream reaches this point."""
+        ev = self._mark("wait_reduce")
         self.dp.wait()
+        self._finish_embed_exchange()
+        self._mark_end(ev)
+
+    _embed_inflight = None
+
+    # optional CUDA-event spans around the exposed parts of the exchange (bench.py --gpus N: dp_timeline)
+    trace_spans = None          # None: off; dict name -> list of (start event, end event)
+    # SMs kept out of the persistent GEMM grids while gradients are being exchanged, and for how many layers of the trunk
+    # backward after the head gradients were handed to NCCL (default recipe)
+    nccl_sm_reserve = int(os.environ.get("ESB_NCCL_SM_RESERVE", "8"))
+    nccl_reserve_layers = int(os.environ.get("ESB_NCCL_RESERVE_LAYERS", "4"))
+
+    def _mark(self, name):
+        if self.trace_spans is None or self.world == 1:
+            return None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        self.trace_spans.setdefault(name, []).append((e0, e1))
+        return e1
+
+    @staticmethod
+    def _mark_end(ev):
+        if ev is not None:
+            ev.record()
 
     # ------------------------------------------------------------------ optimizer
     def optimizer_step(self):
-        self._wait_reduce()
         lr = linear_warmup_lr(self.lr, self.step_count, self.warmup, self.total) if self.total > 0 else self.lr
         self.step_count += 1
         scale = 1.0 / self.world                                   # mean over ranks (DDP semantics)
-        for n in self.names:
+        # tensors in the order their exchange was started (head first, embedding last): each AdamW launch waits only for its own
+        # collective, so the tail of the exchange (projector all-reduce, embedding-row gathers) hides behind the earlier updates
+        emb = "model.embed_tokens.weight"
+        order = [n for n in self.names if n.startswith("lm_head.") or n == "model.norm.weight"]
+        order += [n for n in self.names if n not in order and n != emb] + [n for n in self.names if n == emb]
+        for n in order:
             p = self.param[n]
+            ev = self._mark("wait:" + ("point_backbone" if n.startswith("model.point_backbone.") else n)) if n in self.dp._named else None
+            self.dp.wait_named(n)
+            self._mark_end(ev)
+            if n == emb:
+                self._finish_embed_exchange()
             ops.adamw_(self.master[n], self.grad[n], self.m[n], self.v[n], p.detach() if p.dtype == torch.bfloat16 else None,
                        lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_count, scale)
             if p.dtype != torch.bfloat16:
                 p.detach().copy_(self.master[n])
+        self._wait_reduce()                                         # LLM-layer units (ZeRO-1 reductions), anything left
         if self.trunk_units:
             self._trunk_step(lr, scale)
         # refresh derived operands of the trainable tensors (the fused AdamW kernel writes the parameters through raw
@@ -251,8 +316,14 @@ class Trainer:
 
     def train_step(self, batch: dict, fps_start: Optional[torch.Tensor] = None, drop_u: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration of train.py:157-184 on a collate_fn-shaped batch (dataset.py:184-194)."""
+        ev = self._mark("zero_grad")
         self.zero_grad()
+        self._mark_end(ev)
+        ev = self._mark("forward_backward")
         loss = self.forward_backward(batch["tokens"], batch["attention_masks"], batch["pcrgbs"], batch["prompts"].shape[1],
                                      fps_start, drop_u)
+        self._mark_end(ev)
+        ev = self._mark("optimizer_step")
         self.optimizer_step()
+        self._mark_end(ev)
         return loss

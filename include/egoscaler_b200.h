@@ -90,6 +90,9 @@ int esb_gemm_t_bf16(const void* A, int64_t lda, int trans_a, const void* B, int6
  * tcgen05.mma.cta_group::2 on 256 x 256 tiles, each SM stages half of the weight tile.  Returns the previous setting.  Default:
  * on (environment variable ESB_GEMM_2CTA=0 turns it off). */
 int esb_set_gemm_2cta(int on);
+/* Data-parallel training (train.py:92-125, DeepSpeed's gradient all-reduce overlapped with the backward): leave k SMs out of the
+ * persistent GEMM grids while a collective is in flight so that NCCL's CTAs get SMs of their own; returns the previous k. */
+int esb_set_gemm_sm_reserve(int k);
 
 /* Weight-streaming variant for the cached single-token decode step (M = sequences per GPU <= 64):
  * C[M,N] = X[M,K] . W[N,K]^T + residual[M,N], bf16 in/out, fp32 accumulation, split-K over the SMs with a
@@ -243,6 +246,10 @@ int esb_embed_rows_pack(const int64_t* ids, const void* dx, const int32_t* splic
                         int64_t* ids_out, int64_t pad_id, int B, int L, int d, void* stream);
 int esb_embed_scatter_rows(const int64_t* ids, const void* rows, float* dembed, int64_t pad_id, int64_t vocab_size, int R, int d,
                            void* stream);
+/* esb_embed_scatter_rows for ids the caller has sorted (stable, ascending): order[p] = index into rows of the p-th sorted id.  Same
+ * sums in the same order (rows of one id in increasing original index), no limit on R, no O(R^2) scan. */
+int esb_embed_scatter_sorted(const int64_t* sorted_ids, const int64_t* order, const void* rows, float* dembed, int64_t pad_id,
+                             int64_t vocab_size, int R, int d, void* stream);
 /* Batched strided row copy (logits slice train.py:174-175, hidden-row gathers); all byte strides multiples of 16. */
 int esb_copy_rows(const void* src, int64_t src_bstride_bytes, int64_t src_ld_bytes, void* dst, int64_t dst_bstride_bytes,
                   int64_t dst_ld_bytes, int batches, int rows, int row_bytes, void* stream);

@@ -423,6 +423,22 @@ def test_embed_rows_pack_and_deterministic_scatter():
     okb = ridb > 0
     expb.index_add_(0, ridb[okb], rowsb[okb].double())
     torch.testing.assert_close(acc.double(), expb, atol=2e-3, rtol=1e-5)
+    # the sorted variant (what the trainer calls): same sums in the same order -> same bits, also beyond 65536 rows
+    acc2 = torch.ones(V, d, device="cuda")
+    ops.embed_scatter_sorted(ridb, rowsb, acc2, 0)
+    assert torch.equal(acc2, acc)
+    out3 = torch.zeros(V, d, device="cuda")
+    ops.embed_scatter_sorted(rid, rows, out3, 0)
+    assert torch.equal(out3, out1)
+    R2 = 70000
+    ridc = torch.randint(0, V + 20, (R2,), device="cuda", generator=g)
+    rowsc = rnd(R2, d, seed=8)
+    big = torch.zeros(V, d, device="cuda")
+    ops.embed_scatter_sorted(ridc, rowsc, big, 0)
+    expc = torch.zeros(V, d, device="cuda", dtype=torch.float64)
+    okc = (ridc > 0) & (ridc < V)
+    expc.index_add_(0, ridc[okc], rowsc[okc].double())
+    torch.testing.assert_close(big.double(), expc, atol=5e-3, rtol=1e-5)
 
 
 def test_attention_bwd_on_a_query_row_range():
