@@ -457,6 +457,7 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
         ref_scale = float(world)                                          # global mean * world == sum of equal-count shard means
     tr.sparse_embed_exchange = sparse
     worst, worst_name, n_cmp = 0.0, "", 0
+    rels = []
     # conv biases directly in front of a train-mode BatchNorm have a structurally zero gradient (the batch mean removes them):
     # both sides hold round-off only, so a relative comparison is meaningless (tests/test_variants_gpu.py bounds their size)
     skipped = [n for n in got if tr.enc_train is not None and n.endswith(("encoder.first_conv.0.bias", "encoder.second_conv.0.bias"))]
@@ -479,6 +480,7 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
             continue
         rel = float((g.double() - ref).norm()) / den
         n_cmp += 1
+        rels.append((round(rel, 6), name))
         if rel > worst:
             worst, worst_name = rel, name
     del got
@@ -502,6 +504,8 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
     dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
     wsum = w.clone()
     dist.all_reduce(wsum, op=dist.ReduceOp.SUM)
+    shard_losses = [None] * world
+    dist.all_gather_object(shard_losses, round(float(loss_shard), 5))
     names = [None] * world
     dist.all_gather_object(names, (worst, worst_name))
     worst_all = max(names, key=lambda t: t[0])
@@ -509,6 +513,9 @@ def dp_check(torch, dist, tr, cfg, args, dev, world, rank):
             "max_rel_l2": round(float(wmax[0]), 6), "worst_tensor": worst_all[1], "tensors_compared_rank0": n_cmp,
             "tolerance": 2e-2, "ok": bool(float(wmax[0]) <= 2e-2 and identical),
             "loss_mean_over_ranks": round(float(wsum[1]) / world, 5), "loss_single_gpu_global_batch": round(loss_ref, 5),
+            "loss_per_rank": shard_losses,
+            "loss_recomputed_per_shard_rank0": [round(float(x), 5) for x in losses] if tr.enc_train is not None else None,
+            "worst5_rank0": sorted(rels, reverse=True)[:5],
             "equal_token_counts": equal_counts, "weights_bit_identical_after_step": identical, "skipped_structurally_zero": skipped,
             "reference": ("per-shard recomputation on one GPU (per-rank BatchNorm statistics, no SyncBN)" if tr.enc_train is not None
                           else "one GPU on the concatenated global batch")}

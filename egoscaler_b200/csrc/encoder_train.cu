@@ -87,11 +87,20 @@ __global__ void __launch_bounds__(128) layernorm_bwd_kernel(const __nv_bfloat16*
     }
 }
 
-// Column reductions over a row-major bf16 matrix: CTA = 32 columns x 8 row lanes, grid.y slices the rows; fp32 atomics.
+// Column reductions over a row-major bf16 matrix: CTA = 32 columns x 8 row lanes, grid.y slices the rows.  DETERMINISTIC: the
+// slices leave their partial sums in a device scratch and the last slice of a column block to arrive adds them up in slice order
+// (an fp32 atomicAdd per slice made the train-mode BatchNorm statistics - and through bf16 roundings the whole forward of a
+// --unfreeze_pc_encoder step - differ in the last bits from run to run: bench.py dp_check, 3 % on the embedding gradient).
+// The scratch is shared by all launches of a GPU: launches on different streams must not overlap (the trainer uses one stream).
+constexpr int CS2_MAX_SLICES = 512, CS2_MAX_COLS = 4096;
+__device__ float g_cs2_part[2][CS2_MAX_SLICES][CS2_MAX_COLS];       // 16 MiB
+__device__ unsigned int g_cs2_count[CS2_MAX_COLS / 32];
+
 __global__ void __launch_bounds__(256) colsum2_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                                                       long long lda, long long ldb, long long M, int N, float* __restrict__ out0,
                                                       float* __restrict__ out1) {
     __shared__ float s0[8][33], s1[8][33];
+    __shared__ bool s_last;
     const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + cx;
     float t0 = 0.0f, t1 = 0.0f;
@@ -108,8 +117,40 @@ __global__ void __launch_bounds__(256) colsum2_kernel(const __nv_bfloat16* __res
     if (ry == 0 && col < N) {
 #pragma unroll
         for (int j = 1; j < 8; ++j) { t0 += s0[j][cx]; t1 += s1[j][cx]; }
-        atomicAdd(out0 + col, t0);
-        if (out1) atomicAdd(out1 + col, t1);
+        if (gridDim.y == 1) {
+            out0[col] += t0;
+            if (out1) out1[col] += t1;
+        } else {
+            g_cs2_part[0][blockIdx.y][col] = t0;
+            g_cs2_part[1][blockIdx.y][col] = t1;
+        }
+    }
+    if (gridDim.y == 1) return;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(&g_cs2_count[blockIdx.x], 1u);
+        s_last = prev == gridDim.y - 1;
+        if (s_last) g_cs2_count[blockIdx.x] = 0;                    // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // 8 row lanes take the slices round-robin, then a fixed-order sum over the lanes
+    float u0 = 0.0f, u1 = 0.0f;
+    if (col < N)
+        for (int y = ry; y < static_cast<int>(gridDim.y); y += 8) {
+            u0 += __ldcg(&g_cs2_part[0][y][col]);
+            u1 += __ldcg(&g_cs2_part[1][y][col]);
+        }
+    s0[ry][cx] = u0;
+    s1[ry][cx] = u1;
+    __syncthreads();
+    if (ry == 0 && col < N) {
+#pragma unroll
+        for (int j = 1; j < 8; ++j) { u0 += s0[j][cx]; u1 += s1[j][cx]; }
+        out0[col] += u0;
+        if (out1) out1[col] += u1;
     }
 }
 
@@ -259,6 +300,7 @@ int colsum2_bf16(const void* a, long long lda, const void* b, long long ldb, lon
                  cudaStream_t s) {
     if (M <= 0 || N <= 0) return ESB_OK;
     if (!a || !out0) { set_last_error("colsum2_bf16: null argument"); return ESB_ERR_INVALID_ARG; }
+    if (N > CS2_MAX_COLS) { set_last_error("colsum2_bf16: N=%d columns, at most %d", N, CS2_MAX_COLS); return ESB_ERR_UNSUPPORTED; }
     long long slices = (M + 8 * 64 - 1) / (8 * 64);
     if (slices > 512) slices = 512;
     if (slices < 1) slices = 1;

@@ -345,7 +345,9 @@ int esb_knn_group(const float* pts, const float* centers, int B, int N, int C, i
  * dgamma/dbeta fp32 [d] are ACCUMULATED (or NULL). */
 int esb_layernorm_bwd(const void* dy, const void* x, const float* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
                       int64_t rows, int d, float eps, void* stream);
-/* out0[c] += sum_r a[r,c]; out1[c] += sum_r a[r,c]*b[r,c] (b NULL: a*a).  BatchNorm1d batch statistics, dvae.py:196,202. */
+/* out0[c] += sum_r a[r,c]; out1[c] += sum_r a[r,c]*b[r,c] (b NULL: a*a).  BatchNorm1d batch statistics, dvae.py:196,202.
+ * Deterministic (fixed summation order): the row slices meet in a 16 MiB scratch array of the library, shared by all calls on a
+ * GPU - calls on different streams must not overlap.  N <= 4096. */
 int esb_colsum2_bf16(const void* a, int64_t lda, const void* b, int64_t ldb, int64_t M, int N, float* out0, float* out1, void* stream);
 /* Per-channel BatchNorm coefficients from those sums.  mode 0 (forward): y = A*z + C, saves mean/rstd, updates the running
  * statistics (momentum, unbiased variance).  mode 1 (backward): dz = A*dy + B*z + C, dgamma/dbeta accumulated. */

@@ -322,6 +322,21 @@ def test_layernorm_bwd():
     close(db, bf.grad, 5e-3)
 
 
+def test_colsum2_is_deterministic_and_exact():
+    """Batch statistics of the train-mode BatchNorm: same bits on every call (fixed summation order over the row slices), equal
+    to an fp64 sum within fp32 round-off; accumulates onto the outputs."""
+    for R, C in ((131072, 384), (16384, 128), (300, 70), (7, 40)):
+        z, w = rnd(R, C, seed=R % 97), rnd(R, C, seed=R % 89)
+        outs = []
+        for _ in range(3):
+            s0, s1 = torch.ones(C, device="cuda"), torch.full((C,), 2.0, device="cuda")
+            ops.colsum2(z, w, s0, s1)
+            outs.append((s0, s1))
+        assert all(torch.equal(outs[0][0], o[0]) and torch.equal(outs[0][1], o[1]) for o in outs[1:])
+        torch.testing.assert_close(outs[0][0].double(), 1 + z.double().sum(0), rtol=1e-5, atol=1e-3)
+        torch.testing.assert_close(outs[0][1].double(), 2 + (z.double() * w.double()).sum(0), rtol=1e-5, atol=1e-3)
+
+
 def test_batchnorm_train_forward_backward():
     """colsum2 + bn_coeffs + affine_cols + relu_mask == nn.BatchNorm1d(train) + ReLU and their autograd."""
     R, C = 4096, 128
