@@ -120,13 +120,22 @@ __global__ void __launch_bounds__(128) attn_bwd_stats_kernel(const __nv_bfloat16
 
 // Write 32 consecutive bf16 (16 packed words) of row r, columns [32*half, 32*half+32), into a [128 x 64] K-major
 // SW128 operand tile (row pitch 128 B, 16-byte unit u stored at unit u ^ (r & 7)).
+// Explicit st.shared / ld.shared: through a generic pointer these compiled to ST.E / LD.E plus a MEMBAR.ALL.CTA in front of the proxy
+// fence (7 % of the dK/dV kernel's stall samples, ncu source view).
 ESB_DEVICE void store_operand_half_row(uint8_t* tile, int r, int half, const uint32_t* w) {
-    uint8_t* row = tile + r * 128;
+    const uint32_t row = smem_u32(tile) + static_cast<uint32_t>(r * 128);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int u = half * 4 + i;
-        *reinterpret_cast<uint4*>(row + ((u ^ (r & 7)) << 4)) = make_uint4(w[i * 4 + 0], w[i * 4 + 1], w[i * 4 + 2], w[i * 4 + 3]);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + static_cast<uint32_t>((u ^ (r & 7)) << 4)), "r"(w[i * 4 + 0]),
+                     "r"(w[i * 4 + 1]), "r"(w[i * 4 + 2]), "r"(w[i * 4 + 3])
+                     : "memory");
     }
+}
+ESB_DEVICE float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
 }
 
 // ================================================================================================ dQ
@@ -271,14 +280,16 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
         const float2 stt = p.stats[(static_cast<long long>(b) * p.H + h) * p.Lqp + min(qrow, p.Lqp - 1)];
         const float neg_lse2 = -stt.x, drow = stt.y;        // dead / out-of-range rows carry lse2 = +inf -> P = 0
         const float sc = p.scale_log2;
-        auto key_ok = [&](int key) -> bool { return key < p.Lk && (km == nullptr || km[key] != 0); };
-        bool ok_n = nblk > 0 ? key_ok(half * 32 + lane) : false;
+        // the mask byte of the NEXT block is requested one iteration ahead and only compared at the top of that iteration: a
+        // compare right behind the load stalled the warp for a global-memory round trip per block (10 % of this kernel's samples)
+        auto key_raw = [&](int key) -> uint32_t { return key < p.Lk ? (km ? static_cast<uint32_t>(km[key]) : 1u) : 0u; };
+        uint32_t mk_n = nblk > 0 ? key_raw(half * 32 + lane) : 0u;
 
         for (int j = 0; j < nblk; ++j) {
             const int st = j & 1;
             const int cbase = j * BT_BLK + half * 32;       // first key of this warp's 32 columns
-            uint32_t vb = __ballot_sync(0xffffffffu, ok_n);
-            if (j + 1 < nblk) ok_n = key_ok(cbase + BT_BLK + lane);
+            uint32_t vb = __ballot_sync(0xffffffffu, mk_n != 0u);
+            if (j + 1 < nblk) mk_n = key_raw(cbase + BT_BLK + lane);
             const bool need_mask = vb != 0xffffffffu || (p.causal && cbase + 31 > qpos_warp_min);
             if (p.causal) {
                 const int nvis = qpos - cbase + 1;
@@ -519,11 +530,12 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar_sfree[st]);      // one arrive per warp: 8 instead of 256 serialised arrivals
-            const float2* stq = sStat + q3 * BT_BLK + half * 32;
+            const uint32_t stq = smem_u32(sStat + q3 * BT_BLK + half * 32);
             uint32_t wp[16], wd[16];
 #pragma unroll
             for (int c = 0; c < 32; c += 2) {
-                const float2 s0 = stq[c], s1 = stq[c + 1];
+                const float4 s01 = lds_f4(stq + static_cast<uint32_t>(c * 8));          // (lse2, D) of queries c and c + 1
+                const float2 s0 = make_float2(s01.x, s01.y), s1 = make_float2(s01.z, s01.w);
                 float p0 = ex2_approx(fmaf(__uint_as_float(sr[c]), sc, -s0.x));
                 float p1 = ex2_approx(fmaf(__uint_as_float(sr[c + 1]), sc, -s1.x));
                 if (need_mask) {
