@@ -175,26 +175,49 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
     if (p.causal) kv_end = min(p.Lk, m0 + BT_TILE + p.q_pos0);
     const int nblk = max(0, (kv_end + BT_BLK - 1) / BT_BLK);
 
-    if (tid == 0) {
-        mbar_init(bar_qdo, 1);
-        for (int i = 0; i < DQ_K_STAGES; ++i) mbar_init(&bar_k[i], 1);
-        for (int i = 0; i < DQ_V_STAGES; ++i) mbar_init(&bar_v[i], 1);
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32);
-            mbar_init(&bar_ds[i], BT_COMPUTE / 32); mbar_init(&bar_dq[i], 1);
+    const int hcol = h * BT_HD;
+    if (warp == 8) {
+        // the thread that initialises the barriers also requests the first operand tiles right away: the TMA round trip then runs
+        // under the TMEM allocation and the CTA-wide barrier instead of after them (every CTA pays this prologue, 10.4 waves)
+        if (lane == 0) {
+            mbar_init(bar_qdo, 1);
+            for (int i = 0; i < DQ_K_STAGES; ++i) mbar_init(&bar_k[i], 1);
+            for (int i = 0; i < DQ_V_STAGES; ++i) mbar_init(&bar_v[i], 1);
+            for (int i = 0; i < 2; ++i) {
+                mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32);
+                mbar_init(&bar_ds[i], BT_COMPUTE / 32); mbar_init(&bar_dq[i], 1);
+            }
+            fence_barrier_init();
+            if (nblk > 0) {
+                tma_prefetch_desc(&tq); tma_prefetch_desc(&tdo); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
+                mbar_arrive_expect_tx(bar_qdo, 2 * TILE_BYTES);
+                tma_load_3d(sQ, &tq, bar_qdo, hcol, m0, b);
+                tma_load_3d(sQ + TILE_BYTES / 2, &tq, bar_qdo, hcol + 64, m0, b);
+                tma_load_3d(sDO, &tdo, bar_qdo, hcol, m0, b);
+                tma_load_3d(sDO + TILE_BYTES / 2, &tdo, bar_qdo, hcol + 64, m0, b);
+                for (int j = 0; j < min(nblk, DQ_K_STAGES); ++j) {
+                    mbar_arrive_expect_tx(&bar_k[j], BLK_BYTES);
+                    tma_load_3d(sK + j * BLK_BYTES, &tk, &bar_k[j], hcol, j * BT_BLK, b);
+                    tma_load_3d(sK + j * BLK_BYTES + BLK_BYTES / 2, &tk, &bar_k[j], hcol + 64, j * BT_BLK, b);
+                }
+                for (int j = 0; j < min(nblk, DQ_V_STAGES); ++j) {
+                    mbar_arrive_expect_tx(&bar_v[j], BLK_BYTES);
+                    tma_load_3d(sV + j * BLK_BYTES, &tv, &bar_v[j], hcol, j * BT_BLK, b);
+                    tma_load_3d(sV + j * BLK_BYTES + BLK_BYTES / 2, &tv, &bar_v[j], hcol + 64, j * BT_BLK, b);
+                }
+            }
         }
-        fence_barrier_init();
+        __syncwarp();
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
     }
-    if (warp == 8) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const int hcol = h * BT_HD;
 
     if (warp == 8) {
         if (lane == 0 && nblk > 0) {
-            tma_prefetch_desc(&tq); tma_prefetch_desc(&tdo); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
             constexpr uint32_t idesc_s = umma_idesc_bf16(BT_TILE, BT_BLK);          // 128 x 64, K-major x K-major
             constexpr uint32_t idesc_q = umma_idesc_bf16_bmn(BT_TILE, BT_HD);       // 128 x 128, B MN-major
             auto load_k = [&](int j) {
@@ -229,14 +252,7 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 }
                 umma_commit(&bar_s[st]);
             };
-            mbar_arrive_expect_tx(bar_qdo, 2 * TILE_BYTES);
-            tma_load_3d(sQ, &tq, bar_qdo, hcol, m0, b);
-            tma_load_3d(sQ + TILE_BYTES / 2, &tq, bar_qdo, hcol + 64, m0, b);
-            tma_load_3d(sDO, &tdo, bar_qdo, hcol, m0, b);
-            tma_load_3d(sDO + TILE_BYTES / 2, &tdo, bar_qdo, hcol + 64, m0, b);
-            for (int j = 0; j < min(nblk, DQ_K_STAGES); ++j) load_k(j);
-            for (int j = 0; j < min(nblk, DQ_V_STAGES); ++j) load_v(j);
-            mbar_wait(bar_qdo, 0);
+            mbar_wait(bar_qdo, 0);                       // Q, dO and the first K / V blocks were requested in the prologue
             issue_sdp(0);
             if (nblk > 1) issue_sdp(1);
             for (int j = 0; j < nblk; ++j) {
@@ -414,24 +430,44 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
     if (p.causal) i_begin = max(0, n0 - p.q_pos0) / BT_BLK;
     const int nq = max(0, nq_total - i_begin);
 
-    if (tid == 0) {
-        mbar_init(bar_kv, 1);
-        for (int i = 0; i < KV_Q_STAGES; ++i) mbar_init(&bar_q[i], 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], BT_COMPUTE / 32); mbar_init(&bar_acc[i], 1); }
-        fence_barrier_init();
+    const int hcol = h * BT_HD;
+    const float2* stat_row = p.stats + (static_cast<long long>(b) * p.H + h) * p.Lqp;
+    if (warp == 8) {
+        if (lane == 0) {                                     // barriers, then the first tiles at once (see the dQ kernel)
+            mbar_init(bar_kv, 1);
+            for (int i = 0; i < KV_Q_STAGES; ++i) mbar_init(&bar_q[i], 1);
+            for (int i = 0; i < 2; ++i) { mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], BT_COMPUTE / 32); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], BT_COMPUTE / 32); mbar_init(&bar_acc[i], 1); }
+            fence_barrier_init();
+            if (nq > 0) {
+                tma_prefetch_desc(&tq); tma_prefetch_desc(&tdo); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
+                mbar_arrive_expect_tx(bar_kv, 2 * TILE_BYTES);
+                tma_load_3d(sK, &tk, bar_kv, hcol, n0, b);
+                tma_load_3d(sK + TILE_BYTES / 2, &tk, bar_kv, hcol + 64, n0, b);
+                tma_load_3d(sV, &tv, bar_kv, hcol, n0, b);
+                tma_load_3d(sV + TILE_BYTES / 2, &tv, bar_kv, hcol + 64, n0, b);
+                for (int jj = 0; jj < min(nq, KV_Q_STAGES); ++jj) {
+                    const int row0 = (i_begin + jj) * BT_BLK;
+                    mbar_arrive_expect_tx(&bar_q[jj], 2 * BLK_BYTES + KV_STAT_BYTES);
+                    tma_load_3d(sQ + jj * BLK_BYTES, &tq, &bar_q[jj], hcol, row0, b);
+                    tma_load_3d(sQ + jj * BLK_BYTES + BLK_BYTES / 2, &tq, &bar_q[jj], hcol + 64, row0, b);
+                    tma_load_3d(sDO + jj * BLK_BYTES, &tdo, &bar_q[jj], hcol, row0, b);
+                    tma_load_3d(sDO + jj * BLK_BYTES + BLK_BYTES / 2, &tdo, &bar_q[jj], hcol + 64, row0, b);
+                    bulk_load_1d(sStat + jj * BT_BLK, stat_row + row0, KV_STAT_BYTES, &bar_q[jj]);
+                }
+            }
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
     }
-    if (warp == 8) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const int hcol = h * BT_HD;
-    const float2* stat_row = p.stats + (static_cast<long long>(b) * p.H + h) * p.Lqp;
 
     if (warp == 8) {
         if (lane == 0 && nq > 0) {
-            tma_prefetch_desc(&tq); tma_prefetch_desc(&tdo); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
             constexpr uint32_t idesc_s = umma_idesc_bf16(BT_TILE, BT_BLK);
             constexpr uint32_t idesc_a = umma_idesc_bf16_bmn(BT_TILE, BT_HD);
             auto load_q = [&](int jj) {
@@ -462,12 +498,6 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                 }
                 umma_commit(&bar_s[st]);
             };
-            mbar_arrive_expect_tx(bar_kv, 2 * TILE_BYTES);
-            tma_load_3d(sK, &tk, bar_kv, hcol, n0, b);
-            tma_load_3d(sK + TILE_BYTES / 2, &tk, bar_kv, hcol + 64, n0, b);
-            tma_load_3d(sV, &tv, bar_kv, hcol, n0, b);
-            tma_load_3d(sV + TILE_BYTES / 2, &tv, bar_kv, hcol + 64, n0, b);
-            for (int jj = 0; jj < min(nq, KV_Q_STAGES); ++jj) load_q(jj);
             mbar_wait(bar_kv, 0);
             issue_s(0);
             if (nq > 1) issue_s(1);

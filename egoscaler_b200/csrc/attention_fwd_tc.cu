@@ -244,12 +244,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             }
             // ---- P -> smem (K-major, 128B swizzle: 16-byte unit u of row r lives at unit u ^ (r & 7))
             {
-                uint8_t* prow = sP + tid * 128;
+                const uint32_t prow = smem_u32(sP) + static_cast<uint32_t>(tid * 128);     // explicit st.shared (not a generic ST.E)
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const uint4 val = make_uint4(pk[u * 4 + 0], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
-                    *reinterpret_cast<uint4*>(prow + ((u ^ (tid & 7)) << 4)) = val;
-                }
+                for (int u = 0; u < 8; ++u)
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + static_cast<uint32_t>((u ^ (tid & 7)) << 4)),
+                                 "r"(pk[u * 4 + 0]), "r"(pk[u * 4 + 1]), "r"(pk[u * 4 + 2]), "r"(pk[u * 4 + 3])
+                                 : "memory");
             }
             fence_proxy_async();
             tc_fence_before();
