@@ -79,16 +79,36 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     if (p.causal) kv_end = min(p.Lk, m0 + FA_BM + p.q_pos0);
     const int nblk = (kv_end + FA_BN - 1) / FA_BN;
 
-    if (tid == 0) {
-        mbar_init(bar_q, 1);
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&bar_k[i], 1); mbar_init(&bar_v[i], 1); mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], FA_SOFTMAX_THREADS);
+    const int hcol = h * FA_HD;
+    if (warp == 4) {
+        // barriers, then the first tiles at once: the TMA round trip runs under the TMEM allocation and the CTA barrier
+        if (lane == 0) {
+            mbar_init(bar_q, 1);
+            for (int i = 0; i < 2; ++i) {
+                mbar_init(&bar_k[i], 1); mbar_init(&bar_v[i], 1); mbar_init(&bar_s[i], 1); mbar_init(&bar_sfree[i], FA_SOFTMAX_THREADS);
+            }
+            mbar_init(bar_o, 1);
+            mbar_init(bar_p, FA_SOFTMAX_THREADS);
+            fence_barrier_init();
+            if (nblk > 0) {
+                tma_prefetch_desc(&tq); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
+                mbar_arrive_expect_tx(bar_q, Q_BYTES);
+                tma_load_3d(sQ, &tq, bar_q, hcol, m0, b);
+                tma_load_3d(sQ + Q_BYTES / 2, &tq, bar_q, hcol + 64, m0, b);
+                for (int j = 0; j < min(nblk, 2); ++j) {
+                    mbar_arrive_expect_tx(&bar_k[j], K_BYTES);
+                    tma_load_3d(sK + j * K_BYTES, &tk, &bar_k[j], hcol, j * FA_BN, b);
+                    tma_load_3d(sK + j * K_BYTES + K_BYTES / 2, &tk, &bar_k[j], hcol + 64, j * FA_BN, b);
+                }
+                mbar_arrive_expect_tx(&bar_v[0], V_BYTES);
+                tma_load_3d(sV, &tv, &bar_v[0], hcol, 0, b);
+                tma_load_3d(sV + V_BYTES / 2, &tv, &bar_v[0], hcol + 64, 0, b);
+            }
         }
-        mbar_init(bar_o, 1);
-        mbar_init(bar_p, FA_SOFTMAX_THREADS);
-        fence_barrier_init();
+        __syncwarp();
+        tmem_alloc(tmem_slot, TMEM_COLS);
+        tmem_relinquish();
     }
-    if (warp == 4) { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -98,10 +118,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     if (warp == 4) {
         if (lane == 0 && nblk > 0) {
             // ================================================= TMA producer + MMA issuer
-            tma_prefetch_desc(&tq); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv);
             constexpr uint32_t idesc_s = umma_idesc_bf16(FA_BM, FA_BN);
             constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(FA_BM, FA_HD);
-            const int hcol = h * FA_HD;
             auto load_k = [&](int j) {
                 const int st = j & 1;
                 mbar_arrive_expect_tx(&bar_k[st], K_BYTES);
@@ -127,13 +145,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 }
                 umma_commit(&bar_s[st]);
             };
-            mbar_arrive_expect_tx(bar_q, Q_BYTES);
-            tma_load_3d(sQ, &tq, bar_q, hcol, m0, b);
-            tma_load_3d(sQ + Q_BYTES / 2, &tq, bar_q, hcol + 64, m0, b);
-            load_k(0);
-            if (nblk > 1) load_k(1);
-            load_v(0);
-            mbar_wait(bar_q, 0);
+            mbar_wait(bar_q, 0);                         // Q, K_0, K_1 and V_0 were requested in the prologue
             issue_s(0);
             if (nblk > 1) issue_s(1);
             for (int j = 0; j < nblk; ++j) {
