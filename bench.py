@@ -367,7 +367,7 @@ def run_b200(args):
                 "ms_per_step": round(ms_e2e / args.steps, 3)},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05_kernel", "achieved": round(achieved_tf, 1), "peak": peak_tf,
+        "roofline": {"bound": "tensor", "kernel": "gemm2_bf16_tcgen05_kernel (CTA pairs, large shapes) + gemm_bf16_tcgen05_kernel", "achieved": round(achieved_tf, 1), "peak": peak_tf,
                      "unit": "TFLOP/s", "frac": round(achieved_tf / peak_tf, 4), "traffic": gemm_traffic(), "peak_source": peak_src,
                      "traffic_source": "committed ncu --set full capture (profiles/gemm_traffic.json), not measured in this run",
                      "timing": "CUDA events around every GEMM launch in a separate pass of the same resident step "
