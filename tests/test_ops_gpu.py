@@ -42,6 +42,33 @@ def test_rmsnorm_fwd_bwd(rows, d):
     close(ops.rmsnorm(big[:, :d], w, 1e-6), ops.rmsnorm(big[:, :d].contiguous(), w, 1e-6), 0.0)
 
 
+def test_rmsnorm_register_path_equals_general_path():
+    """d = 16 x threads (the trunk's 4096): the register-resident kernels against the general two-pass kernels
+    (ESB_RMSNORM_GENERIC=1 selects those), with and without residual / weight gradient, over several rows per CTA."""
+    import os
+    rows, d = 5568, 4096
+    x, w, dy, dres = rnd(rows, d, seed=11), (1 + 0.1 * rnd(d, seed=12).float()).bfloat16(), rnd(rows, d, seed=13), rnd(rows, d, seed=14)
+    res = {}
+    for mode in ("0", "1"):
+        os.environ["ESB_RMSNORM_GENERIC"] = mode
+        try:
+            y, rstd = ops.rmsnorm(x, w, 1e-6, want_rstd=True)
+            dx_plain = ops.rmsnorm_bwd(dy, x, w, rstd)
+            dw = torch.zeros(d, device="cuda")
+            dx_full = ops.rmsnorm_bwd(dy, x, w, rstd, dres=dres, dw=dw)
+        finally:
+            os.environ.pop("ESB_RMSNORM_GENERIC", None)
+        res[mode] = (y, rstd, dx_plain, dx_full, dw)
+    # same formulas; the compiler contracts the sums of products into FMAs differently in the two code shapes, so fp32
+    # statistics agree to round-off and a few bf16 outputs land on the neighbouring value
+    torch.testing.assert_close(res["0"][1], res["1"][1], rtol=2e-6, atol=0)
+    for a, b in zip((res["0"][0], res["0"][2], res["0"][3]), (res["1"][0], res["1"][2], res["1"][3])):
+        diff = (a.float() - b.float()).abs()
+        assert float((diff > 0).float().mean()) < 2e-2
+        assert bool((diff <= 2.0 ** -7 * b.float().abs() + 1e-6).all())              # at most one bf16 ulp
+    close(res["0"][4], res["1"][4], 1e-4)          # fp32 atomics over CTAs: order differs with the grid size
+
+
 @pytest.mark.parametrize("rows,d", [(1026, 384), (50, 1152)])
 def test_layernorm_fused_add(rows, d):
     x, add = rnd(rows, d, seed=1), rnd(rows, d, seed=2)
