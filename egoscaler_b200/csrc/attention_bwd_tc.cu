@@ -507,10 +507,6 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                     mbar_wait(&bar_acc[(jj - 1) & 1], ((jj - 1) >> 1) & 1);
                     load_q(jj + 2);
                 }
-                if (jj + 2 < nq) {                       // same early issue as in the dQ kernel
-                    mbar_wait(&bar_sfree[st], (jj >> 1) & 1);
-                    issue_s(jj + 2);
-                }
                 mbar_wait(&bar_p[st], (jj >> 1) & 1);    // P^T_jj, dS^T_jj are in smem (buffer st)
                 tc_fence_after();
                 const uint32_t apt = smem_u32(sPT + st * OP_BYTES), adst = smem_u32(sDST + st * OP_BYTES), aq = smem_u32(sQ + q3 * BLK_BYTES), ado = smem_u32(sDO + q3 * BLK_BYTES);
@@ -527,6 +523,13 @@ attn_bwd_dkdv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_con
                     umma_bf16_ss(tmem_base + 384, da, db, idesc_a, (jj | ks) != 0 ? 1u : 0u);
                 }
                 umma_commit(&bar_acc[st]);
+                // S^T / dP^T of block jj+2 go out BEHIND the accumulate MMAs of block jj: their Q / dO stage was requested at the
+                // top of this iteration, and with only 3 stages its TMA round trip (~1 us) used to stall this thread in front of
+                // the accumulate MMAs every iteration (ncu: the compute warps of this kernel waited 17 % + 9 % on S and Q)
+                if (jj + 2 < nq) {
+                    mbar_wait(&bar_sfree[st], (jj >> 1) & 1);
+                    issue_s(jj + 2);
+                }
             }
         }
     } else {
