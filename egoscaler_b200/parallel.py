@@ -81,7 +81,7 @@ class GradExchange:
         if self.world == 1 or (self._reduce_is_allreduce and t.is_cuda):
             return self.all_gather(t), None
         out = torch.empty((self.world,) + tuple(t.shape), device=t.device, dtype=t.dtype)
-        return out, self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.pg, async_op=True)
+        return out, self.dist.all_gather_into_tensor(self._gather_view(out, t), t.contiguous(), group=self.pg, async_op=True)
 
     def reduce_to_owner_async(self, unit: int, tensor: torch.Tensor) -> None:
         if self.world == 1:
@@ -102,8 +102,15 @@ class GradExchange:
             out[self.rank].copy_(t)
             self.dist.all_reduce(out, op=self.dist.ReduceOp.SUM, group=self.pg)
         else:
-            self.dist.all_gather_into_tensor(out, t.contiguous(), group=self.pg)
+            self.dist.all_gather_into_tensor(self._gather_view(out, t), t.contiguous(), group=self.pg)
         return out
+
+    def _gather_view(self, out: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+        """gloo (CPU tensors, the host-logic tests) only accepts the CONCATENATED output form [world * n, ...]; NCCL takes the
+        stacked [world, n, ...] buffer as it is."""
+        if t.is_cuda or t.dim() == 0:
+            return out
+        return out.view((self.world * t.shape[0],) + tuple(t.shape[1:]))
 
     def broadcast_from_owners(self, units: Sequence["tuple[int, torch.Tensor]"]) -> None:
         if self.world == 1:

@@ -50,6 +50,22 @@ def _worker(rank, world, port, q):
         dp.allreduce_async(g)
         dp.wait()
         assert torch.equal(g[0], torch.full((5, 3), 3.0)) and torch.equal(g[1], torch.arange(7.0) * 3)
+        # (1b) named all-reduces (the optimizer waits per tensor / per bucket), asynchronous gathers (embedding rows + ids)
+        a, bkt = torch.full((3,), float(rank + 1)), torch.arange(6.0) + rank
+        dp.allreduce_async_named([("lm_head.weight", a), ("bucket:point_proj", bkt)])
+        rows, w_rows = dp.all_gather_async(torch.full((2, 4), float(rank)))
+        ids, w_ids = dp.all_gather_async(torch.tensor([10 + rank, 20 + rank]))
+        assert set(dp._named) == {"lm_head.weight", "bucket:point_proj"}
+        dp.wait_named("lm_head.weight")
+        assert torch.equal(a, torch.full((3,), 3.0)) and "lm_head.weight" not in dp._named
+        dp.wait_named("not pending")                                                 # no-op
+        dp.wait()                                                                    # joins whatever is left, named included
+        assert torch.equal(bkt, 2 * torch.arange(6.0) + 1) and not dp._named
+        for w in (w_rows, w_ids):
+            if w is not None:
+                w.wait()
+        assert rows.shape == (2, 2, 4) and torch.equal(rows[1], torch.ones(2, 4)) and torch.equal(rows[0], torch.zeros(2, 4))
+        assert ids.tolist() == [[10, 20], [11, 21]]
         # (2) ZeRO-1: reduce to owner, owner "steps", broadcast the updated weights
         units = [torch.full((4,), float(10 * u + rank)) for u in range(5)]          # gradients
         weights = [torch.zeros(4) for _ in range(5)]
@@ -83,6 +99,10 @@ def _worker(rank, world, port, q):
         dp.allreduce_async(grads.values())
         dp.wait()
         q.put((rank, float(loss), {n: (g * dp.grad_scale).numpy() for n, g in grads.items()}))
+    except Exception:                                            # report instead of leaving the parent to time out
+        import traceback
+        q.put((rank, None, traceback.format_exc()))
+        raise
     finally:
         dist.destroy_process_group()
 
@@ -96,6 +116,8 @@ def test_grad_exchange_world2_gloo():
     for p in procs:
         p.start()
     res = [q.get(timeout=500) for _ in range(world)]
+    for r in res:
+        assert r[1] is not None, f"rank {r[0]} failed:\n{r[2]}"
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
